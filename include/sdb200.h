@@ -1,0 +1,142 @@
+/* sdb200 — C ABI of the B200-native (sm_100a) denoising train-step kernels.
+ *
+ * This is the drop-in boundary for ONE hot path of lodestone-rock/stable_diffusion_training: the data-parallel
+ * denoising train step (training_utils.py:504-762) and the operators it runs (schedulers/, lion_quant.py, the
+ * diffusers-0.21.4 Flax UNet it calls). The reference has no FFI of its own (pure JAX); each entry point below cites
+ * the reference code it replaces, and INTEGRATION.md shows the ctypes stub a maintainer would add.
+ *
+ * Conventions (all entry points):
+ *   - plain pointers and sizes only; every pointer is a DEVICE pointer unless the name ends in _host;
+ *   - the caller owns every buffer including workspaces; the library allocates nothing persistent;
+ *   - return 0 on success, a negative SdbStatus on failure; sdb_last_error_string() gives the thread-local reason;
+ *   - never throws, never exits, never synchronises: work is only enqueued on `stream` (CUDA-graph capturable);
+ *   - bf16 tensors are passed as `void*` (raw __nv_bfloat16 storage); activations are NHWC ("pixels x channels").
+ */
+#ifndef SDB200_H
+#define SDB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SDB200_ABI_VERSION 1
+
+#ifndef __CUDA_RUNTIME_H__
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+/* ---- library ---- */
+const char* sdb_last_error_string(void);
+int sdb_abi_version(void);
+int sdb_check_device(int device); /* fails unless the device is compute capability 10.x */
+
+/* ---- 8-bit Lion (lion_quant.py:20-156, chain 201-211; optax clip/apply as wired at training_utils.py:355-382, 732)
+ * One launch over a flat fp32 segment. Block b of 16 consecutive elements has int8 codes[16*b .. 16*b+15] and the
+ * RECIPROCAL absmax inv_scales[b] (lion_quant.py:66-80). `gnorm_dev` (nullable) is the global gradient norm: when
+ * it is >= max_norm the gradient is divided by it first (optax.clip_by_global_norm).
+ * mode 0: out = p + (-lr) * (sign(c) + wd*p)   (out may alias p_in; optax.apply_updates fused)
+ * mode 1: out =     (-lr) * (sign(c) + wd*p)   (the optax `updates` tree, parameters untouched)
+ * shadow_bf16 (nullable, mode 0 only): bf16 copy of the new parameters for the GEMM operands. */
+int sdb_lion8_update(const float* g, const float* p_in, float* out, void* shadow_bf16, int8_t* codes,
+                     float* inv_scales, long long n, int block_size, double b1, double b2, double lr, double wd,
+                     int wd_flag, const float* gnorm_dev, double max_norm, int mode, cudaStream_t stream);
+
+/* Unquantised-state leaves of the same optimizer (lion_quant.py:109, 145). */
+int sdb_lion_fp32_update(const float* g, const float* p_in, float* out, void* shadow_bf16, float* mu, long long n,
+                         double b1, double b2, double lr, double wd, int wd_flag, const float* gnorm_dev,
+                         double max_norm, int mode, cudaStream_t stream);
+
+/* optax.global_norm over a flat fp32 buffer: gnorm_out[0] = sqrt(sum x^2 [+ carried sum if accumulate]).
+ * Deterministic (fixed grid, fixed reduction tree). Workspace: sdb_sumsq_workspace_bytes(). */
+size_t sdb_sumsq_workspace_bytes(void);
+int sdb_global_norm(const float* x, long long n, void* workspace, size_t ws_bytes, float* gnorm_out, int accumulate,
+                    cudaStream_t stream);
+
+/* ---- schedulers (schedulers/scheduling_utils_flax.py:316-343; scheduling_ddpm_flax.py:196-297) ---- */
+int sdb_add_noise(const float* original_samples, const float* noise, const int* timesteps, const float* alphas_cumprod,
+                  float* noisy, int batch, long long per_sample, cudaStream_t stream);
+int sdb_get_velocity(const float* sample, const float* noise, const int* timesteps, const float* alphas_cumprod,
+                     float* velocity, int batch, long long per_sample, cudaStream_t stream);
+/* prediction_type: 0 epsilon, 1 sample, 2 v_prediction. Scalars are computed by the host in fp32 exactly as the
+ * reference does (scheduling_ddpm_flax.py:229-264); noise == NULL means t == 0 (no variance term). */
+int sdb_ddpm_step(const float* model_output, const float* sample, const float* noise, float* prev_sample, long long n,
+                  float sqrt_alpha_prod, float sqrt_beta_prod, float pred_original_coeff, float current_sample_coeff,
+                  float sigma, int prediction_type, int clip_sample, cudaStream_t stream);
+
+/* ---- loss (training_utils.py:704-709, min-SNR weight 546-568) ----
+ * pred: UNet output NHWC bf16 [B,HW,C]; target: NCHW fp32 [B,C,HW]; sample_weight: nullable fp32 [B].
+ * loss[0] = mean(w_b (target-pred)^2); dpred (nullable) = d loss / d pred * loss_grad_scale, NHWC bf16. */
+size_t sdb_mse_workspace_bytes(void);
+int sdb_mse_fwd_bwd(const void* pred_nhwc_bf16, const float* target_nchw, const float* sample_weight,
+                    void* dpred_nhwc_bf16, float* loss, int B, int C, int HW, float loss_grad_scale, void* workspace,
+                    size_t ws_bytes, cudaStream_t stream);
+
+/* ---- tensor-core GEMM / implicit-GEMM convolution (tcgen05 + TMEM + TMA) ----
+ * Replaces flax nn.Conv / nn.Dense forward and their VJPs inside FlaxUNet2DConditionModel (diffusers 0.21.4,
+ * called at training_utils.py:678-684).
+ *
+ * A 4-D bf16 view: extents (C innermost, then W, H, N) with element strides; C is contiguous. A [rows, cols]
+ * matrix is {C = cols, W = rows, H = N = 1, strideW = ld}. Strides must be multiples of 8 elements. */
+typedef struct {
+  const void* ptr;
+  int C, W, H, N;
+  long long strideW, strideH, strideN;
+} sdb_view4;
+
+#define SDB_MAX_TAPS 9
+#define SDB_MAX_SRC 4
+
+/* mode SDB_GEMM_FWD:  D[pixel, n] = sum_taps sum_k A_src(tap)[pixel + (dh,dw), k] * Bop[tap][k, n]   (+ epilogue)
+ *      the output pixel space is (outW, outH, outN); a tile is a box (bw, bh, bn) of 128 pixels.
+ *      b_mn_major = 1: B memory is [K rows, N cols] (forward weights, Flax HWIO / (in,out));
+ *                      tap_brow[t] = first K row of tap t.
+ *      b_mn_major = 0: B memory is [N rows, K cols] (the same weights used transposed for dgrad);
+ *                      tap_brow[t] = first N row of tap t.
+ *      epilogue: + bias[n] (fp32, nullable) + temb[img, n] (fp32, nullable, row stride N)
+ *                + residual[pixel, n] (bf16, nullable, row stride ldr); output bf16, row stride ldd.
+ * mode SDB_GEMM_WGRAD: dW[tap_brow[t] + m, n] (+)= sum_pixels A_src(tap)[pixel + (dh,dw), m] * B[pixel, n]
+ *      A and B are both pixel-major activations (B is passed as `b`, a 4-D view over the same pixel space);
+ *      a K block is a box (bw, bh, bn) of 64 pixels; output fp32 with row stride ldd; `splits` > 1 splits the pixel
+ *      range and accumulates with red.global.add (the caller zeroes D first); splits == 1 stores.  */
+enum { SDB_GEMM_FWD = 0, SDB_GEMM_WGRAD = 1 };
+
+typedef struct {
+  int mode;
+  int num_src;
+  sdb_view4 a[SDB_MAX_SRC];
+  sdb_view4 b;
+  int b_mn_major;
+  int ntaps;
+  int tap_src[SDB_MAX_TAPS];
+  int tap_dh[SDB_MAX_TAPS];
+  int tap_dw[SDB_MAX_TAPS];
+  int tap_brow[SDB_MAX_TAPS];
+  int outW, outH, outN; /* pixel space */
+  int bw, bh, bn;       /* pixel box: 128 pixels (FWD) / 64 pixels (WGRAD) */
+  int M;                /* WGRAD: rows of dW per tap (Cin). FWD: ignored (pixels) */
+  int N;                /* output columns */
+  int K;                /* FWD: reduction length per tap (channels of A) */
+  int block_n;          /* N tile width, multiple of 16, <= 256 (multiple of 64 when B is MN-major) */
+  int splits;           /* WGRAD only */
+  void* d;
+  long long ldd;
+  const float* bias;
+  const float* temb;
+  const void* residual;
+  long long ldr;
+} sdb_gemm_desc;
+
+int sdb_gemm_tc(const sdb_gemm_desc* desc, cudaStream_t stream);
+
+/* Reference-quality CUDA-core GEMM for shapes the tensor-core tiles do not cover (time embedding M = batch,
+ * conv_in K = 4 per tap, conv_out N = 4) and as the on-device cross-check of sdb_gemm_tc in the tests.
+ * Same descriptor, same semantics; no alignment or divisibility constraints. */
+int sdb_gemm_simt(const sdb_gemm_desc* desc, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDB200_H */

@@ -1,0 +1,479 @@
+// Tensor-core GEMM / implicit-GEMM 3x3 convolution for sm_100a: TMA -> smem ring -> tcgen05.mma -> TMEM -> epilogue.
+//
+// Replaces flax nn.Conv / nn.Dense (forward, dgrad, wgrad) inside FlaxUNet2DConditionModel [diffusers 0.21.4,
+// un-vendored; call site /root/reference/training_utils.py:678-684] — SURVEY §2.1 K1/K2.
+//
+// One persistent, warp-specialised kernel (one CTA per SM, 192 threads):
+//   warp 0      : TMA producer  — 4-D tiled tensor maps over NHWC activations; a 3x3 tap is a box shifted by
+//                 (dh, dw) whose out-of-bounds part TMA zero-fills (= the conv padding); weights are 2-D boxes.
+//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x N x 16, bf16 -> fp32).
+//   warps 2..5  : epilogue — tcgen05.ld of the accumulator (one row per thread), bias / time-embedding / residual
+//                 add, bf16 (or fp32 / red.add for wgrad) stores.
+// Two 256-column TMEM accumulators let the epilogue of tile i overlap the main loop of tile i+1.
+//
+// Operand layouts (all SWIZZLE_128B, produced directly by TMA):
+//   activations as A (fwd/dgrad)     K-major : 128 pixel rows x 64 channels (128 B rows)
+//   weights [K,N] as B (fwd)         MN-major: per 64-column box, 64 K rows x 128 B; boxes 8 KB apart (LBO)
+//   weights [N,K] as B (dgrad)       K-major : N rows x 64 channels
+//   activations as A and B (wgrad)   MN-major: per 64-channel box, 64 pixel rows x 128 B
+#include "sdb_common.cuh"
+#include "ptx_sm100.cuh"
+#include "../../include/sdb200.h"
+#include <mutex>
+
+namespace {
+
+constexpr int kThreads = 192;
+constexpr int kBlockK = 64;                 // bf16 elements per K block (one 128-byte swizzle row)
+constexpr uint32_t kAStageBytes = 128 * 128;  // 16 KB: 128 rows x 128 B, or two 64-row MN-major boxes
+constexpr uint32_t kBoxBytes = 64 * 128;      // one 64-row box
+constexpr int kMaxStages = 8;
+constexpr uint32_t kTmemCols = 512;
+constexpr uint32_t kAccCols = 256;
+
+struct alignas(64) TcParams {
+  CUtensorMap mapA[SDB_MAX_SRC];
+  CUtensorMap mapB;
+  int mode, b_mn, ntaps;
+  int tap_src[SDB_MAX_TAPS], tap_dh[SDB_MAX_TAPS], tap_dw[SDB_MAX_TAPS], tap_brow[SDB_MAX_TAPS];
+  int W, H, NI, bw, bh, bn, tw, th, tn;
+  int M, N, K, BN;
+  int tiles_m, tiles_n, total_tiles, kblocks;
+  int splits, pb_per_split, total_pb;
+  int stages;
+  uint32_t b_stage_bytes, stage_bytes;
+  void* d;
+  long long ldd;
+  const float* bias;
+  const float* temb;
+  const __nv_bfloat16* residual;
+  long long ldr;
+};
+
+struct Tile {
+  int n_off, nw, umma_n, nboxes;
+  int w0, h0, n0;          // FWD: pixel origin of the M tile
+  int tap, m_off;          // WGRAD
+  int kb_begin, num_k;     // K iterations
+};
+
+__device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
+  Tile ti;
+  if (p.mode == SDB_GEMM_FWD) {
+    int n_tile = t % p.tiles_n;
+    int m_tile = t / p.tiles_n;
+    int iw = m_tile % p.tw;
+    int r = m_tile / p.tw;
+    int ih = r % p.th;
+    int in = r / p.th;
+    ti.w0 = iw * p.bw;
+    ti.h0 = ih * p.bh;
+    ti.n0 = in * p.bn;
+    ti.n_off = n_tile * p.BN;
+    ti.tap = 0;
+    ti.m_off = 0;
+    ti.kb_begin = 0;
+    ti.num_k = p.ntaps * p.kblocks;
+  } else {
+    int split = t % p.splits;
+    int r = t / p.splits;
+    int n_tile = r % p.tiles_n;
+    r /= p.tiles_n;
+    int m_tile = r % p.tiles_m;
+    ti.tap = r / p.tiles_m;
+    ti.m_off = m_tile * 128;
+    ti.n_off = n_tile * p.BN;
+    ti.kb_begin = split * p.pb_per_split;
+    int kb_end = min(p.total_pb, ti.kb_begin + p.pb_per_split);
+    ti.num_k = kb_end - ti.kb_begin;
+    ti.w0 = ti.h0 = ti.n0 = 0;
+  }
+  ti.nw = min(p.BN, p.N - ti.n_off);
+  ti.umma_n = (ti.nw + 15) & ~15;
+  ti.nboxes = (ti.umma_n + 63) >> 6;
+  return ti;
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ TcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (size_t)p.stages * p.stage_bytes);
+  uint64_t* full_bar = bars;
+  uint64_t* empty_bar = bars + kMaxStages;
+  uint64_t* tmem_full = bars + 2 * kMaxStages;
+  uint64_t* tmem_empty = bars + 2 * kMaxStages + 2;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    for (int i = 0; i < SDB_MAX_SRC; ++i) ptx::tma_prefetch_desc(&p.mapA[i]);
+    ptx::tma_prefetch_desc(&p.mapB);
+    for (int s = 0; s < p.stages; ++s) {
+      ptx::mbar_init(&full_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      ptx::mbar_init(&tmem_full[a], 1);
+      ptx::mbar_init(&tmem_empty[a], 128);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(tmem_ptr_smem, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+        const Tile ti = decode_tile(p, t);
+        for (int it = 0; it < ti.num_k; ++it) {
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
+          uint8_t* sb = sa + kAStageBytes;
+          if (MODE == SDB_GEMM_FWD) {
+            const int tap = it / p.kblocks;
+            const int kb = it - tap * p.kblocks;
+            const uint32_t bbytes = p.b_mn ? (uint32_t)ti.nboxes * kBoxBytes : p.b_stage_bytes;
+            ptx::mbar_expect_tx(&full_bar[stage], kAStageBytes + bbytes);
+            ptx::tma_load_4d(sa, &p.mapA[p.tap_src[tap]], &full_bar[stage], kb * kBlockK, ti.w0 + p.tap_dw[tap],
+                             ti.h0 + p.tap_dh[tap], ti.n0);
+            if (p.b_mn) {
+              for (int j = 0; j < ti.nboxes; ++j)
+                ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j,
+                                 p.tap_brow[tap] + kb * kBlockK, 0, 0);
+            } else {
+              ptx::tma_load_4d(sb, &p.mapB, &full_bar[stage], kb * kBlockK, p.tap_brow[tap] + ti.n_off, 0, 0);
+            }
+          } else {
+            const int pb = ti.kb_begin + it;
+            const int iw = pb % p.tw;
+            const int r = pb / p.tw;
+            const int ih = r % p.th;
+            const int in = r / p.th;
+            const int pw0 = iw * p.bw, ph0 = ih * p.bh, pn0 = in * p.bn;
+            ptx::mbar_expect_tx(&full_bar[stage], 2 * kBoxBytes + (uint32_t)ti.nboxes * kBoxBytes);
+            const CUtensorMap* ma = &p.mapA[p.tap_src[ti.tap]];
+            for (int i = 0; i < 2; ++i)
+              ptx::tma_load_4d(sa + i * kBoxBytes, ma, &full_bar[stage], ti.m_off + 64 * i, pw0 + p.tap_dw[ti.tap],
+                               ph0 + p.tap_dh[ti.tap], pn0);
+            for (int j = 0; j < ti.nboxes; ++j)
+              ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j, pw0, ph0, pn0);
+          }
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int tile_count = 0;
+      const int a_mn = (MODE == SDB_GEMM_WGRAD) ? 1 : 0;
+      const int b_mn = (MODE == SDB_GEMM_WGRAD) ? 1 : p.b_mn;
+      const uint32_t a_lbo = a_mn ? kBoxBytes : 0u, a_kadv = a_mn ? 2048u : 32u;
+      const uint32_t b_lbo = b_mn ? kBoxBytes : 0u, b_kadv = b_mn ? 2048u : 32u;
+      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tile_count) {
+        const Tile ti = decode_tile(p, t);
+        const int acc = tile_count & 1;
+        const uint32_t acc_phase = (uint32_t)(tile_count >> 1) & 1u;
+        ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t tmem_d = tmem_base + (uint32_t)acc * kAccCols;
+        const uint32_t idesc = ptx::umma_idesc_bf16(ti.umma_n, a_mn, b_mn);
+        for (int it = 0; it < ti.num_k; ++it) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after();
+          const uint32_t sa = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes);
+          const uint32_t sb = sa + kAStageBytes;
+#pragma unroll
+          for (int ks = 0; ks < kBlockK / 16; ++ks) {
+            const uint64_t da = ptx::umma_desc_sw128(sa + ks * a_kadv, a_lbo, 1024u);
+            const uint64_t db = ptx::umma_desc_sw128(sb + ks * b_kadv, b_lbo, 1024u);
+            ptx::umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+          }
+          ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+        ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;
+    int tile_count = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tile_count) {
+      const Tile ti = decode_tile(p, t);
+      const int acc = tile_count & 1;
+      const uint32_t acc_phase = (uint32_t)(tile_count >> 1) & 1u;
+      ptx::mbar_wait(&tmem_full[acc], acc_phase);
+      ptx::tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kAccCols;
+
+      if (MODE == SDB_GEMM_FWD) {
+        const int wi = row % p.bw;
+        const int r2 = row / p.bw;
+        const int hi = r2 % p.bh;
+        const int ni = r2 / p.bh;
+        const int w = ti.w0 + wi, h = ti.h0 + hi, n = ti.n0 + ni;
+        const bool valid = (w < p.W) && (h < p.H) && (n < p.NI);
+        const long long grow = ((long long)n * p.H + h) * p.W + w;
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.d) + grow * p.ldd + ti.n_off;
+        const __nv_bfloat16* res = p.residual ? p.residual + grow * p.ldr + ti.n_off : nullptr;
+        const float* bias = p.bias ? p.bias + ti.n_off : nullptr;
+        const float* temb = p.temb ? p.temb + (long long)n * p.N + ti.n_off : nullptr;
+        for (int c0 = 0; c0 < ti.nw; c0 += 32) {
+          uint32_t v[32];
+          ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
+          ptx::tmem_ld_wait();
+          if (valid) {
+#pragma unroll
+            for (int j8 = 0; j8 < 32; j8 += 8) {
+              if (c0 + j8 < ti.nw) {
+                float f[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[j8 + j]);
+                if (bias) {
+                  const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + c0 + j8));
+                  const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + c0 + j8 + 4));
+                  f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                  f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+                }
+                if (temb) {
+                  const float4 b0 = __ldg(reinterpret_cast<const float4*>(temb + c0 + j8));
+                  const float4 b1 = __ldg(reinterpret_cast<const float4*>(temb + c0 + j8 + 4));
+                  f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
+                  f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+                }
+                if (res) {
+                  const uint4 rv = sdb::ld_u4(res + c0 + j8);
+                  f[0] += sdb::bf16_lo(rv.x); f[1] += sdb::bf16_hi(rv.x);
+                  f[2] += sdb::bf16_lo(rv.y); f[3] += sdb::bf16_hi(rv.y);
+                  f[4] += sdb::bf16_lo(rv.z); f[5] += sdb::bf16_hi(rv.z);
+                  f[6] += sdb::bf16_lo(rv.w); f[7] += sdb::bf16_hi(rv.w);
+                }
+                uint4 o;
+                o.x = sdb::pack_bf16x2(f[0], f[1]);
+                o.y = sdb::pack_bf16x2(f[2], f[3]);
+                o.z = sdb::pack_bf16x2(f[4], f[5]);
+                o.w = sdb::pack_bf16x2(f[6], f[7]);
+                sdb::st_u4(out + c0 + j8, o);
+              }
+            }
+          }
+        }
+      } else {
+        const int m = ti.m_off + row;
+        const bool valid = m < p.M;
+        float* out = reinterpret_cast<float*>(p.d) + ((long long)p.tap_brow[ti.tap] + m) * p.ldd + ti.n_off;
+        for (int c0 = 0; c0 < ti.nw; c0 += 32) {
+          uint32_t v[32];
+          ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
+          ptx::tmem_ld_wait();
+          if (valid) {
+#pragma unroll
+            for (int j4 = 0; j4 < 32; j4 += 4) {
+              if (c0 + j4 < ti.nw) {
+                float* dst = out + c0 + j4;
+                if (p.splits > 1) {
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst),
+                               "f"(__uint_as_float(v[j4])), "f"(__uint_as_float(v[j4 + 1])),
+                               "f"(__uint_as_float(v[j4 + 2])), "f"(__uint_as_float(v[j4 + 3]))
+                               : "memory");
+                } else {
+                  sdb::st_f4(dst, make_float4(__uint_as_float(v[j4]), __uint_as_float(v[j4 + 1]),
+                                              __uint_as_float(v[j4 + 2]), __uint_as_float(v[j4 + 3])));
+                }
+              }
+            }
+          }
+        }
+      }
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&tmem_empty[acc]);
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ---------------- host side ----------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+int encode_view(CUtensorMap* map, const sdb_view4& v, int b0, int b1, int b2, int b3, const char* what) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (!fn) return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: cuTensorMapEncodeTiled entry point unavailable");
+  if (v.ptr == nullptr || (((uintptr_t)v.ptr) & 15) != 0)
+    return sdb_set_error(SDB_ERR_INVALID, "sdb_gemm_tc: %s pointer must be non-null and 16-byte aligned", what);
+  if (v.C <= 0 || v.W <= 0 || v.H <= 0 || v.N <= 0)
+    return sdb_set_error(SDB_ERR_INVALID, "sdb_gemm_tc: %s has a non-positive extent", what);
+  if ((v.strideW % 8) || (v.strideH % 8) || (v.strideN % 8))
+    return sdb_set_error(SDB_ERR_INVALID, "sdb_gemm_tc: %s strides must be multiples of 8 elements", what);
+  cuuint64_t gdim[4] = {(cuuint64_t)v.C, (cuuint64_t)v.W, (cuuint64_t)v.H, (cuuint64_t)v.N};
+  cuuint64_t gstr[3] = {(cuuint64_t)v.strideW * 2, (cuuint64_t)v.strideH * 2, (cuuint64_t)v.strideN * 2};
+  cuuint32_t box[4] = {(cuuint32_t)b0, (cuuint32_t)b1, (cuuint32_t)b2, (cuuint32_t)b3};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(v.ptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return sdb_set_error(SDB_ERR_CUDA,
+                         "sdb_gemm_tc: cuTensorMapEncodeTiled(%s) failed with %d (dims %d,%d,%d,%d strides %lld,%lld,%lld "
+                         "box %d,%d,%d,%d)",
+                         what, (int)r, v.C, v.W, v.H, v.N, v.strideW, v.strideH, v.strideN, b0, b1, b2, b3);
+  return SDB_OK;
+}
+
+}  // namespace
+
+extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
+  SDB_CHECK_ARG(d != nullptr, "sdb_gemm_tc: null descriptor");
+  SDB_CHECK_ARG(d->mode == SDB_GEMM_FWD || d->mode == SDB_GEMM_WGRAD, "sdb_gemm_tc: bad mode %d", d->mode);
+  SDB_CHECK_ARG(d->num_src >= 1 && d->num_src <= SDB_MAX_SRC, "sdb_gemm_tc: num_src %d out of range", d->num_src);
+  SDB_CHECK_ARG(d->ntaps >= 1 && d->ntaps <= SDB_MAX_TAPS, "sdb_gemm_tc: ntaps %d out of range", d->ntaps);
+  SDB_CHECK_ARG(d->outW > 0 && d->outH > 0 && d->outN > 0, "sdb_gemm_tc: bad pixel space");
+  const int box_pixels = d->bw * d->bh * d->bn;
+  const bool wgrad = d->mode == SDB_GEMM_WGRAD;
+  SDB_CHECK_ARG(d->bw > 0 && d->bh > 0 && d->bn > 0 && box_pixels == (wgrad ? 64 : 128) && d->bw <= 256 &&
+                    d->bh <= 256 && d->bn <= 256,
+                "sdb_gemm_tc: pixel box %dx%dx%d must hold exactly %d pixels", d->bw, d->bh, d->bn, wgrad ? 64 : 128);
+  SDB_CHECK_ARG(d->N > 0 && d->block_n >= 16 && d->block_n <= 256 && d->block_n % 16 == 0,
+                "sdb_gemm_tc: block_n %d must be a multiple of 16 in [16,256]", d->block_n);
+  SDB_CHECK_ARG(d->d != nullptr, "sdb_gemm_tc: null output");
+  for (int t = 0; t < d->ntaps; ++t)
+    SDB_CHECK_ARG(d->tap_src[t] >= 0 && d->tap_src[t] < d->num_src, "sdb_gemm_tc: tap %d names source %d", t,
+                  d->tap_src[t]);
+
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.mode = d->mode;
+  p.ntaps = d->ntaps;
+  for (int t = 0; t < d->ntaps; ++t) {
+    p.tap_src[t] = d->tap_src[t];
+    p.tap_dh[t] = d->tap_dh[t];
+    p.tap_dw[t] = d->tap_dw[t];
+    p.tap_brow[t] = d->tap_brow[t];
+  }
+  p.W = d->outW; p.H = d->outH; p.NI = d->outN;
+  p.bw = d->bw; p.bh = d->bh; p.bn = d->bn;
+  p.tw = sdb::ceil_div(p.W, p.bw); p.th = sdb::ceil_div(p.H, p.bh); p.tn = sdb::ceil_div(p.NI, p.bn);
+  p.N = d->N; p.BN = d->block_n;
+  p.tiles_n = sdb::ceil_div(p.N, p.BN);
+  p.d = d->d; p.ldd = d->ldd;
+  p.bias = d->bias; p.temb = d->temb;
+  p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual); p.ldr = d->ldr;
+
+  int rc;
+  for (int i = 0; i < d->num_src; ++i) {
+    if (wgrad) rc = encode_view(&p.mapA[i], d->a[i], 64, d->bw, d->bh, d->bn, "A (wgrad activations)");
+    else rc = encode_view(&p.mapA[i], d->a[i], 64, d->bw, d->bh, d->bn, "A (activations)");
+    if (rc) return rc;
+  }
+  for (int i = d->num_src; i < SDB_MAX_SRC; ++i) p.mapA[i] = p.mapA[0];
+
+  if (!wgrad) {
+    SDB_CHECK_ARG(d->K > 0, "sdb_gemm_tc: K must be positive");
+    SDB_CHECK_ARG(d->N % 8 == 0 && d->ldd % 8 == 0 && (((uintptr_t)d->d) & 15) == 0,
+                  "sdb_gemm_tc: N (%d) and ldd (%lld) must be multiples of 8 and D 16-byte aligned", d->N, d->ldd);
+    SDB_CHECK_ARG(d->residual == nullptr || (d->ldr % 8 == 0 && (((uintptr_t)d->residual) & 15) == 0),
+                  "sdb_gemm_tc: residual needs ldr %% 8 == 0 and 16-byte alignment");
+    SDB_CHECK_ARG((((uintptr_t)d->bias) & 15) == 0 && (((uintptr_t)d->temb) & 15) == 0,
+                  "sdb_gemm_tc: bias/temb need 16-byte alignment");
+    p.b_mn = d->b_mn_major ? 1 : 0;
+    p.K = d->K;
+    p.kblocks = sdb::ceil_div(p.K, kBlockK);
+    p.tiles_m = p.tw * p.th * p.tn;
+    p.total_tiles = p.tiles_m * p.tiles_n;
+    p.splits = 1;
+    if (p.b_mn) {
+      SDB_CHECK_ARG(d->block_n % 64 == 0 || d->block_n >= d->N, "sdb_gemm_tc: MN-major B needs block_n %% 64 == 0");
+      rc = encode_view(&p.mapB, d->b, 64, 64, 1, 1, "B (weights [K,N])");
+      p.b_stage_bytes = (uint32_t)(((p.BN + 63) / 64) * kBoxBytes);
+    } else {
+      rc = encode_view(&p.mapB, d->b, 64, p.BN, 1, 1, "B (weights [N,K])");
+      p.b_stage_bytes = (uint32_t)p.BN * 128u;
+    }
+    if (rc) return rc;
+  } else {
+    SDB_CHECK_ARG(d->M > 0, "sdb_gemm_tc: WGRAD needs M (rows of dW per tap)");
+    SDB_CHECK_ARG(d->N % 4 == 0 && d->ldd % 4 == 0 && (((uintptr_t)d->d) & 15) == 0,
+                  "sdb_gemm_tc: WGRAD needs N %% 4 == 0, ldd %% 4 == 0 and a 16-byte aligned output");
+    SDB_CHECK_ARG(d->block_n % 64 == 0 || d->block_n >= d->N, "sdb_gemm_tc: WGRAD needs block_n %% 64 == 0");
+    p.b_mn = 1;
+    p.M = d->M;
+    p.tiles_m = sdb::ceil_div(p.M, 128);
+    p.total_pb = p.tw * p.th * p.tn;
+    int splits = d->splits < 1 ? 1 : d->splits;
+    if (splits > p.total_pb) splits = p.total_pb;
+    p.pb_per_split = sdb::ceil_div(p.total_pb, splits);
+    p.splits = sdb::ceil_div(p.total_pb, p.pb_per_split);
+    p.total_tiles = p.ntaps * p.tiles_m * p.tiles_n * p.splits;
+    rc = encode_view(&p.mapB, d->b, 64, d->bw, d->bh, d->bn, "B (wgrad output gradients)");
+    if (rc) return rc;
+    p.b_stage_bytes = (uint32_t)(((p.BN + 63) / 64) * kBoxBytes);
+  }
+  p.b_stage_bytes = (p.b_stage_bytes + 1023u) & ~1023u;
+  p.stage_bytes = kAStageBytes + p.b_stage_bytes;
+  const uint32_t budget = 200 * 1024;
+  int stages = (int)(budget / p.stage_bytes);
+  if (stages > kMaxStages) stages = kMaxStages;
+  if (stages < 2) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_gemm_tc: stage too large");
+  p.stages = stages;
+  const size_t smem_bytes = (size_t)stages * p.stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
+
+  static std::once_flag attr_once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(attr_once, [] {
+    attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  });
+  if (attr_err != cudaSuccess)
+    return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
+
+  const int grid = p.total_tiles < sdb::kNumSMs ? p.total_tiles : sdb::kNumSMs;
+  if (wgrad) gemm_tc_kernel<SDB_GEMM_WGRAD><<<grid, kThreads, smem_bytes, stream>>>(p);
+  else gemm_tc_kernel<SDB_GEMM_FWD><<<grid, kThreads, smem_bytes, stream>>>(p);
+  SDB_CUDA_LAUNCH_CHECK("sdb_gemm_tc");
+  return SDB_OK;
+}
