@@ -1,0 +1,95 @@
+"""ctypes binding of libsdb200.so (include/sdb200.h). There is no CPU fallback: if the library cannot be loaded the
+import of any operator fails loudly, and every call checks its return code and raises with the library's message."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libsdb200.so")
+
+SDB_MAX_TAPS = 9
+SDB_MAX_SRC = 4
+SDB_GEMM_FWD = 0
+SDB_GEMM_WGRAD = 1
+
+
+class SdbError(RuntimeError):
+    pass
+
+
+class View4(C.Structure):
+    _fields_ = [("ptr", C.c_void_p), ("C", C.c_int), ("W", C.c_int), ("H", C.c_int), ("N", C.c_int),
+                ("strideW", C.c_longlong), ("strideH", C.c_longlong), ("strideN", C.c_longlong)]
+
+
+class GemmDesc(C.Structure):
+    _fields_ = [
+        ("mode", C.c_int), ("num_src", C.c_int), ("a", View4 * SDB_MAX_SRC), ("b", View4), ("b_mn_major", C.c_int),
+        ("ntaps", C.c_int), ("tap_src", C.c_int * SDB_MAX_TAPS), ("tap_dh", C.c_int * SDB_MAX_TAPS),
+        ("tap_dw", C.c_int * SDB_MAX_TAPS), ("tap_brow", C.c_int * SDB_MAX_TAPS),
+        ("outW", C.c_int), ("outH", C.c_int), ("outN", C.c_int), ("bw", C.c_int), ("bh", C.c_int), ("bn", C.c_int),
+        ("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("block_n", C.c_int), ("splits", C.c_int),
+        ("d", C.c_void_p), ("ldd", C.c_longlong), ("bias", C.c_void_p), ("temb", C.c_void_p),
+        ("residual", C.c_void_p), ("ldr", C.c_longlong),
+    ]
+
+
+_P = C.c_void_p
+_I = C.c_int
+_LL = C.c_longlong
+_D = C.c_double
+_F = C.c_float
+_SZ = C.c_size_t
+
+# name -> (restype, argtypes). Must list every symbol include/sdb200.h declares (tests/test_abi.py checks it).
+SIGNATURES = {
+    "sdb_last_error_string": (C.c_char_p, []),
+    "sdb_abi_version": (_I, []),
+    "sdb_check_device": (_I, [_I]),
+    "sdb_lion8_update": (_I, [_P, _P, _P, _P, _P, _P, _LL, _I, _D, _D, _D, _D, _I, _P, _D, _I, _P]),
+    "sdb_lion_fp32_update": (_I, [_P, _P, _P, _P, _P, _LL, _D, _D, _D, _D, _I, _P, _D, _I, _P]),
+    "sdb_sumsq_workspace_bytes": (_SZ, []),
+    "sdb_global_norm": (_I, [_P, _LL, _P, _SZ, _P, _I, _P]),
+    "sdb_add_noise": (_I, [_P, _P, _P, _P, _P, _I, _LL, _P]),
+    "sdb_get_velocity": (_I, [_P, _P, _P, _P, _P, _I, _LL, _P]),
+    "sdb_ddpm_step": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _F, _I, _I, _P]),
+    "sdb_mse_workspace_bytes": (_SZ, []),
+    "sdb_mse_fwd_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _SZ, _P]),
+    "sdb_gemm_tc": (_I, [C.POINTER(GemmDesc), _P]),
+    "sdb_gemm_simt": (_I, [C.POINTER(GemmDesc), _P]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libsdb200.so (built in-tree by _build.py). Raises if it is missing — there is no fallback path."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise SdbError(
+                f"{LIB_PATH} not found: build it with `python -m stable_diffusion_training_b200._build` "
+                "(the product path has no CPU or eager fallback)")
+        l = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = l
+    return _lib
+
+
+def check(rc: int, what: str = "") -> None:
+    if rc != 0:
+        msg = lib().sdb_last_error_string().decode("utf-8", "replace")
+        raise SdbError(f"{what} failed ({rc}): {msg}")
+
+
+def stream_ptr() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+def ptr(t) -> int:
+    return 0 if t is None else t.data_ptr()

@@ -1,0 +1,84 @@
+"""GPU parity of the tcgen05 GEMM / implicit-GEMM conv (sdb_gemm_tc) against torch fp32 on the same bf16 inputs.
+
+Tolerance: inputs are exact bf16, accumulation fp32, output rounded to bf16 once -> |err| <= 2^-8 * |ref| + small
+absolute slack for cancellation (stated per test).
+"""
+import pytest
+import torch
+
+from stable_diffusion_training_b200 import ops
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(shape, dev, scale=1.0, seed=0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(torch.bfloat16).to(dev)
+
+
+def _close(out, ref, rtol=1.0 / 128, atol=2e-2):
+    out = out.float()
+    err = (out - ref).abs()
+    tol = atol + rtol * ref.abs()
+    bad = (err > tol).sum().item()
+    assert bad == 0, f"{bad} mismatches, max err {err.max().item()} (ref max {ref.abs().max().item()})"
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 64, 64), (256, 128, 128), (512, 320, 320), (1024, 1280, 640), (384, 96, 48),
+                                   (8192, 640, 5120), (616, 768, 320)])
+@pytest.mark.parametrize("impl", ["tc", "simt"])
+def test_linear_fwd(cuda, M, K, N, impl):
+    if impl == "simt" and M * N * K > 2 ** 28:
+        pytest.skip("simt reference path is slow")
+    x = _rand((M, K), cuda, seed=1)
+    w = _rand((K, N), cuda, 1.0 / K ** 0.5, seed=2)
+    bias = torch.randn(N, device=cuda)
+    res = _rand((M, N), cuda, seed=3)
+    y = ops.linear(x, w, bias=bias, residual=res, impl=impl)
+    torch.cuda.synchronize()
+    ref = x.float() @ w.float() + bias + res.float()
+    _close(y, ref)
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 64, 64), (512, 320, 320), (1024, 640, 1280), (384, 48, 96)])
+def test_linear_dgrad(cuda, M, K, N):
+    # dx[M,K] = dy[M,N] @ w[K,N]^T : weights used as [N' = K rows, K' = N cols], K-major B
+    dy = _rand((M, N), cuda, seed=1)
+    w = _rand((K, N), cuda, 1.0 / N ** 0.5, seed=2)
+    dx = ops.linear_dgrad(dy, w)
+    torch.cuda.synchronize()
+    _close(dx, dy.float() @ w.float().t())
+
+
+@pytest.mark.parametrize("M,K,N", [(128, 64, 64), (512, 320, 320), (4096, 640, 1280), (8192, 96, 48), (616, 768, 320)])
+def test_linear_wgrad(cuda, M, K, N):
+    x = _rand((M, K), cuda, seed=1)
+    dy = _rand((M, N), cuda, seed=2)
+    dw = ops.linear_wgrad(x, dy)
+    torch.cuda.synchronize()
+    ref = x.float().t() @ dy.float()
+    err = (dw - ref).abs().max().item()
+    assert err <= 1e-3 * max(1.0, ref.abs().max().item()), err
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(2, 8, 8, 64, 64), (2, 16, 16, 320, 320), (1, 32, 32, 128, 64),
+                                            (2, 16, 8, 96, 32), (8, 8, 8, 1280, 1280)])
+def test_conv3x3_fwd_dgrad_wgrad(cuda, B, H, W, Cin, Cout):
+    x = _rand((B, H, W, Cin), cuda, seed=1)
+    w = _rand((3, 3, Cin, Cout), cuda, 1.0 / (9 * Cin) ** 0.5, seed=2)
+    bias = torch.randn(Cout, device=cuda)
+    y = ops.conv3x3(x, w, bias=bias)
+    torch.cuda.synchronize()
+    xt = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wt = w.float().permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    ref = torch.nn.functional.conv2d(xt, wt, bias, padding=1)
+    _close(y, ref.permute(0, 2, 3, 1))
+    dy = _rand((B, H, W, Cout), cuda, seed=3)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = ops.conv3x3_dgrad(dy, w)
+    dw = ops.conv3x3_wgrad(x, dy)
+    torch.cuda.synchronize()
+    _close(dx, xt.grad.permute(0, 2, 3, 1), atol=5e-2)
+    ref_dw = wt.grad.permute(2, 3, 1, 0)
+    err = (dw - ref_dw).abs().max().item()
+    assert err <= 2e-3 * max(1.0, ref_dw.abs().max().item()), err
