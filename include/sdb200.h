@@ -95,7 +95,7 @@ typedef struct {
  *                      tap_brow[t] = first K row of tap t.
  *      b_mn_major = 0: B memory is [N rows, K cols] (the same weights used transposed for dgrad);
  *                      tap_brow[t] = first N row of tap t.
- *      epilogue: + bias[n] (fp32, nullable) + temb[img, n] (fp32, nullable, row stride N)
+ *      epilogue: + bias[n] (fp32, nullable) + temb[img, n] (bf16, nullable, row stride ldt)
  *                + residual[pixel, n] (bf16, nullable, row stride ldr); output bf16, row stride ldd.
  * mode SDB_GEMM_WGRAD: dW[tap_brow[t] + m, n] (+)= sum_pixels A_src(tap)[pixel + (dh,dw), m] * B[pixel, n]
  *      A and B are both pixel-major activations (B is passed as `b`, a 4-D view over the same pixel space);
@@ -124,7 +124,8 @@ typedef struct {
   void* d;
   long long ldd;
   const float* bias;
-  const float* temb;
+  const void* temb;
+  long long ldt;
   const void* residual;
   long long ldr;
 } sdb_gemm_desc;
@@ -135,6 +136,60 @@ int sdb_gemm_tc(const sdb_gemm_desc* desc, cudaStream_t stream);
  * conv_in K = 4 per tap, conv_out N = 4) and as the on-device cross-check of sdb_gemm_tc in the tests.
  * Same descriptor, same semantics; no alignment or divisibility constraints. */
 int sdb_gemm_simt(const sdb_gemm_desc* desc, cudaStream_t stream);
+
+/* ---- normalisation / activation (flax.linen GroupNorm, LayerNorm, nn.gelu as used by diffusers-0.21.4
+ * FlaxResnetBlock2D / FlaxTransformer2DModel / FlaxBasicTransformerBlock / FlaxGEGLU [upstream, un-vendored], reached
+ * from training_utils.py:678-684). bf16 "pixels x channels" tensors, fp32 parameters and statistics.
+ * GroupNorm: 32 groups, fast variance, y = act((x-mean)*rstd*gamma+beta), act = SiLU when `silu`.
+ *   stats: fp32 [B][32][2] = (mean, rstd), written by fwd, read by bwd.
+ *   bwd: dx = GN'(dy) (+ dx_add, nullable, same shape: gradient accumulation), dgamma/dbeta fp32 [C] (overwritten). */
+size_t sdb_groupnorm_workspace_bytes(int B, int HW, int C);
+int sdb_groupnorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, int B, int HW, int C,
+                      float eps, int silu, void* workspace, size_t ws_bytes, cudaStream_t stream);
+int sdb_groupnorm_bwd(const void* x, const void* dy, const float* stats, const float* gamma, const float* beta,
+                      const void* dx_add, void* dx, float* dgamma, float* dbeta, int B, int HW, int C, int silu,
+                      void* workspace, size_t ws_bytes, cudaStream_t stream);
+/* LayerNorm over the last axis; stats fp32 [rows][2] = (mean, rstd). */
+int sdb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, long long rows, int C,
+                      float eps, cudaStream_t stream);
+size_t sdb_layernorm_bwd_workspace_bytes(long long rows, int C);
+int sdb_layernorm_bwd(const void* x, const void* dy, const float* stats, const float* gamma, const void* dx_add, void* dx,
+                      float* dgamma, float* dbeta, long long rows, int C, void* workspace, size_t ws_bytes,
+                      cudaStream_t stream);
+/* GEGLU: u [rows, 2H] = [lin | gate] -> out [rows, H] = lin * gelu_tanh(gate); bwd writes du [rows, 2H]. */
+int sdb_geglu_fwd(const void* u, void* out, long long rows, int H, cudaStream_t stream);
+int sdb_geglu_bwd(const void* u, const void* dout, void* du, long long rows, int H, cudaStream_t stream);
+
+/* ---- attention (diffusers-0.21.4 FlaxAttention + jax_memory_efficient_attention [upstream] as patched by
+ * key_chunk_patch.patch:5-6). q/o/dO: [B, Sq, H*d] bf16 with row strides ld*; k/v: [B, Skv, H*d]. lse2: fp32
+ * [B][H][Sq], log2-domain log-sum-exp. kbias2 (nullable): fp32 [Skv] additive per-key bias in the log2 domain —
+ * log2(multiplicity) reproduces the patched reference's clamped-chunk double count. `scale` multiplies
+ * q.k (the reference pre-divides q by sqrt(d)). */
+int sdb_attn_fwd(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv, void* o,
+                 long long ldo, float* lse2, const float* kbias2, int B, int H, int Sq, int Skv, int d, float scale,
+                 cudaStream_t stream);
+size_t sdb_attn_bwd_workspace_bytes(int B, int H, int Sq);
+int sdb_attn_bwd(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv, const void* o,
+                 long long ldo, const void* dO, long long lddo, const float* lse2, const float* kbias2, void* dq,
+                 long long lddq, void* dk, long long lddk, void* dv, long long lddv, int B, int H, int Sq, int Skv, int d,
+                 float scale, void* workspace, size_t ws_bytes, cudaStream_t stream);
+
+/* ---- data movement / small elementwise pieces of the UNet graph (FlaxUpsample2D nearest resize, skip-connection
+ * concatenate, FlaxTimesteps sinusoid, silu(temb), NCHW->NHWC entry transpose [upstream diffusers 0.21.4]) ---- */
+int sdb_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream);
+int sdb_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int HW, cudaStream_t stream);
+int sdb_upsample2x_fwd(const void* x, void* y, int B, int H, int W, int C, cudaStream_t stream); /* H,W: input */
+int sdb_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, cudaStream_t stream);
+int sdb_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, long long rows, int cols, int accumulate,
+                    cudaStream_t stream);
+int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStream_t stream);
+size_t sdb_colsum_workspace_bytes(long long rows, int cols);
+int sdb_colsum_bf16(const void* x, long long ld, long long rows, int cols, float* out, void* workspace, size_t ws_bytes,
+                    cudaStream_t stream); /* bias gradient: out[c] = sum_r x[r,c] */
+int sdb_silu_fwd(const void* x, void* y, long long n, cudaStream_t stream);
+int sdb_silu_bwd(const void* x, const void* dy, void* dx, long long n, cudaStream_t stream);
+int sdb_timestep_embedding(const int* timesteps, void* out, int B, int dim, int flip_sin_to_cos, float freq_shift,
+                           cudaStream_t stream);
 
 #ifdef __cplusplus
 }

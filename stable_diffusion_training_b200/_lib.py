@@ -30,7 +30,7 @@ class GemmDesc(C.Structure):
         ("tap_dw", C.c_int * SDB_MAX_TAPS), ("tap_brow", C.c_int * SDB_MAX_TAPS),
         ("outW", C.c_int), ("outH", C.c_int), ("outN", C.c_int), ("bw", C.c_int), ("bh", C.c_int), ("bn", C.c_int),
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("block_n", C.c_int), ("splits", C.c_int),
-        ("d", C.c_void_p), ("ldd", C.c_longlong), ("bias", C.c_void_p), ("temb", C.c_void_p),
+        ("d", C.c_void_p), ("ldd", C.c_longlong), ("bias", C.c_void_p), ("temb", C.c_void_p), ("ldt", C.c_longlong),
         ("residual", C.c_void_p), ("ldr", C.c_longlong),
     ]
 
@@ -58,6 +58,29 @@ SIGNATURES = {
     "sdb_mse_fwd_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _SZ, _P]),
     "sdb_gemm_tc": (_I, [C.POINTER(GemmDesc), _P]),
     "sdb_gemm_simt": (_I, [C.POINTER(GemmDesc), _P]),
+    "sdb_groupnorm_workspace_bytes": (_SZ, [_I, _I, _I]),
+    "sdb_groupnorm_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _F, _I, _P, _SZ, _P]),
+    "sdb_groupnorm_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _SZ, _P]),
+    "sdb_layernorm_fwd": (_I, [_P, _P, _P, _P, _P, _LL, _I, _F, _P]),
+    "sdb_layernorm_bwd_workspace_bytes": (_SZ, [_LL, _I]),
+    "sdb_layernorm_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _LL, _I, _P, _SZ, _P]),
+    "sdb_geglu_fwd": (_I, [_P, _P, _LL, _I, _P]),
+    "sdb_geglu_bwd": (_I, [_P, _P, _P, _LL, _I, _P]),
+    "sdb_attn_fwd": (_I, [_P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _P, _I, _I, _I, _I, _I, _F, _P]),
+    "sdb_attn_bwd_workspace_bytes": (_SZ, [_I, _I, _I]),
+    "sdb_attn_bwd": (_I, [_P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _P, _P, _LL, _P, _LL, _P, _LL, _I, _I, _I,
+                          _I, _I, _F, _P, _SZ, _P]),
+    "sdb_cast_f32_bf16": (_I, [_P, _P, _LL, _P]),
+    "sdb_nchw_f32_to_nhwc_bf16": (_I, [_P, _P, _I, _I, _I, _P]),
+    "sdb_upsample2x_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P]),
+    "sdb_upsample2x_bwd": (_I, [_P, _P, _I, _I, _I, _I, _P]),
+    "sdb_copy2d_bf16": (_I, [_P, _LL, _P, _LL, _LL, _I, _I, _P]),
+    "sdb_add_bf16": (_I, [_P, _P, _P, _LL, _P]),
+    "sdb_colsum_workspace_bytes": (_SZ, [_LL, _I]),
+    "sdb_colsum_bf16": (_I, [_P, _LL, _LL, _I, _P, _P, _SZ, _P]),
+    "sdb_silu_fwd": (_I, [_P, _P, _LL, _P]),
+    "sdb_silu_bwd": (_I, [_P, _P, _P, _LL, _P]),
+    "sdb_timestep_embedding": (_I, [_P, _P, _I, _I, _I, _F, _P]),
 }
 
 _lib = None

@@ -1,0 +1,685 @@
+// Flash-style attention for sm_100a: online softmax with tcgen05.mma (S = QK^T and O += PV accumulate in TMEM),
+// operands staged by TMA into 128B-swizzled shared memory. Forward + backward.
+//
+// Replaces diffusers-0.21.4 FlaxAttention with use_memory_efficient_attention=True — jax_memory_efficient_attention /
+// _query_chunk_attention [upstream attention_flax.py, un-vendored] as patched by /root/reference/key_chunk_patch.patch:5-6
+// (key_chunk_size = flatten_latent_dim); call site /root/reference/training_utils.py:678-684. The reference's
+// query-chunk scan x key-chunk map is replaced by one pass over 128-key blocks. The patch's side effect (keys in the
+// clamped last chunk are counted twice) is reproduced exactly by an additive per-key bias log2(m_k)
+// (`kbias2`, log2 domain); the same array carries -inf for masked keys.
+//
+// Layout: q/k/v/o/dO are [B, S, H*d] row-major bf16 with independent row strides (heads interleaved in columns), so the
+// projections' outputs are consumed in place: a 4-D tensor map (d, S, H, B) picks one head; columns d..63 of the last
+// 64-wide swizzle atom are zero-filled by TMA, which pads d = 40 / 80 / 160 for the K = 16 UMMA steps.
+//
+// Forward (192 threads): warps 0-3 = softmax (one thread per query row: S row from TMEM with tcgen05.ld, no shuffles),
+// warp 4 = tcgen05.mma issuer + TMEM owner, warp 5 = TMA producer. O stays in TMEM across key blocks and is rescaled
+// lazily (only when the running max grows by > 2^8, FA4-style), P goes through shared memory as the A operand of PV.
+//
+// Backward: one kernel in two modes, no atomics, deterministic.
+//   mode 0: a CTA owns 128 KEY rows and streams query blocks:  S^T = K Q^T, dP^T = V dO^T, P^T = exp2(...),
+//           dS^T = P^T o (dP^T - D) * scale, dV += P^T dO, dK += dS^T Q.
+//   mode 1: the same code with the roles swapped (a CTA owns 128 QUERY rows, streams key blocks): dQ += dS K.
+#include "sdb_common.cuh"
+#include "ptx_sm100.cuh"
+#include "../../include/sdb200.h"
+#include <cmath>
+#include <mutex>
+
+namespace {
+
+constexpr uint32_t kAtom128 = 128 * 128;  // bytes of a [128 rows x 64 bf16] swizzle atom column
+constexpr int kThreads = 192;
+
+__device__ __forceinline__ float u2f(uint32_t v) { return __uint_as_float(v); }
+
+// 16-byte store of 8 bf16 into a K-major SWIZZLE_128B tile: row r, 16B chunk index c (0..7) of the 128B row
+__device__ __forceinline__ void st_swz(uint8_t* atom_base, int r, int c, uint4 v) {
+  *reinterpret_cast<uint4*>(atom_base + r * 128 + ((c ^ (r & 7)) << 4)) = v;
+}
+
+__device__ __forceinline__ void tma_tile(uint8_t* dst, const CUtensorMap* m, uint64_t* bar, int atoms,
+                                         uint32_t atom_bytes, int row0, int h, int b) {
+  for (int a = 0; a < atoms; ++a) ptx::tma_load_4d(dst + a * atom_bytes, m, bar, 64 * a, row0, h, b);
+}
+
+// UMMA descriptors for the two operand flavours used here
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, uint32_t atom_bytes, int kstep) {
+  return ptx::umma_desc_sw128(base + (uint32_t)(kstep >> 2) * atom_bytes + (uint32_t)(kstep & 3) * 32u, 0u, 1024u);
+}
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, uint32_t atom_bytes, int kstep) {
+  return ptx::umma_desc_sw128(base + (uint32_t)kstep * 2048u, atom_bytes, 1024u);
+}
+
+// =============================================== forward ===============================================
+struct FwdParams {
+  CUtensorMap mapQ, mapK, mapV;
+  __nv_bfloat16* o;
+  long long ldo;
+  float* lse2;
+  const float* kbias2;
+  int B, H, Sq, Skv, d, dpad, atoms, stages, nkb;
+  float scale2;
+  uint32_t tmem_cols;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_constant__ FwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  const uint32_t tile_bytes = (uint32_t)p.atoms * kAtom128;
+  uint8_t* sQ = smem;
+  uint8_t* sK = sQ + tile_bytes;
+  uint8_t* sV = sK + (size_t)p.stages * tile_bytes;
+  uint8_t* sP = sV + (size_t)p.stages * tile_bytes;
+  float* sKb = reinterpret_cast<float*>(sP + 2 * kAtom128);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKb + 128);
+  uint64_t* barQ = bars;
+  uint64_t* kv_full = bars + 1;
+  uint64_t* kv_empty = bars + 3;
+  uint64_t* bar_S = bars + 5;
+  uint64_t* bar_P = bars + 6;
+  uint64_t* bar_PV = bars + 7;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
+
+  if (warp == 5 && lane == 0) {
+    ptx::tma_prefetch_desc(&p.mapQ);
+    ptx::tma_prefetch_desc(&p.mapK);
+    ptx::tma_prefetch_desc(&p.mapV);
+    ptx::mbar_init(barQ, 1);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&kv_full[s], 1);
+      ptx::mbar_init(&kv_empty[s], 1);
+    }
+    ptx::mbar_init(bar_S, 1);
+    ptx::mbar_init(bar_P, 128);
+    ptx::mbar_init(bar_PV, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 4) {
+    ptx::tmem_alloc(tmem_ptr_smem, p.tmem_cols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t tS = tmem_base;         // 128 columns
+  const uint32_t tO = tmem_base + 128u;  // dpad columns
+
+  if (warp == 5) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      ptx::mbar_expect_tx(barQ, tile_bytes);
+      tma_tile(sQ, &p.mapQ, barQ, p.atoms, kAtom128, q0, h, b);
+      for (int j = 0; j < p.nkb; ++j) {
+        const int s = j % p.stages, n = j / p.stages;
+        ptx::mbar_wait(&kv_empty[s], (uint32_t)((n & 1) ^ 1));
+        ptx::mbar_expect_tx(&kv_full[s], 2 * tile_bytes);
+        tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &kv_full[s], p.atoms, kAtom128, j * 128, h, b);
+        tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &kv_full[s], p.atoms, kAtom128, j * 128, h, b);
+      }
+    }
+  } else if (warp == 4) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      const uint32_t idescS = ptx::umma_idesc_bf16(128, 0, 0);
+      const uint32_t idescO = ptx::umma_idesc_bf16(p.dpad, 0, 1);
+      const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
+      const int ksteps = p.dpad / 16;
+      auto issue_S = [&](int j) {
+        const int s = j % p.stages, n = j / p.stages;
+        ptx::mbar_wait(&kv_full[s], (uint32_t)(n & 1));
+        ptx::tc_fence_after();
+        const uint32_t aK = ptx::smem_u32(sK + (size_t)s * tile_bytes);
+        for (int k = 0; k < ksteps; ++k)
+          ptx::umma_bf16(tS, desc_kmajor(aQ, kAtom128, k), desc_kmajor(aK, kAtom128, k), idescS, k > 0 ? 1u : 0u);
+        ptx::umma_commit(bar_S);
+      };
+      ptx::mbar_wait(barQ, 0);
+      issue_S(0);
+      for (int j = 0; j < p.nkb; ++j) {
+        const int s = j % p.stages;
+        ptx::mbar_wait(bar_P, (uint32_t)(j & 1));
+        ptx::tc_fence_after();
+        const uint32_t aV = ptx::smem_u32(sV + (size_t)s * tile_bytes);
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+          ptx::umma_bf16(tO, desc_kmajor(aP, kAtom128, k), desc_mnmajor(aV, kAtom128, k), idescO,
+                         (j > 0 || k > 0) ? 1u : 0u);
+        ptx::umma_commit(&kv_empty[s]);
+        ptx::umma_commit(bar_PV);
+        if (j + 1 < p.nkb) issue_S(j + 1);
+      }
+    }
+  } else {
+    // ===================== softmax / epilogue: thread = query row =====================
+    const int row = threadIdx.x;
+    const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+    float m_used = -INFINITY, l = 0.f;
+    for (int j = 0; j < p.nkb; ++j) {
+      ptx::mbar_wait(bar_S, (uint32_t)(j & 1));
+      ptx::tc_fence_after();
+      const bool use_kb = (p.kbias2 != nullptr) || (j * 128 + 128 > p.Skv);
+      if (use_kb) {
+        const int key = j * 128 + row;
+        sKb[row] = (key < p.Skv) ? (p.kbias2 ? p.kbias2[key] : 0.f) : -INFINITY;
+        ptx::named_bar_sync(1, 128);
+      }
+      // pass 1: row max of the scaled, biased scores (log2 domain)
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int cc = 0; cc < 4; ++cc) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tS + lane_base + cc * 32, v);
+        ptx::tmem_ld_wait();
+        if (use_kb) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(u2f(v[i]), p.scale2, sKb[cc * 32 + i]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, u2f(v[i]) * p.scale2);
+        }
+      }
+      if (j == 0) {
+        m_used = mx;
+      } else {
+        ptx::mbar_wait(bar_PV, (uint32_t)((j - 1) & 1));  // O complete, P buffer free
+        ptx::tc_fence_after();
+        const bool need = mx > m_used + 8.0f;
+        if (__any_sync(0xffffffffu, need)) {
+          const float alpha = need ? ptx::ex2_approx(m_used - mx) : 1.0f;
+          if (need) m_used = mx;
+          l *= alpha;
+          for (int c0 = 0; c0 < p.dpad; c0 += 16) {
+            uint32_t v[16];
+            ptx::tmem_ld_32x16(tO + lane_base + c0, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(u2f(v[i]) * alpha);
+            ptx::tmem_st_32x16(tO + lane_base + c0, v);
+          }
+          ptx::tmem_st_wait();
+        }
+      }
+      // pass 2: P = exp2(s - m), bf16, into the swizzled A-operand tile
+#pragma unroll 1
+      for (int cc = 0; cc < 4; ++cc) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32(tS + lane_base + cc * 32, v);
+        ptx::tmem_ld_wait();
+        float pv[32];
+        if (use_kb) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) pv[i] = ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, sKb[cc * 32 + i] - m_used));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) pv[i] = ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, -m_used));
+        }
+        uint8_t* atom = sP + (cc >> 1) * kAtom128;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint4 o;
+          o.x = sdb::pack_bf16x2(pv[c * 8 + 0], pv[c * 8 + 1]);
+          o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
+          o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
+          o.w = sdb::pack_bf16x2(pv[c * 8 + 6], pv[c * 8 + 7]);
+          st_swz(atom, row, (cc & 1) * 4 + c, o);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; ++i) l += pv[i];
+      }
+      ptx::fence_proxy_async_smem();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(bar_P);
+    }
+    // ---- epilogue: O / l -> global, lse ----
+    ptx::mbar_wait(bar_PV, (uint32_t)((p.nkb - 1) & 1));
+    ptx::tc_fence_after();
+    const int q = q0 + row;
+    const bool valid = q < p.Sq;
+    const float inv_l = 1.0f / l;
+    __nv_bfloat16* orow = p.o + ((long long)b * p.Sq + q) * p.ldo + (long long)h * p.d;
+    for (int c0 = 0; c0 < p.dpad; c0 += 16) {
+      uint32_t v[16];
+      ptx::tmem_ld_32x16(tO + lane_base + c0, v);
+      ptx::tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          if (c0 + c * 8 < p.d) {
+            uint4 o;
+            o.x = sdb::pack_bf16x2(u2f(v[c * 8 + 0]) * inv_l, u2f(v[c * 8 + 1]) * inv_l);
+            o.y = sdb::pack_bf16x2(u2f(v[c * 8 + 2]) * inv_l, u2f(v[c * 8 + 3]) * inv_l);
+            o.z = sdb::pack_bf16x2(u2f(v[c * 8 + 4]) * inv_l, u2f(v[c * 8 + 5]) * inv_l);
+            o.w = sdb::pack_bf16x2(u2f(v[c * 8 + 6]) * inv_l, u2f(v[c * 8 + 7]) * inv_l);
+            sdb::st_u4(orow + c0 + c * 8, o);
+          }
+        }
+      }
+    }
+    if (valid) p.lse2[((long long)b * p.H + h) * p.Sq + q] = m_used + log2f(l);
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+// =============================================== backward ===============================================
+struct BwdParams {
+  CUtensorMap mapR1, mapR2, mapC1, mapC2;
+  const float* lse2;
+  const float* dvec;
+  const float* kbias2;
+  __nv_bfloat16* out1;
+  long long ld1;
+  __nv_bfloat16* out2;
+  long long ld2;
+  int mode;  // 0: rows = keys (out1 = dK, out2 = dV); 1: rows = queries (out1 = dQ)
+  int B, H, Sq, Skv, Srow, Scol, d, dpad, atoms, bc, stages, ncb;
+  float scale2, scale;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_constant__ BwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  const uint32_t rtile = (uint32_t)p.atoms * kAtom128;          // row tile: 128 rows
+  const uint32_t catom = (uint32_t)p.bc * 128u;                 // column tile atom: bc rows x 128 B
+  const uint32_t ctile = (uint32_t)p.atoms * catom;
+  const uint32_t ptile = (uint32_t)(p.bc / 64) * kAtom128;      // [128 rows x bc] bf16
+  uint8_t* sR1 = smem;
+  uint8_t* sR2 = sR1 + rtile;
+  uint8_t* sC1 = sR2 + rtile;
+  uint8_t* sC2 = sC1 + (size_t)p.stages * ctile;
+  uint8_t* sPT = sC2 + (size_t)p.stages * ctile;
+  uint8_t* sDS = sPT + ptile;
+  float* sColA = reinterpret_cast<float*>(sDS + ptile);  // [2][128]
+  float* sColB = sColA + 256;                            // [2][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sColB + 256);
+  uint64_t* barR = bars;
+  uint64_t* c_full = bars + 1;
+  uint64_t* c_empty = bars + 3;
+  uint64_t* bar_SdP = bars + 5;
+  uint64_t* bar_PdS = bars + 6;
+  uint64_t* bar_acc = bars + 7;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
+
+  if (warp == 5 && lane == 0) {
+    ptx::tma_prefetch_desc(&p.mapR1);
+    ptx::tma_prefetch_desc(&p.mapR2);
+    ptx::tma_prefetch_desc(&p.mapC1);
+    ptx::tma_prefetch_desc(&p.mapC2);
+    ptx::mbar_init(barR, 1);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&c_full[s], 1);
+      ptx::mbar_init(&c_empty[s], 1);
+    }
+    ptx::mbar_init(bar_SdP, 1);
+    ptx::mbar_init(bar_PdS, 128);
+    ptx::mbar_init(bar_acc, 1);
+    ptx::fence_barrier_init();
+  }
+  if (warp == 4) {
+    ptx::tmem_alloc(tmem_ptr_smem, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  const uint32_t tS = tmem_base;
+  const uint32_t tdP = tmem_base + (uint32_t)p.bc;
+  const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc;
+  const uint32_t tA2 = tA1 + (uint32_t)p.dpad;
+
+  if (warp == 5) {
+    if (lane == 0) {
+      ptx::mbar_expect_tx(barR, 2 * rtile);
+      tma_tile(sR1, &p.mapR1, barR, p.atoms, kAtom128, r0, h, b);
+      tma_tile(sR2, &p.mapR2, barR, p.atoms, kAtom128, r0, h, b);
+      for (int i = 0; i < p.ncb; ++i) {
+        const int s = i % p.stages, n = i / p.stages;
+        ptx::mbar_wait(&c_empty[s], (uint32_t)((n & 1) ^ 1));
+        ptx::mbar_expect_tx(&c_full[s], 2 * ctile);
+        tma_tile(sC1 + (size_t)s * ctile, &p.mapC1, &c_full[s], p.atoms, catom, i * p.bc, h, b);
+        tma_tile(sC2 + (size_t)s * ctile, &p.mapC2, &c_full[s], p.atoms, catom, i * p.bc, h, b);
+      }
+    }
+  } else if (warp == 4) {
+    if (lane == 0) {
+      const uint32_t idescS = ptx::umma_idesc_bf16(p.bc, 0, 0);
+      const uint32_t idescA = ptx::umma_idesc_bf16(p.dpad, 0, 1);
+      const uint32_t aR1 = ptx::smem_u32(sR1), aR2 = ptx::smem_u32(sR2);
+      const uint32_t aPT = ptx::smem_u32(sPT), aDS = ptx::smem_u32(sDS);
+      const int ksteps = p.dpad / 16;
+      ptx::mbar_wait(barR, 0);
+      for (int i = 0; i < p.ncb; ++i) {
+        const int s = i % p.stages, n = i / p.stages;
+        ptx::mbar_wait(&c_full[s], (uint32_t)(n & 1));
+        ptx::tc_fence_after();
+        const uint32_t aC1 = ptx::smem_u32(sC1 + (size_t)s * ctile);
+        const uint32_t aC2 = ptx::smem_u32(sC2 + (size_t)s * ctile);
+        for (int k = 0; k < ksteps; ++k)
+          ptx::umma_bf16(tS, desc_kmajor(aR1, kAtom128, k), desc_kmajor(aC1, catom, k), idescS, k > 0 ? 1u : 0u);
+        for (int k = 0; k < ksteps; ++k)
+          ptx::umma_bf16(tdP, desc_kmajor(aR2, kAtom128, k), desc_kmajor(aC2, catom, k), idescS, k > 0 ? 1u : 0u);
+        ptx::umma_commit(bar_SdP);
+        ptx::mbar_wait(bar_PdS, (uint32_t)(i & 1));
+        ptx::tc_fence_after();
+        const int k2 = p.bc / 16;
+        for (int k = 0; k < k2; ++k)
+          ptx::umma_bf16(tA1, desc_kmajor(aDS, kAtom128, k), desc_mnmajor(aC1, catom, k), idescA,
+                         (i > 0 || k > 0) ? 1u : 0u);
+        if (p.mode == 0) {
+          for (int k = 0; k < k2; ++k)
+            ptx::umma_bf16(tA2, desc_kmajor(aPT, kAtom128, k), desc_mnmajor(aC2, catom, k), idescA,
+                           (i > 0 || k > 0) ? 1u : 0u);
+        }
+        ptx::umma_commit(&c_empty[s]);
+        ptx::umma_commit(bar_acc);
+      }
+    }
+  } else {
+    // ===================== compute threads: thread = row =====================
+    const int row = threadIdx.x;
+    const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+    const int r = r0 + row;
+    const long long bh = (long long)b * p.H + h;
+    float rowA, rowD = 0.f;  // mode 0: rowA = key bias; mode 1: rowA = -lse2[q], rowD = D[q]
+    if (p.mode == 0) {
+      rowA = (r < p.Skv) ? (p.kbias2 ? p.kbias2[r] : 0.f) : -INFINITY;
+    } else {
+      rowA = (r < p.Sq) ? -p.lse2[bh * p.Sq + r] : -INFINITY;
+      rowD = (r < p.Sq) ? p.dvec[bh * p.Sq + r] : 0.f;
+    }
+    for (int i = 0; i < p.ncb; ++i) {
+      float* cA = sColA + (i & 1) * 128;
+      float* cB = sColB + (i & 1) * 128;
+      if (row < p.bc) {
+        const int c = i * p.bc + row;
+        if (p.mode == 0) {
+          cA[row] = (c < p.Sq) ? -p.lse2[bh * p.Sq + c] : -INFINITY;
+          cB[row] = (c < p.Sq) ? p.dvec[bh * p.Sq + c] : 0.f;
+        } else {
+          cA[row] = (c < p.Skv) ? (p.kbias2 ? p.kbias2[c] : 0.f) : -INFINITY;
+          cB[row] = 0.f;
+        }
+      }
+      ptx::named_bar_sync(1, 128);
+      ptx::mbar_wait(bar_SdP, (uint32_t)(i & 1));
+      ptx::tc_fence_after();
+      if (i > 0) ptx::mbar_wait(bar_acc, (uint32_t)((i - 1) & 1));  // P^T / dS^T tiles free again
+#pragma unroll 1
+      for (int cc = 0; cc < p.bc / 32; ++cc) {
+        uint32_t sv[32], dv[32];
+        ptx::tmem_ld_32x32(tS + lane_base + cc * 32, sv);
+        ptx::tmem_ld_32x32(tdP + lane_base + cc * 32, dv);
+        ptx::tmem_ld_wait();
+        float pv[32], ds[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) {
+          const float a = cA[cc * 32 + k] + rowA;  // bias - lse (either order); -inf masks
+          const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, a));
+          const float dd = (p.mode == 0) ? cB[cc * 32 + k] : rowD;
+          pv[k] = pk;
+          ds[k] = pk * (u2f(dv[k]) - dd) * p.scale;
+        }
+        uint8_t* atomP = sPT + (cc >> 1) * kAtom128;
+        uint8_t* atomD = sDS + (cc >> 1) * kAtom128;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint4 o;
+          o.x = sdb::pack_bf16x2(ds[c * 8 + 0], ds[c * 8 + 1]);
+          o.y = sdb::pack_bf16x2(ds[c * 8 + 2], ds[c * 8 + 3]);
+          o.z = sdb::pack_bf16x2(ds[c * 8 + 4], ds[c * 8 + 5]);
+          o.w = sdb::pack_bf16x2(ds[c * 8 + 6], ds[c * 8 + 7]);
+          st_swz(atomD, row, (cc & 1) * 4 + c, o);
+          if (p.mode == 0) {
+            o.x = sdb::pack_bf16x2(pv[c * 8 + 0], pv[c * 8 + 1]);
+            o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
+            o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
+            o.w = sdb::pack_bf16x2(pv[c * 8 + 6], pv[c * 8 + 7]);
+            st_swz(atomP, row, (cc & 1) * 4 + c, o);
+          }
+        }
+      }
+      ptx::fence_proxy_async_smem();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(bar_PdS);
+    }
+    // ---- drain the accumulators ----
+    ptx::mbar_wait(bar_acc, (uint32_t)((p.ncb - 1) & 1));
+    ptx::tc_fence_after();
+    const bool valid = r < p.Srow;
+    for (int which = 0; which < (p.mode == 0 ? 2 : 1); ++which) {
+      const uint32_t tA = which == 0 ? tA1 : tA2;
+      __nv_bfloat16* base = which == 0 ? p.out1 : p.out2;
+      const long long ld = which == 0 ? p.ld1 : p.ld2;
+      __nv_bfloat16* orow = base + ((long long)b * p.Srow + r) * ld + (long long)h * p.d;
+      for (int c0 = 0; c0 < p.dpad; c0 += 16) {
+        uint32_t v[16];
+        ptx::tmem_ld_32x16(tA + lane_base + c0, v);
+        ptx::tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            if (c0 + c * 8 < p.d) {
+              uint4 o;
+              o.x = sdb::pack_bf16x2(u2f(v[c * 8 + 0]), u2f(v[c * 8 + 1]));
+              o.y = sdb::pack_bf16x2(u2f(v[c * 8 + 2]), u2f(v[c * 8 + 3]));
+              o.z = sdb::pack_bf16x2(u2f(v[c * 8 + 4]), u2f(v[c * 8 + 5]));
+              o.w = sdb::pack_bf16x2(u2f(v[c * 8 + 6]), u2f(v[c * 8 + 7]));
+              sdb::st_u4(orow + c0 + c * 8, o);
+            }
+          }
+        }
+      }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 4) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// D[b,h,q] = sum_c dO[b,q,h,c] * O[b,q,h,c]
+__global__ void __launch_bounds__(256)
+attn_dvec_kernel(const __nv_bfloat16* __restrict__ o, long long ldo, const __nv_bfloat16* __restrict__ dO,
+                 long long lddo, float* __restrict__ dvec, int B, int H, int Sq, int d) {
+  const long long total = (long long)B * Sq * H;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const int h = (int)(idx % H);
+    const long long bq = idx / H;
+    const int q = (int)(bq % Sq);
+    const int b = (int)(bq / Sq);
+    const __nv_bfloat16* po = o + bq * ldo + (long long)h * d;
+    const __nv_bfloat16* pd = dO + bq * lddo + (long long)h * d;
+    float acc = 0.f;
+    for (int c = 0; c < d; c += 8) {
+      const uint4 a = sdb::ld_u4(po + c), g = sdb::ld_u4(pd + c);
+      acc = fmaf(sdb::bf16_lo(a.x), sdb::bf16_lo(g.x), acc); acc = fmaf(sdb::bf16_hi(a.x), sdb::bf16_hi(g.x), acc);
+      acc = fmaf(sdb::bf16_lo(a.y), sdb::bf16_lo(g.y), acc); acc = fmaf(sdb::bf16_hi(a.y), sdb::bf16_hi(g.y), acc);
+      acc = fmaf(sdb::bf16_lo(a.z), sdb::bf16_lo(g.z), acc); acc = fmaf(sdb::bf16_hi(a.z), sdb::bf16_hi(g.z), acc);
+      acc = fmaf(sdb::bf16_lo(a.w), sdb::bf16_lo(g.w), acc); acc = fmaf(sdb::bf16_hi(a.w), sdb::bf16_hi(g.w), acc);
+    }
+    dvec[((long long)b * H + h) * Sq + q] = acc;
+  }
+}
+
+// ---------------- host side ----------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn attn_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* sym = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &sym, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(sym);
+  });
+  return fn;
+}
+
+// [B, S, H*d] tensor with row stride ld -> map over (d, S, H, B), box (64, box_rows, 1, 1)
+int encode_heads(CUtensorMap* map, const void* ptr, long long ld, int B, int S, int H, int d, int box_rows,
+                 const char* what) {
+  EncodeTiledFn fn = attn_encode_fn();
+  if (!fn) return sdb_set_error(SDB_ERR_CUDA, "sdb_attn: cuTensorMapEncodeTiled entry point unavailable");
+  if (ptr == nullptr || (((uintptr_t)ptr) & 15) != 0 || ld % 8 != 0 || d % 8 != 0)
+    return sdb_set_error(SDB_ERR_INVALID, "sdb_attn: %s must be 16-byte aligned with ld %% 8 == 0 and d %% 8 == 0", what);
+  cuuint64_t gdim[4] = {(cuuint64_t)d, (cuuint64_t)S, (cuuint64_t)H, (cuuint64_t)B};
+  cuuint64_t gstr[3] = {(cuuint64_t)ld * 2, (cuuint64_t)d * 2, (cuuint64_t)S * (cuuint64_t)ld * 2};
+  cuuint32_t box[4] = {64, (cuuint32_t)box_rows, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS)
+    return sdb_set_error(SDB_ERR_CUDA, "sdb_attn: cuTensorMapEncodeTiled(%s) failed with %d (B %d S %d H %d d %d ld %lld)",
+                         what, (int)r, B, S, H, d, ld);
+  return SDB_OK;
+}
+
+int check_shape(const char* name, int B, int H, int Sq, int Skv, int d) {
+  SDB_CHECK_ARG(B > 0 && H > 0 && Sq > 0 && Skv > 0, "%s: bad shape", name);
+  SDB_CHECK_ARG(d % 8 == 0 && d >= 16 && d <= 192, "%s: head dim %d must be a multiple of 8 in [16,192]", name, d);
+  SDB_CHECK_ARG(H <= 65535 && B <= 65535, "%s: H/B too large for the grid", name);
+  return SDB_OK;
+}
+
+}  // namespace
+
+extern "C" int sdb_attn_fwd(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                            void* o, long long ldo, float* lse2, const float* kbias2, int B, int H, int Sq, int Skv,
+                            int d, float scale, cudaStream_t stream) {
+  int rc = check_shape("sdb_attn_fwd", B, H, Sq, Skv, d);
+  if (rc) return rc;
+  SDB_CHECK_ARG(o != nullptr && lse2 != nullptr && (((uintptr_t)o) & 15) == 0 && ldo % 8 == 0,
+                "sdb_attn_fwd: output must be 16-byte aligned with ldo %% 8 == 0");
+  FwdParams p;
+  memset(&p, 0, sizeof(p));
+  if ((rc = encode_heads(&p.mapQ, q, ldq, B, Sq, H, d, 128, "q"))) return rc;
+  if ((rc = encode_heads(&p.mapK, k, ldk, B, Skv, H, d, 128, "k"))) return rc;
+  if ((rc = encode_heads(&p.mapV, v, ldv, B, Skv, H, d, 128, "v"))) return rc;
+  p.o = reinterpret_cast<__nv_bfloat16*>(o);
+  p.ldo = ldo;
+  p.lse2 = lse2;
+  p.kbias2 = kbias2;
+  p.B = B; p.H = H; p.Sq = Sq; p.Skv = Skv; p.d = d;
+  p.dpad = (d + 15) & ~15;
+  p.atoms = (d + 63) / 64;
+  p.nkb = (Skv + 127) / 128;
+  p.scale2 = scale * 1.4426950408889634f;
+  p.tmem_cols = (128 + p.dpad <= 256) ? 256 : 512;
+  const size_t tile = (size_t)p.atoms * kAtom128;
+  const size_t fixed = tile + 2 * kAtom128 + 128 * sizeof(float) + 128 /*barriers*/ + 1024 /*align*/;
+  p.stages = (fixed + 4 * tile <= 220 * 1024 && p.nkb > 1) ? 2 : 1;
+  const size_t smem_bytes = fixed + (size_t)p.stages * 2 * tile;
+  if (smem_bytes > 227 * 1024) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_fwd: head dim %d needs too much smem", d);
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  });
+  if (attr_err != cudaSuccess)
+    return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
+  dim3 grid((Sq + 127) / 128, H, B);
+  attn_fwd_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
+  SDB_CUDA_LAUNCH_CHECK("sdb_attn_fwd");
+  return SDB_OK;
+}
+
+extern "C" size_t sdb_attn_bwd_workspace_bytes(int B, int H, int Sq) { return (size_t)B * H * Sq * sizeof(float); }
+
+extern "C" int sdb_attn_bwd(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                            const void* o, long long ldo, const void* dO, long long lddo, const float* lse2,
+                            const float* kbias2, void* dq, long long lddq, void* dk, long long lddk, void* dv,
+                            long long lddv, int B, int H, int Sq, int Skv, int d, float scale, void* workspace,
+                            size_t ws_bytes, cudaStream_t stream) {
+  int rc = check_shape("sdb_attn_bwd", B, H, Sq, Skv, d);
+  if (rc) return rc;
+  if (ws_bytes < sdb_attn_bwd_workspace_bytes(B, H, Sq))
+    return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_attn_bwd: workspace %zu < %zu", ws_bytes,
+                         sdb_attn_bwd_workspace_bytes(B, H, Sq));
+  SDB_CHECK_ARG(dq && dk && dv && ((((uintptr_t)dq) | ((uintptr_t)dk) | ((uintptr_t)dv)) & 15) == 0 &&
+                    lddq % 8 == 0 && lddk % 8 == 0 && lddv % 8 == 0 && ldo % 8 == 0 && lddo % 8 == 0,
+                "sdb_attn_bwd: gradient outputs must be 16-byte aligned with row strides %% 8 == 0");
+  float* dvec = reinterpret_cast<float*>(workspace);
+  {
+    const long long total = (long long)B * Sq * H;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    attn_dvec_kernel<<<(int)blocks, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(o), ldo,
+                                                      reinterpret_cast<const __nv_bfloat16*>(dO), lddo, dvec, B, H, Sq, d);
+    SDB_CUDA_LAUNCH_CHECK("sdb_attn_bwd(dvec)");
+  }
+  static std::once_flag once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(once, [] {
+    attr_err = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+  });
+  if (attr_err != cudaSuccess)
+    return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
+
+  for (int mode = 0; mode < 2; ++mode) {
+    BwdParams p;
+    memset(&p, 0, sizeof(p));
+    p.mode = mode;
+    p.B = B; p.H = H; p.Sq = Sq; p.Skv = Skv; p.d = d;
+    p.dpad = (d + 15) & ~15;
+    p.atoms = (d + 63) / 64;
+    p.bc = (p.dpad > 128) ? 64 : 128;
+    p.Srow = mode == 0 ? Skv : Sq;
+    p.Scol = mode == 0 ? Sq : Skv;
+    p.ncb = (p.Scol + p.bc - 1) / p.bc;
+    p.scale = scale;
+    p.scale2 = scale * 1.4426950408889634f;
+    p.lse2 = lse2; p.dvec = dvec; p.kbias2 = kbias2;
+    if (mode == 0) {
+      if ((rc = encode_heads(&p.mapR1, k, ldk, B, Skv, H, d, 128, "k"))) return rc;
+      if ((rc = encode_heads(&p.mapR2, v, ldv, B, Skv, H, d, 128, "v"))) return rc;
+      if ((rc = encode_heads(&p.mapC1, q, ldq, B, Sq, H, d, p.bc, "q"))) return rc;
+      if ((rc = encode_heads(&p.mapC2, dO, lddo, B, Sq, H, d, p.bc, "dO"))) return rc;
+      p.out1 = reinterpret_cast<__nv_bfloat16*>(dk); p.ld1 = lddk;
+      p.out2 = reinterpret_cast<__nv_bfloat16*>(dv); p.ld2 = lddv;
+    } else {
+      if ((rc = encode_heads(&p.mapR1, q, ldq, B, Sq, H, d, 128, "q"))) return rc;
+      if ((rc = encode_heads(&p.mapR2, dO, lddo, B, Sq, H, d, 128, "dO"))) return rc;
+      if ((rc = encode_heads(&p.mapC1, k, ldk, B, Skv, H, d, p.bc, "k"))) return rc;
+      if ((rc = encode_heads(&p.mapC2, v, ldv, B, Skv, H, d, p.bc, "v"))) return rc;
+      p.out1 = reinterpret_cast<__nv_bfloat16*>(dq); p.ld1 = lddq;
+      p.out2 = nullptr; p.ld2 = 0;
+    }
+    const size_t rtile = (size_t)p.atoms * kAtom128;
+    const size_t ctile = (size_t)p.atoms * p.bc * 128;
+    const size_t ptile = (size_t)(p.bc / 64) * kAtom128;
+    const size_t fixed = 2 * rtile + 2 * ptile + 512 * sizeof(float) + 128 + 1024;
+    p.stages = (fixed + 4 * ctile <= 220 * 1024 && p.ncb > 1) ? 2 : 1;
+    const size_t smem_bytes = fixed + (size_t)p.stages * 2 * ctile;
+    if (smem_bytes > 227 * 1024)
+      return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_bwd: head dim %d needs too much smem", d);
+    dim3 grid((p.Srow + 127) / 128, H, B);
+    attn_bwd_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
+    SDB_CUDA_LAUNCH_CHECK("sdb_attn_bwd");
+  }
+  return SDB_OK;
+}

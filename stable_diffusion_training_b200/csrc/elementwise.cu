@@ -1,0 +1,308 @@
+// Data-movement and small elementwise kernels of the UNet graph: layout casts, nearest 2x upsample (+ its adjoint),
+// strided 2-D copies (skip-connection concat / split), gradient accumulation, bias gradients (column sums), SiLU on
+// the time embedding and the sinusoidal timestep embedding.
+//
+// Replaces [upstream diffusers 0.21.4 Flax, un-vendored]: FlaxUpsample2D (jax.image.resize nearest),
+// jnp.concatenate of skip connections in FlaxCrossAttnUpBlock2D / FlaxUpBlock2D, FlaxTimesteps /
+// get_sinusoidal_embeddings (embeddings_flax.py), nn.silu on temb in FlaxResnetBlock2D, and the NCHW->NHWC transpose
+// at the top of FlaxUNet2DConditionModel.__call__ (call site /root/reference/training_utils.py:678-684).
+#include "sdb_common.cuh"
+#include "../../include/sdb200.h"
+
+namespace {
+
+int ew_grid(long long work, int per_sm = 8) {
+  long long blocks = (work + 255) / 256;
+  long long cap = (long long)sdb::kNumSMs * per_sm;
+  return (int)(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
+}
+
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  f[0] = sdb::bf16_lo(v.x); f[1] = sdb::bf16_hi(v.x); f[2] = sdb::bf16_lo(v.y); f[3] = sdb::bf16_hi(v.y);
+  f[4] = sdb::bf16_lo(v.z); f[5] = sdb::bf16_hi(v.z); f[6] = sdb::bf16_lo(v.w); f[7] = sdb::bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 o;
+  o.x = sdb::pack_bf16x2(f[0], f[1]); o.y = sdb::pack_bf16x2(f[2], f[3]);
+  o.z = sdb::pack_bf16x2(f[4], f[5]); o.w = sdb::pack_bf16x2(f[6], f[7]);
+  return o;
+}
+
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  const long long n4 = n / 4;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n4; v += stride) {
+    const float4 a = sdb::ld_f4(src + 4 * v);
+    uint2 o;
+    o.x = sdb::pack_bf16x2(a.x, a.y);
+    o.y = sdb::pack_bf16x2(a.z, a.w);
+    *reinterpret_cast<uint2*>(dst + 4 * v) = o;
+  }
+  for (long long i = n4 * 4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    dst[i] = __float2bfloat16_rn(src[i]);
+}
+
+// src NCHW fp32 [B,C,HW] -> dst NHWC bf16 [B,HW,C] (C tiny: 4)
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B, int C,
+                                    int HW) {
+  const long long total = (long long)B * C * HW;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const long long bp = i / C;
+    const int p = (int)(bp % HW);
+    const int b = (int)(bp / HW);
+    dst[i] = __float2bfloat16_rn(src[((long long)b * C + c) * HW + p]);
+  }
+}
+
+// y[b, 2h+i, 2w+j, :] = x[b, h, w, :]
+__global__ void upsample2x_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int B, int H, int W, int CV) {
+  const long long total = (long long)B * 2 * H * 2 * W * CV;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % CV);
+    long long r = i / CV;
+    const int ow = (int)(r % (2 * W)); r /= 2 * W;
+    const int oh = (int)(r % (2 * H));
+    const int b = (int)(r / (2 * H));
+    y[i] = x[(((long long)b * H + oh / 2) * W + ow / 2) * CV + v];
+  }
+}
+// dx[b,h,w,:] = sum_{i,j} dy[b,2h+i,2w+j,:]
+__global__ void upsample2x_bwd_kernel(const uint4* __restrict__ dy, uint4* __restrict__ dx, int B, int H, int W,
+                                      int CV) {
+  const long long total = (long long)B * H * W * CV;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % CV);
+    long long r = i / CV;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int b = (int)(r / H);
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int di = 0; di < 2; ++di)
+#pragma unroll
+      for (int dj = 0; dj < 2; ++dj) {
+        float f[8];
+        unpack8(dy[(((long long)b * 2 * H + 2 * h + di) * 2 * W + 2 * w + dj) * CV + v], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      }
+    dx[i] = pack8(acc);
+  }
+}
+
+// dst[r, 0:cols] (=|+=) src[r, 0:cols], bf16, row strides in elements (multiples of 8)
+template <bool ACC>
+__global__ void copy2d_kernel(const __nv_bfloat16* __restrict__ src, long long lds, __nv_bfloat16* __restrict__ dst,
+                              long long ldd, long long rows, int cv) {
+  const long long total = rows * cv;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / cv;
+    const int v = (int)(i - r * cv);
+    const uint4 a = sdb::ld_u4(src + r * lds + v * 8);
+    if (!ACC) {
+      sdb::st_u4(dst + r * ldd + v * 8, a);
+    } else {
+      float fa[8], fb[8];
+      unpack8(a, fa);
+      unpack8(sdb::ld_u4(dst + r * ldd + v * 8), fb);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) fb[k] += fa[k];
+      sdb::st_u4(dst + r * ldd + v * 8, pack8(fb));
+    }
+  }
+}
+
+__global__ void add_bf16_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out,
+                                long long nv) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
+    float fa[8], fb[8];
+    unpack8(a[i], fa);
+    unpack8(b[i], fb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) fa[k] += fb[k];
+    out[i] = pack8(fa);
+  }
+}
+
+// column sums of a bf16 [rows, cols] matrix (row stride ld): stage 1 -> part[block][cols]
+constexpr int kColsumRowsPerBlock = 256;
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows, int cols,
+                      float* __restrict__ part) {
+  // thread (ty, tx): tx over 8-wide column vectors (32 per pass), ty over 8 row lanes
+  __shared__ float s[8][256 + 8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const long long r0 = (long long)blockIdx.x * kColsumRowsPerBlock;
+  const long long r1 = min(rows, r0 + kColsumRowsPerBlock);
+  for (int c0 = 0; c0 < cols; c0 += 256) {
+    const int c = c0 + tx * 8;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (c < cols) {
+      for (long long r = r0 + ty; r < r1; r += 8) {
+        float f[8];
+        unpack8(sdb::ld_u4(x + r * ld + c), f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[ty][tx * 8 + k] = acc[k];
+    __syncthreads();
+    const int cc = c0 + threadIdx.x;
+    if (cc < cols) {
+      float t = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) t += s[j][threadIdx.x];
+      part[(size_t)blockIdx.x * cols + cc] = t;
+    }
+    __syncthreads();
+  }
+}
+__global__ void colsum_final_kernel(const float* __restrict__ part, int nblocks, int cols, float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= cols) return;
+  float t = 0.f;
+  for (int j = 0; j < nblocks; ++j) t += part[(size_t)j * cols + c];
+  out[c] = t;
+}
+
+__global__ void silu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float v = __bfloat162float(x[i]);
+    y[i] = __float2bfloat16_rn(v / (1.0f + __expf(-v)));
+  }
+}
+// dx = dy * silu'(x) (+ add)
+__global__ void silu_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                                __nv_bfloat16* __restrict__ dx, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float v = __bfloat162float(x[i]);
+    const float sg = 1.0f / (1.0f + __expf(-v));
+    dx[i] = __float2bfloat16_rn(__bfloat162float(dy[i]) * sg * (1.0f + v * (1.0f - sg)));
+  }
+}
+
+// emb[b, :] = flip ? [cos(t f), sin(t f)] : [sin, cos], f_i = exp(-ln(10000) * i / (half - freq_shift))
+__global__ void timestep_embedding_kernel(const int* __restrict__ t, __nv_bfloat16* __restrict__ out, int B, int dim,
+                                          int flip_sin_to_cos, float freq_shift) {
+  const int half = dim / 2;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= B * half) return;
+  const int b = idx / half, i = idx - b * half;
+  const float f = expf(-logf(10000.0f) * (float)i / ((float)half - freq_shift));
+  const float arg = (float)t[b] * f;
+  const float sv = sinf(arg), cv = cosf(arg);
+  __nv_bfloat16* o = out + (size_t)b * dim;
+  o[i] = __float2bfloat16_rn(flip_sin_to_cos ? cv : sv);
+  o[half + i] = __float2bfloat16_rn(flip_sin_to_cos ? sv : cv);
+}
+
+}  // namespace
+
+extern "C" int sdb_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream) {
+  SDB_CHECK_ARG(n >= 0 && (((uintptr_t)src) & 15) == 0 && (((uintptr_t)dst) & 7) == 0, "sdb_cast_f32_bf16: alignment");
+  if (n == 0) return SDB_OK;
+  cast_f32_bf16_kernel<<<ew_grid(n / 4 + 1), 256, 0, stream>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  SDB_CUDA_LAUNCH_CHECK("sdb_cast_f32_bf16");
+  return SDB_OK;
+}
+
+extern "C" int sdb_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int HW, cudaStream_t stream) {
+  SDB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "sdb_nchw_f32_to_nhwc_bf16: bad shape");
+  nchw_to_nhwc_kernel<<<ew_grid((long long)B * C * HW), 256, 0, stream>>>(src, reinterpret_cast<__nv_bfloat16*>(dst), B,
+                                                                          C, HW);
+  SDB_CUDA_LAUNCH_CHECK("sdb_nchw_f32_to_nhwc_bf16");
+  return SDB_OK;
+}
+
+extern "C" int sdb_upsample2x_fwd(const void* x, void* y, int B, int H, int W, int C, cudaStream_t stream) {
+  SDB_CHECK_ARG(C % 8 == 0, "sdb_upsample2x_fwd: C=%d must be a multiple of 8", C);
+  upsample2x_fwd_kernel<<<ew_grid((long long)B * H * W * 4 * (C / 8)), 256, 0, stream>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(y), B, H, W, C / 8);
+  SDB_CUDA_LAUNCH_CHECK("sdb_upsample2x_fwd");
+  return SDB_OK;
+}
+
+extern "C" int sdb_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, cudaStream_t stream) {
+  SDB_CHECK_ARG(C % 8 == 0, "sdb_upsample2x_bwd: C=%d must be a multiple of 8", C);
+  upsample2x_bwd_kernel<<<ew_grid((long long)B * H * W * (C / 8)), 256, 0, stream>>>(
+      reinterpret_cast<const uint4*>(dy), reinterpret_cast<uint4*>(dx), B, H, W, C / 8);
+  SDB_CUDA_LAUNCH_CHECK("sdb_upsample2x_bwd");
+  return SDB_OK;
+}
+
+extern "C" int sdb_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, long long rows, int cols,
+                               int accumulate, cudaStream_t stream) {
+  SDB_CHECK_ARG(cols % 8 == 0 && lds % 8 == 0 && ldd % 8 == 0, "sdb_copy2d_bf16: cols/strides must be multiples of 8");
+  SDB_CHECK_ARG(((((uintptr_t)src) | ((uintptr_t)dst)) & 15) == 0, "sdb_copy2d_bf16: 16-byte alignment required");
+  if (rows <= 0 || cols <= 0) return SDB_OK;
+  const int grid = ew_grid(rows * (cols / 8));
+  if (accumulate)
+    copy2d_kernel<true><<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(src), lds,
+                                                  reinterpret_cast<__nv_bfloat16*>(dst), ldd, rows, cols / 8);
+  else
+    copy2d_kernel<false><<<grid, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(src), lds,
+                                                   reinterpret_cast<__nv_bfloat16*>(dst), ldd, rows, cols / 8);
+  SDB_CUDA_LAUNCH_CHECK("sdb_copy2d_bf16");
+  return SDB_OK;
+}
+
+extern "C" int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStream_t stream) {
+  SDB_CHECK_ARG(n % 8 == 0, "sdb_add_bf16: n must be a multiple of 8");
+  if (n == 0) return SDB_OK;
+  add_bf16_kernel<<<ew_grid(n / 8), 256, 0, stream>>>(reinterpret_cast<const uint4*>(a),
+                                                      reinterpret_cast<const uint4*>(b), reinterpret_cast<uint4*>(out),
+                                                      n / 8);
+  SDB_CUDA_LAUNCH_CHECK("sdb_add_bf16");
+  return SDB_OK;
+}
+
+extern "C" size_t sdb_colsum_workspace_bytes(long long rows, int cols) {
+  const long long blocks = (rows + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
+  return (size_t)blocks * cols * sizeof(float);
+}
+
+extern "C" int sdb_colsum_bf16(const void* x, long long ld, long long rows, int cols, float* out, void* workspace,
+                               size_t ws_bytes, cudaStream_t stream) {
+  SDB_CHECK_ARG(cols % 8 == 0 && ld % 8 == 0 && rows > 0, "sdb_colsum_bf16: cols/ld must be multiples of 8");
+  if (ws_bytes < sdb_colsum_workspace_bytes(rows, cols))
+    return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_colsum_bf16: workspace too small");
+  const int blocks = (int)((rows + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock);
+  float* part = reinterpret_cast<float*>(workspace);
+  colsum_partial_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld, rows, cols, part);
+  SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(partial)");
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, stream>>>(part, blocks, cols, out);
+  SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(final)");
+  return SDB_OK;
+}
+
+extern "C" int sdb_silu_fwd(const void* x, void* y, long long n, cudaStream_t stream) {
+  if (n <= 0) return SDB_OK;
+  silu_fwd_kernel<<<ew_grid(n), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                  reinterpret_cast<__nv_bfloat16*>(y), n);
+  SDB_CUDA_LAUNCH_CHECK("sdb_silu_fwd");
+  return SDB_OK;
+}
+
+extern "C" int sdb_silu_bwd(const void* x, const void* dy, void* dx, long long n, cudaStream_t stream) {
+  if (n <= 0) return SDB_OK;
+  silu_bwd_kernel<<<ew_grid(n), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x),
+                                                  reinterpret_cast<const __nv_bfloat16*>(dy),
+                                                  reinterpret_cast<__nv_bfloat16*>(dx), n);
+  SDB_CUDA_LAUNCH_CHECK("sdb_silu_bwd");
+  return SDB_OK;
+}
+
+extern "C" int sdb_timestep_embedding(const int* timesteps, void* out, int B, int dim, int flip_sin_to_cos,
+                                      float freq_shift, cudaStream_t stream) {
+  SDB_CHECK_ARG(B > 0 && dim > 0 && dim % 2 == 0, "sdb_timestep_embedding: dim must be even");
+  timestep_embedding_kernel<<<(B * (dim / 2) + 255) / 256, 256, 0, stream>>>(
+      timesteps, reinterpret_cast<__nv_bfloat16*>(out), B, dim, flip_sin_to_cos, freq_shift);
+  SDB_CUDA_LAUNCH_CHECK("sdb_timestep_embedding");
+  return SDB_OK;
+}

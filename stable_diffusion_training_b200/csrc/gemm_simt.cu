@@ -17,7 +17,8 @@ struct SimtParams {
   void* d;
   long long ldd;
   const float* bias;
-  const float* temb;
+  const __nv_bfloat16* temb;
+  long long ldt;
   const __nv_bfloat16* residual;
   long long ldr;
   int pixel_chunks;
@@ -55,7 +56,7 @@ __global__ void __launch_bounds__(256) simt_fwd_kernel(const SimtParams p) {
       }
     }
     if (p.bias) acc += p.bias[n];
-    if (p.temb) acc += p.temb[(long long)img * p.N + n];
+    if (p.temb) acc += __bfloat162float(p.temb[(long long)img * p.ldt + n]);
     if (p.residual) acc += __bfloat162float(p.residual[pix * p.ldr + n]);
     reinterpret_cast<__nv_bfloat16*>(p.d)[pix * p.ldd + n] = __float2bfloat16_rn(acc);
   }
@@ -115,7 +116,8 @@ extern "C" int sdb_gemm_simt(const sdb_gemm_desc* d, cudaStream_t stream) {
   p.W = d->outW; p.H = d->outH; p.NI = d->outN;
   p.M = d->M; p.N = d->N; p.K = d->K;
   p.d = d->d; p.ldd = d->ldd;
-  p.bias = d->bias; p.temb = d->temb;
+  p.bias = d->bias;
+  p.temb = reinterpret_cast<const __nv_bfloat16*>(d->temb); p.ldt = d->ldt;
   p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual); p.ldr = d->ldr;
   if (d->mode == SDB_GEMM_FWD) {
     SDB_CHECK_ARG(d->K > 0, "sdb_gemm_simt: K must be positive");

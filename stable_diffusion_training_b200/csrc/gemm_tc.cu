@@ -45,7 +45,8 @@ struct alignas(64) TcParams {
   void* d;
   long long ldd;
   const float* bias;
-  const float* temb;
+  const __nv_bfloat16* temb;
+  long long ldt;
   const __nv_bfloat16* residual;
   long long ldr;
 };
@@ -241,7 +242,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.d) + grow * p.ldd + ti.n_off;
         const __nv_bfloat16* res = p.residual ? p.residual + grow * p.ldr + ti.n_off : nullptr;
         const float* bias = p.bias ? p.bias + ti.n_off : nullptr;
-        const float* temb = p.temb ? p.temb + (long long)n * p.N + ti.n_off : nullptr;
+        const __nv_bfloat16* temb = p.temb ? p.temb + (long long)n * p.ldt + ti.n_off : nullptr;
         for (int c0 = 0; c0 < ti.nw; c0 += 32) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
@@ -260,10 +261,11 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                   f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
                 }
                 if (temb) {
-                  const float4 b0 = __ldg(reinterpret_cast<const float4*>(temb + c0 + j8));
-                  const float4 b1 = __ldg(reinterpret_cast<const float4*>(temb + c0 + j8 + 4));
-                  f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
-                  f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+                  const uint4 tv = sdb::ld_u4(temb + c0 + j8);
+                  f[0] += sdb::bf16_lo(tv.x); f[1] += sdb::bf16_hi(tv.x);
+                  f[2] += sdb::bf16_lo(tv.y); f[3] += sdb::bf16_hi(tv.y);
+                  f[4] += sdb::bf16_lo(tv.z); f[5] += sdb::bf16_hi(tv.z);
+                  f[6] += sdb::bf16_lo(tv.w); f[7] += sdb::bf16_hi(tv.w);
                 }
                 if (res) {
                   const uint4 rv = sdb::ld_u4(res + c0 + j8);
@@ -400,7 +402,8 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
   p.N = d->N; p.BN = d->block_n;
   p.tiles_n = sdb::ceil_div(p.N, p.BN);
   p.d = d->d; p.ldd = d->ldd;
-  p.bias = d->bias; p.temb = d->temb;
+  p.bias = d->bias;
+  p.temb = reinterpret_cast<const __nv_bfloat16*>(d->temb); p.ldt = d->ldt;
   p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual); p.ldr = d->ldr;
 
   int rc;
@@ -417,8 +420,8 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
                   "sdb_gemm_tc: N (%d) and ldd (%lld) must be multiples of 8 and D 16-byte aligned", d->N, d->ldd);
     SDB_CHECK_ARG(d->residual == nullptr || (d->ldr % 8 == 0 && (((uintptr_t)d->residual) & 15) == 0),
                   "sdb_gemm_tc: residual needs ldr %% 8 == 0 and 16-byte alignment");
-    SDB_CHECK_ARG((((uintptr_t)d->bias) & 15) == 0 && (((uintptr_t)d->temb) & 15) == 0,
-                  "sdb_gemm_tc: bias/temb need 16-byte alignment");
+    SDB_CHECK_ARG((((uintptr_t)d->bias) & 15) == 0 && (((uintptr_t)d->temb) & 15) == 0 && d->ldt % 8 == 0,
+                  "sdb_gemm_tc: bias/temb need 16-byte alignment (ldt %% 8 == 0)");
     p.b_mn = d->b_mn_major ? 1 : 0;
     p.K = d->K;
     p.kblocks = sdb::ceil_div(p.K, kBlockK);

@@ -1,0 +1,596 @@
+// GroupNorm(32)+SiLU, LayerNorm and GEGLU, forward and backward — HBM-bound kernels with 128-bit coalesced access.
+//
+// Replaces flax.linen.GroupNorm / LayerNorm / nn.gelu as used by diffusers-0.21.4 FlaxResnetBlock2D,
+// FlaxTransformer2DModel, FlaxBasicTransformerBlock and FlaxGEGLU [upstream, un-vendored; called from
+// /root/reference/training_utils.py:678-684]. Semantics restated in SURVEY.md B.4/B.5: statistics in fp32 with the
+// fast variance max(0, E[x^2]-E[x]^2), eps 1e-5, affine per channel, SiLU in fp32, tanh-GELU.
+//
+// Layout: activations are "pixels x channels" bf16 (NHWC), one 16-byte vector = 8 channels. A thread owns a fixed set
+// of channel vectors (so gamma/beta and the per-channel accumulators live in registers) and strides over pixel rows.
+#include "sdb_common.cuh"
+#include "../../include/sdb200.h"
+
+namespace {
+
+constexpr int kGroups = 32;
+
+struct GnShape {
+  int C, HW, B, cpg, nv, TC, RL, KC, chunks, rows_per_chunk;
+};
+
+__host__ bool gn_shape(int B, int HW, int C, GnShape* s) {
+  if (C % 8 != 0 || C % kGroups != 0) return false;
+  s->C = C; s->HW = HW; s->B = B; s->cpg = C / kGroups; s->nv = C / 8;
+  int tc = 1;
+  for (int d = 1; d <= s->nv && d <= 256; ++d)
+    if (s->nv % d == 0) tc = d;
+  s->TC = tc;
+  s->KC = s->nv / tc;
+  if (s->KC > 2) return false;
+  s->RL = 256 / tc;
+  if (s->RL > HW) s->RL = HW;
+  // enough blocks for ~2 waves, at least RL rows each
+  int want = (2 * sdb::kNumSMs + B - 1) / B;
+  int max_chunks = (HW + s->RL - 1) / s->RL;
+  s->chunks = want < max_chunks ? want : max_chunks;
+  if (s->chunks < 1) s->chunks = 1;
+  s->rows_per_chunk = (HW + s->chunks - 1) / s->chunks;
+  s->chunks = (HW + s->rows_per_chunk - 1) / s->rows_per_chunk;
+  return true;
+}
+
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  f[0] = sdb::bf16_lo(v.x); f[1] = sdb::bf16_hi(v.x); f[2] = sdb::bf16_lo(v.y); f[3] = sdb::bf16_hi(v.y);
+  f[4] = sdb::bf16_lo(v.z); f[5] = sdb::bf16_hi(v.z); f[6] = sdb::bf16_lo(v.w); f[7] = sdb::bf16_hi(v.w);
+}
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 o;
+  o.x = sdb::pack_bf16x2(f[0], f[1]); o.y = sdb::pack_bf16x2(f[2], f[3]);
+  o.z = sdb::pack_bf16x2(f[4], f[5]); o.w = sdb::pack_bf16x2(f[6], f[7]);
+  return o;
+}
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
+
+// ---------------------------------------------------------------------------------------------------------------
+// GroupNorm pass 1: per (sample, chunk, channel) partial sums.
+//   BWD = false: (sum x, sum x^2)
+//   BWD = true : dz = dy * (SILU ? silu'(z) : 1), z = xhat*gamma+beta; (sum dz, sum dz*xhat)
+template <int KC, bool BWD, bool SILU>
+__global__ void __launch_bounds__(256)
+gn_partial_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                  const float2* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                  float2* __restrict__ part, GnShape s) {
+  extern __shared__ float smem[];
+  float* s_a = smem;                       // [RL][C]
+  float* s_b = smem + (size_t)s.RL * s.C;  // [RL][C]
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int tc = threadIdx.x % s.TC, rl = threadIdx.x / s.TC;
+  const int r0 = chunk * s.rows_per_chunk;
+  const int r1 = min(s.HW, r0 + s.rows_per_chunk);
+  float a0[KC][8], a1[KC][8], gm[KC][8], bt[KC][8], mu[KC][8], rs[KC][8];
+#pragma unroll
+  for (int k = 0; k < KC; ++k)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a0[k][i] = 0.f; a1[k][i] = 0.f;
+      if (BWD) {
+        const int c = (tc + k * s.TC) * 8 + i;
+        const float2 st = stats[b * kGroups + c / s.cpg];
+        mu[k][i] = st.x; rs[k][i] = st.y; gm[k][i] = gamma[c]; bt[k][i] = beta[c];
+      }
+    }
+  const __nv_bfloat16* xb = x + (size_t)b * s.HW * s.C;
+  const __nv_bfloat16* dyb = BWD ? dy + (size_t)b * s.HW * s.C : nullptr;
+  if (rl < s.RL) {
+    for (int r = r0 + rl; r < r1; r += s.RL) {
+#pragma unroll
+      for (int k = 0; k < KC; ++k) {
+        const size_t off = (size_t)r * s.C + (size_t)(tc + k * s.TC) * 8;
+        float xv[8];
+        unpack8(sdb::ld_u4(xb + off), xv);
+        if (!BWD) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { a0[k][i] += xv[i]; a1[k][i] = fmaf(xv[i], xv[i], a1[k][i]); }
+        } else {
+          float dv[8];
+          unpack8(sdb::ld_u4(dyb + off), dv);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = (xv[i] - mu[k][i]) * rs[k][i];
+            float dz = dv[i];
+            if (SILU) {
+              const float z = fmaf(xh, gm[k][i], bt[k][i]);
+              const float sg = sigmoid_f(z);
+              dz *= sg * (1.0f + z * (1.0f - sg));
+            }
+            a0[k][i] += dz; a1[k][i] = fmaf(dz, xh, a1[k][i]);
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KC; ++k)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int c = (tc + k * s.TC) * 8 + i;
+        s_a[rl * s.C + c] = a0[k][i];
+        s_b[rl * s.C + c] = a1[k][i];
+      }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < s.C; c += blockDim.x) {
+    float t0 = 0.f, t1 = 0.f;
+    for (int j = 0; j < s.RL; ++j) { t0 += s_a[j * s.C + c]; t1 += s_b[j * s.C + c]; }
+    part[((size_t)b * s.chunks + chunk) * s.C + c] = make_float2(t0, t1);
+  }
+}
+
+// GroupNorm pass 2 (one block per sample): reduce chunks -> per-channel totals -> per-group scalars.
+//   BWD = false: stats[b][g] = (mean, rstd)
+//   BWD = true : chan_tot[b][c] = (sum dz, sum dz*xhat); grp[b][g] = (mean_g(gamma*dz), mean_g(gamma*dz*xhat))
+template <bool BWD>
+__global__ void __launch_bounds__(256)
+gn_finalize_kernel(const float2* __restrict__ part, const float* __restrict__ gamma, float2* __restrict__ out_grp,
+                   float2* __restrict__ chan_tot, GnShape s, float eps) {
+  extern __shared__ float2 s_chan[];  // [C]
+  const int b = blockIdx.x;
+  for (int c = threadIdx.x; c < s.C; c += blockDim.x) {
+    float t0 = 0.f, t1 = 0.f;
+    for (int j = 0; j < s.chunks; ++j) {
+      const float2 p = part[((size_t)b * s.chunks + j) * s.C + c];
+      t0 += p.x; t1 += p.y;
+    }
+    if (BWD) {
+      chan_tot[(size_t)b * s.C + c] = make_float2(t0, t1);
+      const float g = gamma[c];
+      t0 *= g; t1 *= g;
+    }
+    s_chan[c] = make_float2(t0, t1);
+  }
+  __syncthreads();
+  if (threadIdx.x < kGroups) {
+    float t0 = 0.f, t1 = 0.f;
+    for (int c = threadIdx.x * s.cpg; c < (threadIdx.x + 1) * s.cpg; ++c) { t0 += s_chan[c].x; t1 += s_chan[c].y; }
+    const float inv_n = 1.0f / ((float)s.HW * (float)s.cpg);
+    if (!BWD) {
+      const float mean = t0 * inv_n;
+      const float var = fmaxf(0.0f, t1 * inv_n - mean * mean);
+      out_grp[b * kGroups + threadIdx.x] = make_float2(mean, rsqrtf(var + eps));
+    } else {
+      out_grp[b * kGroups + threadIdx.x] = make_float2(t0 * inv_n, t1 * inv_n);
+    }
+  }
+}
+
+// GroupNorm pass 3: apply.
+//   BWD = false: y = act(xhat*gamma + beta)
+//   BWD = true : dx = rstd * (gamma*dz - A_g - xhat*B_g) (+ dx_add if given: gradient accumulation into a fan-out)
+template <int KC, bool BWD, bool SILU>
+__global__ void __launch_bounds__(256)
+gn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+                const float2* __restrict__ stats, const float2* __restrict__ grp, const float* __restrict__ gamma,
+                const float* __restrict__ beta, const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
+                GnShape s) {
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int tc = threadIdx.x % s.TC, rl = threadIdx.x / s.TC;
+  if (rl >= s.RL) return;
+  const int r0 = chunk * s.rows_per_chunk;
+  const int r1 = min(s.HW, r0 + s.rows_per_chunk);
+  float gm[KC][8], bt[KC][8], mu[KC][8], rs[KC][8], ga[KC][8], gb[KC][8];
+#pragma unroll
+  for (int k = 0; k < KC; ++k)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = (tc + k * s.TC) * 8 + i;
+      const int g = c / s.cpg;
+      const float2 st = stats[b * kGroups + g];
+      mu[k][i] = st.x; rs[k][i] = st.y; gm[k][i] = gamma[c]; bt[k][i] = beta[c];
+      if (BWD) { const float2 gg = grp[b * kGroups + g]; ga[k][i] = gg.x; gb[k][i] = gg.y; }
+    }
+  const size_t base = (size_t)b * s.HW * s.C;
+  for (int r = r0 + rl; r < r1; r += s.RL) {
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const size_t off = base + (size_t)r * s.C + (size_t)(tc + k * s.TC) * 8;
+      float xv[8], o[8];
+      unpack8(sdb::ld_u4(x + off), xv);
+      if (!BWD) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float z = fmaf((xv[i] - mu[k][i]) * rs[k][i], gm[k][i], bt[k][i]);
+          o[i] = SILU ? z * sigmoid_f(z) : z;
+        }
+      } else {
+        float dv[8];
+        unpack8(sdb::ld_u4(dy + off), dv);
+        float av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (add != nullptr) unpack8(sdb::ld_u4(add + off), av);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const float xh = (xv[i] - mu[k][i]) * rs[k][i];
+          float dz = dv[i];
+          if (SILU) {
+            const float z = fmaf(xh, gm[k][i], bt[k][i]);
+            const float sg = sigmoid_f(z);
+            dz *= sg * (1.0f + z * (1.0f - sg));
+          }
+          o[i] = rs[k][i] * (gm[k][i] * dz - ga[k][i] - xh * gb[k][i]) + av[i];
+        }
+      }
+      sdb::st_u4(out + off, pack8(o));
+    }
+  }
+}
+
+// dgamma[c] = sum_b chan_tot[b][c].y ; dbeta[c] = sum_b chan_tot[b][c].x
+__global__ void gn_param_grad_kernel(const float2* __restrict__ chan_tot, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta, int B, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float t0 = 0.f, t1 = 0.f;
+  for (int b = 0; b < B; ++b) { const float2 p = chan_tot[(size_t)b * C + c]; t0 += p.x; t1 += p.y; }
+  dbeta[c] = t0;
+  dgamma[c] = t1;
+}
+
+size_t gn_ws_bytes(const GnShape& s) {
+  // part [B][chunks][C] float2 | chan_tot [B][C] float2 | grp [B][32] float2
+  return sizeof(float2) * ((size_t)s.B * s.chunks * s.C + (size_t)s.B * s.C + (size_t)s.B * kGroups);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// LayerNorm: one warp per row; lane l owns vectors l, l+32, ... (C <= 2048).
+constexpr int kLnMaxVec = 8;  // C <= 8*32*8 = 2048
+constexpr int kLnRowsPerBlock = 8;
+
+template <int NV>  // vectors per lane
+__global__ void __launch_bounds__(256)
+ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+              __nv_bfloat16* __restrict__ y, float2* __restrict__ stats, int rows, int C, float eps) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nv = C / 8;
+  for (int row = blockIdx.x * kLnRowsPerBlock + warp; row < rows; row += gridDim.x * kLnRowsPerBlock) {
+    float xv[NV][8];
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (v < nv) {
+        unpack8(sdb::ld_u4(x + (size_t)row * C + v * 8), xv[k]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s0 += xv[k][i]; s1 = fmaf(xv[k][i], xv[k][i], s1); }
+      }
+    }
+    s0 = sdb::warp_sum(s0);
+    s1 = sdb::warp_sum(s1);
+    const float mean = s0 / (float)C;
+    const float var = fmaxf(0.0f, s1 / (float)C - mean * mean);
+    const float rstd = rsqrtf(var + eps);
+    if (lane == 0 && stats != nullptr) stats[row] = make_float2(mean, rstd);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (v < nv) {
+        float o[8];
+        const float4 g0 = sdb::ld_f4(gamma + v * 8), g1 = sdb::ld_f4(gamma + v * 8 + 4);
+        const float4 b0 = sdb::ld_f4(beta + v * 8), b1 = sdb::ld_f4(beta + v * 8 + 4);
+        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = fmaf((xv[k][i] - mean) * rstd, g[i], bb[i]);
+        sdb::st_u4(y + (size_t)row * C + v * 8, pack8(o));
+      }
+    }
+  }
+}
+
+// dx = rstd*(g*dy - mean(g*dy) - xhat*mean(g*dy*xhat)) (+ add); per-block partial dgamma/dbeta -> part[block][2][C]
+template <int NV>
+__global__ void __launch_bounds__(256)
+ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
+              const float2* __restrict__ stats, const float* __restrict__ gamma, const __nv_bfloat16* __restrict__ add,
+              __nv_bfloat16* __restrict__ dx, float* __restrict__ part, int rows, int C) {
+  extern __shared__ float smem[];  // [8 warps][2][C]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nv = C / 8;
+  float dg[NV][8], db[NV][8], g[NV][8];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int v = lane + 32 * k;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { dg[k][i] = 0.f; db[k][i] = 0.f; g[k][i] = (v < nv) ? gamma[v * 8 + i] : 0.f; }
+  }
+  for (int row = blockIdx.x * kLnRowsPerBlock + warp; row < rows; row += gridDim.x * kLnRowsPerBlock) {
+    const float2 st = stats[row];
+    float xh[NV][8], gd[NV][8];
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (v < nv) {
+        float xv[8], dv[8];
+        unpack8(sdb::ld_u4(x + (size_t)row * C + v * 8), xv);
+        unpack8(sdb::ld_u4(dy + (size_t)row * C + v * 8), dv);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          xh[k][i] = (xv[i] - st.x) * st.y;
+          gd[k][i] = g[k][i] * dv[i];
+          s0 += gd[k][i];
+          s1 = fmaf(gd[k][i], xh[k][i], s1);
+          dg[k][i] = fmaf(dv[i], xh[k][i], dg[k][i]);
+          db[k][i] += dv[i];
+        }
+      }
+    }
+    s0 = sdb::warp_sum(s0) / (float)C;
+    s1 = sdb::warp_sum(s1) / (float)C;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int v = lane + 32 * k;
+      if (v < nv) {
+        float o[8], av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (add != nullptr) unpack8(sdb::ld_u4(add + (size_t)row * C + v * 8), av);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = st.y * (gd[k][i] - s0 - xh[k][i] * s1) + av[i];
+        sdb::st_u4(dx + (size_t)row * C + v * 8, pack8(o));
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int v = lane + 32 * k;
+    if (v < nv) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        smem[(warp * 2 + 0) * C + v * 8 + i] = dg[k][i];
+        smem[(warp * 2 + 1) * C + v * 8 + i] = db[k][i];
+      }
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+    const int which = c / C, cc = c - which * C;
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += smem[(w * 2 + which) * C + cc];
+    part[(size_t)blockIdx.x * 2 * C + c] = t;
+  }
+}
+
+// out[which][c] = sum_blocks part[block][which][c]   (which 0 -> dgamma, 1 -> dbeta)
+__global__ void colsum_finalize_kernel(const float* __restrict__ part, int nblocks, int width, float* __restrict__ out0,
+                                       float* __restrict__ out1, int C) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= width) return;
+  float t = 0.f;
+  for (int j = 0; j < nblocks; ++j) t += part[(size_t)j * width + c];
+  if (c < C) out0[c] = t;
+  else out1[c - C] = t;
+}
+
+int ln_grid(int rows) {
+  int blocks = (rows + kLnRowsPerBlock - 1) / kLnRowsPerBlock;
+  const int cap = sdb::kNumSMs * 4;
+  return blocks < cap ? blocks : cap;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// GEGLU: u [rows, 2*H] = [lin | gate]; out [rows, H] = lin * gelu_tanh(gate)
+__device__ __forceinline__ float gelu_tanh_f(float z) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  const float t = tanhf(k0 * (z + k1 * z * z * z));
+  return 0.5f * z * (1.0f + t);
+}
+__device__ __forceinline__ void gelu_tanh_both(float z, float* val, float* grad) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  const float inner = k0 * (z + k1 * z * z * z);
+  const float t = tanhf(inner);
+  *val = 0.5f * z * (1.0f + t);
+  *grad = 0.5f * (1.0f + t) + 0.5f * z * (1.0f - t * t) * k0 * (1.0f + 3.0f * k1 * z * z);
+}
+
+__global__ void __launch_bounds__(256)
+geglu_fwd_kernel(const __nv_bfloat16* __restrict__ u, __nv_bfloat16* __restrict__ out, long long rows, int H) {
+  const int hv = H / 8;
+  const long long total = rows * hv;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long r = idx / hv;
+    const int v = (int)(idx - r * hv);
+    float lin[8], gate[8], o[8];
+    unpack8(sdb::ld_u4(u + r * 2 * H + v * 8), lin);
+    unpack8(sdb::ld_u4(u + r * 2 * H + H + v * 8), gate);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = lin[i] * gelu_tanh_f(gate[i]);
+    sdb::st_u4(out + r * H + v * 8, pack8(o));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+geglu_bwd_kernel(const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict__ dout,
+                 __nv_bfloat16* __restrict__ du, long long rows, int H) {
+  const int hv = H / 8;
+  const long long total = rows * hv;
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+       idx += (long long)gridDim.x * blockDim.x) {
+    const long long r = idx / hv;
+    const int v = (int)(idx - r * hv);
+    float lin[8], gate[8], d[8], dl[8], dg[8];
+    unpack8(sdb::ld_u4(u + r * 2 * H + v * 8), lin);
+    unpack8(sdb::ld_u4(u + r * 2 * H + H + v * 8), gate);
+    unpack8(sdb::ld_u4(dout + r * H + v * 8), d);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float gv, gg;
+      gelu_tanh_both(gate[i], &gv, &gg);
+      dl[i] = d[i] * gv;
+      dg[i] = d[i] * lin[i] * gg;
+    }
+    sdb::st_u4(du + r * 2 * H + v * 8, pack8(dl));
+    sdb::st_u4(du + r * 2 * H + H + v * 8, pack8(dg));
+  }
+}
+
+int ew_grid(long long work, int per_sm = 8) {
+  long long blocks = (work + 255) / 256;
+  long long cap = (long long)sdb::kNumSMs * per_sm;
+  return (int)(blocks < 1 ? 1 : (blocks < cap ? blocks : cap));
+}
+
+}  // namespace
+
+// ===================================================== C ABI =====================================================
+extern "C" size_t sdb_groupnorm_workspace_bytes(int B, int HW, int C) {
+  GnShape s;
+  if (!gn_shape(B, HW, C, &s)) return 0;
+  return gn_ws_bytes(s);
+}
+
+extern "C" int sdb_groupnorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, int B,
+                                 int HW, int C, float eps, int silu, void* workspace, size_t ws_bytes,
+                                 cudaStream_t stream) {
+  GnShape s;
+  SDB_CHECK_ARG(gn_shape(B, HW, C, &s), "sdb_groupnorm_fwd: unsupported C=%d (need C %% 32 == 0, C %% 8 == 0)", C);
+  if (ws_bytes < gn_ws_bytes(s))
+    return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_groupnorm_fwd: workspace %zu < %zu", ws_bytes, gn_ws_bytes(s));
+  float2* part = reinterpret_cast<float2*>(workspace);
+  const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(y);
+  float2* st = reinterpret_cast<float2*>(stats);
+  const dim3 grid(s.chunks, B);
+  const int threads = s.TC * s.RL;
+  const size_t sm = (size_t)s.RL * s.C * 2 * sizeof(float);
+  if (s.KC == 1) gn_partial_kernel<1, false, false><<<grid, threads, sm, stream>>>(xp, nullptr, nullptr, nullptr, nullptr, part, s);
+  else gn_partial_kernel<2, false, false><<<grid, threads, sm, stream>>>(xp, nullptr, nullptr, nullptr, nullptr, part, s);
+  SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_fwd(partial)");
+  gn_finalize_kernel<false><<<B, 256, s.C * sizeof(float2), stream>>>(part, nullptr, st, nullptr, s, eps);
+  SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_fwd(finalize)");
+#define GN_APPLY(KC_, SILU_) \
+  gn_apply_kernel<KC_, false, SILU_><<<grid, threads, 0, stream>>>(xp, nullptr, st, nullptr, gamma, beta, nullptr, yp, s)
+  if (s.KC == 1) { if (silu) GN_APPLY(1, true); else GN_APPLY(1, false); }
+  else { if (silu) GN_APPLY(2, true); else GN_APPLY(2, false); }
+#undef GN_APPLY
+  SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_fwd(apply)");
+  return SDB_OK;
+}
+
+extern "C" int sdb_groupnorm_bwd(const void* x, const void* dy, const float* stats, const float* gamma,
+                                 const float* beta, const void* dx_add, void* dx, float* dgamma, float* dbeta, int B,
+                                 int HW, int C, int silu, void* workspace, size_t ws_bytes, cudaStream_t stream) {
+  GnShape s;
+  SDB_CHECK_ARG(gn_shape(B, HW, C, &s), "sdb_groupnorm_bwd: unsupported C=%d", C);
+  if (ws_bytes < gn_ws_bytes(s))
+    return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_groupnorm_bwd: workspace %zu < %zu", ws_bytes, gn_ws_bytes(s));
+  float2* part = reinterpret_cast<float2*>(workspace);
+  float2* chan_tot = part + (size_t)s.B * s.chunks * s.C;
+  float2* grp = chan_tot + (size_t)s.B * s.C;
+  const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* dyp = reinterpret_cast<const __nv_bfloat16*>(dy);
+  const __nv_bfloat16* addp = reinterpret_cast<const __nv_bfloat16*>(dx_add);
+  __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx);
+  const float2* st = reinterpret_cast<const float2*>(stats);
+  const dim3 grid(s.chunks, B);
+  const int threads = s.TC * s.RL;
+  const size_t sm = (size_t)s.RL * s.C * 2 * sizeof(float);
+#define GN_PART(KC_, SILU_) \
+  gn_partial_kernel<KC_, true, SILU_><<<grid, threads, sm, stream>>>(xp, dyp, st, gamma, beta, part, s)
+  if (s.KC == 1) { if (silu) GN_PART(1, true); else GN_PART(1, false); }
+  else { if (silu) GN_PART(2, true); else GN_PART(2, false); }
+#undef GN_PART
+  SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(partial)");
+  gn_finalize_kernel<true><<<B, 256, s.C * sizeof(float2), stream>>>(part, gamma, grp, chan_tot, s, 0.f);
+  SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(finalize)");
+  gn_param_grad_kernel<<<(C + 255) / 256, 256, 0, stream>>>(chan_tot, dgamma, dbeta, B, C);
+  SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(param)");
+#define GN_APPLY(KC_, SILU_) \
+  gn_apply_kernel<KC_, true, SILU_><<<grid, threads, 0, stream>>>(xp, dyp, st, grp, gamma, beta, addp, dxp, s)
+  if (s.KC == 1) { if (silu) GN_APPLY(1, true); else GN_APPLY(1, false); }
+  else { if (silu) GN_APPLY(2, true); else GN_APPLY(2, false); }
+#undef GN_APPLY
+  SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(apply)");
+  return SDB_OK;
+}
+
+extern "C" int sdb_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats,
+                                 long long rows, int C, float eps, cudaStream_t stream) {
+  SDB_CHECK_ARG(C % 8 == 0 && C <= kLnMaxVec * 256, "sdb_layernorm_fwd: C=%d must be a multiple of 8 and <= 2048", C);
+  SDB_CHECK_ARG(rows > 0 && rows < (1ll << 31), "sdb_layernorm_fwd: bad rows");
+  const int NV = (C / 8 + 31) / 32;
+  const int grid = ln_grid((int)rows);
+  const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
+  __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(y);
+  float2* st = reinterpret_cast<float2*>(stats);
+#define LN_F(NV_) ln_fwd_kernel<NV_><<<grid, 256, 0, stream>>>(xp, gamma, beta, yp, st, (int)rows, C, eps)
+  switch (NV) {
+    case 1: LN_F(1); break;
+    case 2: LN_F(2); break;
+    case 3: LN_F(3); break;
+    case 4: LN_F(4); break;
+    case 5: LN_F(5); break;
+    case 6: LN_F(6); break;
+    case 7: LN_F(7); break;
+    default: LN_F(8); break;
+  }
+#undef LN_F
+  SDB_CUDA_LAUNCH_CHECK("sdb_layernorm_fwd");
+  return SDB_OK;
+}
+
+extern "C" size_t sdb_layernorm_bwd_workspace_bytes(long long rows, int C) {
+  return (size_t)ln_grid((int)rows) * 2 * C * sizeof(float);
+}
+
+extern "C" int sdb_layernorm_bwd(const void* x, const void* dy, const float* stats, const float* gamma,
+                                 const void* dx_add, void* dx, float* dgamma, float* dbeta, long long rows, int C,
+                                 void* workspace, size_t ws_bytes, cudaStream_t stream) {
+  SDB_CHECK_ARG(C % 8 == 0 && C <= kLnMaxVec * 256, "sdb_layernorm_bwd: C=%d must be a multiple of 8 and <= 2048", C);
+  SDB_CHECK_ARG(rows > 0 && rows < (1ll << 31), "sdb_layernorm_bwd: bad rows");
+  if (ws_bytes < sdb_layernorm_bwd_workspace_bytes(rows, C))
+    return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_layernorm_bwd: workspace too small");
+  const int NV = (C / 8 + 31) / 32;
+  const int grid = ln_grid((int)rows);
+  const size_t sm = (size_t)8 * 2 * C * sizeof(float);
+  float* part = reinterpret_cast<float*>(workspace);
+  const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
+  const __nv_bfloat16* dyp = reinterpret_cast<const __nv_bfloat16*>(dy);
+  const __nv_bfloat16* addp = reinterpret_cast<const __nv_bfloat16*>(dx_add);
+  __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx);
+  const float2* st = reinterpret_cast<const float2*>(stats);
+#define LN_B(NV_)                                                                                                  \
+  do {                                                                                                             \
+    if (sm > 48 * 1024)                                                                                            \
+      cudaFuncSetAttribute(ln_bwd_kernel<NV_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);              \
+    ln_bwd_kernel<NV_><<<grid, 256, sm, stream>>>(xp, dyp, st, gamma, addp, dxp, part, (int)rows, C);              \
+  } while (0)
+  switch (NV) {
+    case 1: LN_B(1); break;
+    case 2: LN_B(2); break;
+    case 3: LN_B(3); break;
+    case 4: LN_B(4); break;
+    case 5: LN_B(5); break;
+    case 6: LN_B(6); break;
+    case 7: LN_B(7); break;
+    default: LN_B(8); break;
+  }
+#undef LN_B
+  SDB_CUDA_LAUNCH_CHECK("sdb_layernorm_bwd");
+  colsum_finalize_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(part, grid, 2 * C, dgamma, dbeta, C);
+  SDB_CUDA_LAUNCH_CHECK("sdb_layernorm_bwd(finalize)");
+  return SDB_OK;
+}
+
+extern "C" int sdb_geglu_fwd(const void* u, void* out, long long rows, int H, cudaStream_t stream) {
+  SDB_CHECK_ARG(H % 8 == 0 && rows > 0, "sdb_geglu_fwd: H=%d must be a multiple of 8", H);
+  geglu_fwd_kernel<<<ew_grid(rows * (H / 8)), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(u),
+                                                                reinterpret_cast<__nv_bfloat16*>(out), rows, H);
+  SDB_CUDA_LAUNCH_CHECK("sdb_geglu_fwd");
+  return SDB_OK;
+}
+
+extern "C" int sdb_geglu_bwd(const void* u, const void* dout, void* du, long long rows, int H, cudaStream_t stream) {
+  SDB_CHECK_ARG(H % 8 == 0 && rows > 0, "sdb_geglu_bwd: H=%d must be a multiple of 8", H);
+  geglu_bwd_kernel<<<ew_grid(rows * (H / 8)), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(u),
+                                                                reinterpret_cast<const __nv_bfloat16*>(dout),
+                                                                reinterpret_cast<__nv_bfloat16*>(du), rows, H);
+  SDB_CUDA_LAUNCH_CHECK("sdb_geglu_bwd");
+  return SDB_OK;
+}

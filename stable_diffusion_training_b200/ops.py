@@ -98,7 +98,9 @@ def gemm_fwd(a_views, taps, b: torch.Tensor, b_mn: bool, out: torch.Tensor, pix,
     d.d = out2.data_ptr()
     d.ldd = out2.stride(0)
     d.bias = _lib.ptr(bias)
-    d.temb = _lib.ptr(temb)
+    if temb is not None:
+        d.temb = temb.data_ptr()
+        d.ldt = temb.stride(0)
     if residual is not None:
         r2 = residual.view(-1, residual.shape[-1])
         d.residual = r2.data_ptr()
@@ -207,4 +209,182 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, *, out=None, impl="tc") -> 
         out = torch.empty((3, 3, Cin, Cout), device=x.device, dtype=torch.float32)
     gemm_wgrad([_view_nhwc(x)], _conv_taps(Cin, False), _view_nhwc(dy), out.view(9 * Cin, Cout), (W, H, B), Cin, Cout,
                impl=impl)
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# normalisation / activation / attention / data movement
+_WS = {}
+
+
+def workspace(device, nbytes: int = 64 << 20) -> torch.Tensor:
+    """One stream-ordered scratch buffer per device (partials of reductions; every op finishes with it in-stream)."""
+    key = (device.type, device.index)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 64 << 20), dtype=torch.uint8, device=device)
+        _WS[key] = ws
+    return ws
+
+
+def _L():
+    return _lib.lib()
+
+
+def groupnorm_fwd(x, gamma, beta, *, silu: bool, eps: float = 1e-5, out=None):
+    """x [B, HW, C] (or NHWC) bf16 -> (y, stats[B,32,2])."""
+    B, C = x.shape[0], x.shape[-1]
+    HW = x.numel() // (B * C)
+    y = torch.empty_like(x) if out is None else out
+    stats = torch.empty((B, 32, 2), device=x.device, dtype=torch.float32)
+    ws = workspace(x.device)
+    _lib.check(_L().sdb_groupnorm_fwd(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), y.data_ptr(), stats.data_ptr(),
+                                      B, HW, C, eps, int(silu), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
+               "sdb_groupnorm_fwd")
+    return y, stats
+
+
+def groupnorm_bwd(x, dy, stats, gamma, beta, dgamma, dbeta, *, silu: bool, dx_add=None, out=None):
+    B, C = x.shape[0], x.shape[-1]
+    HW = x.numel() // (B * C)
+    dx = torch.empty_like(x) if out is None else out
+    ws = workspace(x.device)
+    _lib.check(_L().sdb_groupnorm_bwd(x.data_ptr(), dy.data_ptr(), stats.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+                                      _lib.ptr(dx_add), dx.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), B, HW, C,
+                                      int(silu), ws.data_ptr(), ws.numel(), _lib.stream_ptr()), "sdb_groupnorm_bwd")
+    return dx
+
+
+def layernorm_fwd(x, gamma, beta, *, eps: float = 1e-5):
+    C = x.shape[-1]
+    rows = x.numel() // C
+    y = torch.empty_like(x)
+    stats = torch.empty((rows, 2), device=x.device, dtype=torch.float32)
+    _lib.check(_L().sdb_layernorm_fwd(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), y.data_ptr(), stats.data_ptr(),
+                                      rows, C, eps, _lib.stream_ptr()), "sdb_layernorm_fwd")
+    return y, stats
+
+
+def layernorm_bwd(x, dy, stats, gamma, dgamma, dbeta, *, dx_add=None, out=None):
+    C = x.shape[-1]
+    rows = x.numel() // C
+    dx = torch.empty_like(x) if out is None else out
+    ws = workspace(x.device)
+    _lib.check(_L().sdb_layernorm_bwd(x.data_ptr(), dy.data_ptr(), stats.data_ptr(), gamma.data_ptr(),
+                                      _lib.ptr(dx_add), dx.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), rows, C,
+                                      ws.data_ptr(), ws.numel(), _lib.stream_ptr()), "sdb_layernorm_bwd")
+    return dx
+
+
+def geglu_fwd(u):
+    H = u.shape[-1] // 2
+    rows = u.numel() // (2 * H)
+    out = torch.empty(u.shape[:-1] + (H,), device=u.device, dtype=BF16)
+    _lib.check(_L().sdb_geglu_fwd(u.data_ptr(), out.data_ptr(), rows, H, _lib.stream_ptr()), "sdb_geglu_fwd")
+    return out
+
+
+def geglu_bwd(u, dout):
+    H = u.shape[-1] // 2
+    rows = u.numel() // (2 * H)
+    du = torch.empty_like(u)
+    _lib.check(_L().sdb_geglu_bwd(u.data_ptr(), dout.data_ptr(), du.data_ptr(), rows, H, _lib.stream_ptr()),
+               "sdb_geglu_bwd")
+    return du
+
+
+def attention_fwd(q, k, v, heads: int, *, kbias2=None, out=None):
+    """q [B,Sq,C], k/v [B,Skv,C] bf16 (last dim contiguous, arbitrary row stride) -> (o [B,Sq,C], lse2 [B,H,Sq])."""
+    B, Sq, Cc = q.shape
+    Skv = k.shape[1]
+    d = Cc // heads
+    o = torch.empty((B, Sq, Cc), device=q.device, dtype=BF16) if out is None else out
+    lse2 = torch.empty((B, heads, Sq), device=q.device, dtype=torch.float32)
+    _lib.check(_L().sdb_attn_fwd(q.data_ptr(), q.stride(1), k.data_ptr(), k.stride(1), v.data_ptr(), v.stride(1),
+                                 o.data_ptr(), o.stride(1), lse2.data_ptr(), _lib.ptr(kbias2), B, heads, Sq, Skv, d,
+                                 1.0 / d ** 0.5, _lib.stream_ptr()), "sdb_attn_fwd")
+    return o, lse2
+
+
+def attention_bwd(q, k, v, o, dO, lse2, heads: int, *, kbias2=None, dq=None, dk=None, dv=None):
+    B, Sq, Cc = q.shape
+    Skv = k.shape[1]
+    d = Cc // heads
+    dq = torch.empty((B, Sq, Cc), device=q.device, dtype=BF16) if dq is None else dq
+    dk = torch.empty((B, Skv, Cc), device=q.device, dtype=BF16) if dk is None else dk
+    dv = torch.empty((B, Skv, Cc), device=q.device, dtype=BF16) if dv is None else dv
+    ws = workspace(q.device)
+    _lib.check(_L().sdb_attn_bwd(q.data_ptr(), q.stride(1), k.data_ptr(), k.stride(1), v.data_ptr(), v.stride(1),
+                                 o.data_ptr(), o.stride(1), dO.data_ptr(), dO.stride(1), lse2.data_ptr(),
+                                 _lib.ptr(kbias2), dq.data_ptr(), dq.stride(1), dk.data_ptr(), dk.stride(1),
+                                 dv.data_ptr(), dv.stride(1), B, heads, Sq, Skv, d, 1.0 / d ** 0.5, ws.data_ptr(),
+                                 ws.numel(), _lib.stream_ptr()), "sdb_attn_bwd")
+    return dq, dk, dv
+
+
+def cast_bf16(src: torch.Tensor, out=None) -> torch.Tensor:
+    out = torch.empty(src.shape, device=src.device, dtype=BF16) if out is None else out
+    _lib.check(_L().sdb_cast_f32_bf16(src.data_ptr(), out.data_ptr(), src.numel(), _lib.stream_ptr()), "sdb_cast")
+    return out
+
+
+def nchw_to_nhwc_bf16(src: torch.Tensor) -> torch.Tensor:
+    B, Cc, H, W = src.shape
+    out = torch.empty((B, H, W, Cc), device=src.device, dtype=BF16)
+    _lib.check(_L().sdb_nchw_f32_to_nhwc_bf16(src.data_ptr(), out.data_ptr(), B, Cc, H * W, _lib.stream_ptr()), "nhwc")
+    return out
+
+
+def upsample2x_fwd(x):
+    B, H, W, Cc = x.shape
+    y = torch.empty((B, 2 * H, 2 * W, Cc), device=x.device, dtype=BF16)
+    _lib.check(_L().sdb_upsample2x_fwd(x.data_ptr(), y.data_ptr(), B, H, W, Cc, _lib.stream_ptr()), "upsample_fwd")
+    return y
+
+
+def upsample2x_bwd(dy):
+    B, H2, W2, Cc = dy.shape
+    dx = torch.empty((B, H2 // 2, W2 // 2, Cc), device=dy.device, dtype=BF16)
+    _lib.check(_L().sdb_upsample2x_bwd(dy.data_ptr(), dx.data_ptr(), B, H2 // 2, W2 // 2, Cc, _lib.stream_ptr()),
+               "upsample_bwd")
+    return dx
+
+
+def copy2d(src2d, dst2d, accumulate: bool = False):
+    """dst[r, :cols] (=|+=) src[r, :cols]; both 2-D bf16 views with contiguous last dim."""
+    rows, cols = src2d.shape
+    _lib.check(_L().sdb_copy2d_bf16(src2d.data_ptr(), src2d.stride(0), dst2d.data_ptr(), dst2d.stride(0), rows, cols,
+                                    int(accumulate), _lib.stream_ptr()), "sdb_copy2d_bf16")
+
+
+def add_(a, b):
+    """a += b (bf16, same shape, contiguous)."""
+    _lib.check(_L().sdb_add_bf16(a.data_ptr(), b.data_ptr(), a.data_ptr(), a.numel(), _lib.stream_ptr()), "sdb_add")
+    return a
+
+
+def colsum(x2d, out):
+    rows, cols = x2d.shape
+    ws = workspace(x2d.device)
+    _lib.check(_L().sdb_colsum_bf16(x2d.data_ptr(), x2d.stride(0), rows, cols, out.data_ptr(), ws.data_ptr(),
+                                    ws.numel(), _lib.stream_ptr()), "sdb_colsum_bf16")
+    return out
+
+
+def silu_fwd(x):
+    y = torch.empty_like(x)
+    _lib.check(_L().sdb_silu_fwd(x.data_ptr(), y.data_ptr(), x.numel(), _lib.stream_ptr()), "sdb_silu_fwd")
+    return y
+
+
+def silu_bwd(x, dy):
+    dx = torch.empty_like(x)
+    _lib.check(_L().sdb_silu_bwd(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), x.numel(), _lib.stream_ptr()), "silu_bwd")
+    return dx
+
+
+def timestep_embedding(t, dim: int, flip_sin_to_cos: bool = True, freq_shift: float = 0.0):
+    out = torch.empty((t.shape[0], dim), device=t.device, dtype=BF16)
+    _lib.check(_L().sdb_timestep_embedding(t.data_ptr(), out.data_ptr(), t.shape[0], dim, int(flip_sin_to_cos),
+                                           freq_shift, _lib.stream_ptr()), "sdb_timestep_embedding")
     return out
