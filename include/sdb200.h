@@ -123,6 +123,9 @@ typedef struct {
   int splits;           /* WGRAD only */
   void* d;
   long long ldd;
+  long long d_strideW, d_strideH, d_strideN; /* FWD only: element strides of the output pixel grid; all 0 = dense
+                                                (ldd, ldd*outW, ldd*outW*outH). Lets a tile write a strided sub-grid
+                                                (stride-2 transposed convolution by output parity). */
   const float* bias;
   const void* temb;
   long long ldt;
@@ -161,7 +164,8 @@ int sdb_geglu_fwd(const void* u, void* out, long long rows, int H, cudaStream_t 
 int sdb_geglu_bwd(const void* u, const void* dout, void* du, long long rows, int H, cudaStream_t stream);
 
 /* ---- attention (diffusers-0.21.4 FlaxAttention + jax_memory_efficient_attention [upstream] as patched by
- * key_chunk_patch.patch:5-6). q/o/dO: [B, Sq, H*d] bf16 with row strides ld*; k/v: [B, Skv, H*d]. lse2: fp32
+ * key_chunk_patch.patch:5-6). q/o/dO: [B, Sq, H*d] bf16 with row strides ld* (batch stride = S * ld: the buffers are
+ * [B*S, ld] matrices, so column slices of fused projections work in place); k/v: [B, Skv, H*d]. lse2: fp32
  * [B][H][Sq], log2-domain log-sum-exp. kbias2 (nullable): fp32 [Skv] additive per-key bias in the log2 domain —
  * log2(multiplicity) reproduces the patched reference's clamped-chunk double count. `scale` multiplies
  * q.k (the reference pre-divides q by sqrt(d)). */
@@ -184,8 +188,10 @@ int sdb_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, lo
                     cudaStream_t stream);
 int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStream_t stream);
 size_t sdb_colsum_workspace_bytes(long long rows, int cols);
-int sdb_colsum_bf16(const void* x, long long ld, long long rows, int cols, float* out, void* workspace, size_t ws_bytes,
-                    cudaStream_t stream); /* bias gradient: out[c] = sum_r x[r,c] */
+int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long rows_per_seg, int cols, float* out_total,
+                    void* out_seg_bf16, void* workspace, size_t ws_bytes, cudaStream_t stream);
+/* column sums of a bf16 [nseg*rows_per_seg, cols] matrix: out_total[c] (fp32, nullable) = bias gradient;
+ * out_seg[s][c] (bf16, nullable) = per-image sums = gradient of the broadcast time-embedding add. */
 int sdb_silu_fwd(const void* x, void* y, long long n, cudaStream_t stream);
 int sdb_silu_bwd(const void* x, const void* dy, void* dx, long long n, cudaStream_t stream);
 int sdb_timestep_embedding(const int* timesteps, void* out, int B, int dim, int flip_sin_to_cos, float freq_shift,

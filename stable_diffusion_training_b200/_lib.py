@@ -30,7 +30,8 @@ class GemmDesc(C.Structure):
         ("tap_dw", C.c_int * SDB_MAX_TAPS), ("tap_brow", C.c_int * SDB_MAX_TAPS),
         ("outW", C.c_int), ("outH", C.c_int), ("outN", C.c_int), ("bw", C.c_int), ("bh", C.c_int), ("bn", C.c_int),
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("block_n", C.c_int), ("splits", C.c_int),
-        ("d", C.c_void_p), ("ldd", C.c_longlong), ("bias", C.c_void_p), ("temb", C.c_void_p), ("ldt", C.c_longlong),
+        ("d", C.c_void_p), ("ldd", C.c_longlong), ("d_strideW", C.c_longlong), ("d_strideH", C.c_longlong),
+        ("d_strideN", C.c_longlong), ("bias", C.c_void_p), ("temb", C.c_void_p), ("ldt", C.c_longlong),
         ("residual", C.c_void_p), ("ldr", C.c_longlong),
     ]
 
@@ -77,7 +78,7 @@ SIGNATURES = {
     "sdb_copy2d_bf16": (_I, [_P, _LL, _P, _LL, _LL, _I, _I, _P]),
     "sdb_add_bf16": (_I, [_P, _P, _P, _LL, _P]),
     "sdb_colsum_workspace_bytes": (_SZ, [_LL, _I]),
-    "sdb_colsum_bf16": (_I, [_P, _LL, _LL, _I, _P, _P, _SZ, _P]),
+    "sdb_colsum_bf16": (_I, [_P, _LL, _I, _LL, _I, _P, _P, _P, _SZ, _P]),
     "sdb_silu_fwd": (_I, [_P, _P, _LL, _P]),
     "sdb_silu_bwd": (_I, [_P, _P, _P, _LL, _P]),
     "sdb_timestep_embedding": (_I, [_P, _P, _I, _I, _I, _F, _P]),

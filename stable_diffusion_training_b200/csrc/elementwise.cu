@@ -129,16 +129,18 @@ __global__ void add_bf16_kernel(const uint4* __restrict__ a, const uint4* __rest
   }
 }
 
-// column sums of a bf16 [rows, cols] matrix (row stride ld): stage 1 -> part[block][cols]
+// column sums of a bf16 [nseg * rows_per_seg, cols] matrix (row stride ld), per segment and in total:
+// stage 1 -> part[seg][block][cols]; stage 2 -> out_total[c] (fp32) and/or out_seg[seg][c] (bf16).
 constexpr int kColsumRowsPerBlock = 256;
 __global__ void __launch_bounds__(256)
-colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows, int cols,
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows_per_seg, int bps, int cols,
                       float* __restrict__ part) {
   // thread (ty, tx): tx over 8-wide column vectors (32 per pass), ty over 8 row lanes
   __shared__ float s[8][256 + 8];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const long long r0 = (long long)blockIdx.x * kColsumRowsPerBlock;
-  const long long r1 = min(rows, r0 + kColsumRowsPerBlock);
+  const int seg = blockIdx.x / bps, blk = blockIdx.x - seg * bps;
+  const long long r0 = seg * rows_per_seg + (long long)blk * kColsumRowsPerBlock;
+  const long long r1 = min((seg + 1) * rows_per_seg, r0 + kColsumRowsPerBlock);
   for (int c0 = 0; c0 < cols; c0 += 256) {
     const int c = c0 + tx * 8;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -163,12 +165,18 @@ colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long lo
     __syncthreads();
   }
 }
-__global__ void colsum_final_kernel(const float* __restrict__ part, int nblocks, int cols, float* __restrict__ out) {
+__global__ void colsum_final_kernel(const float* __restrict__ part, int nseg, int bps, int cols,
+                                    float* __restrict__ out_total, __nv_bfloat16* __restrict__ out_seg) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= cols) return;
-  float t = 0.f;
-  for (int j = 0; j < nblocks; ++j) t += part[(size_t)j * cols + c];
-  out[c] = t;
+  float tot = 0.f;
+  for (int sgm = 0; sgm < nseg; ++sgm) {
+    float t = 0.f;
+    for (int j = 0; j < bps; ++j) t += part[((size_t)sgm * bps + j) * cols + c];
+    if (out_seg != nullptr) out_seg[(size_t)sgm * cols + c] = __float2bfloat16_rn(t);
+    tot += t;
+  }
+  if (out_total != nullptr) out_total[c] = tot;
 }
 
 __global__ void silu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
@@ -263,20 +271,24 @@ extern "C" int sdb_add_bf16(const void* a, const void* b, void* out, long long n
 }
 
 extern "C" size_t sdb_colsum_workspace_bytes(long long rows, int cols) {
+  // upper bound for any segmentation of `rows` rows (each segment rounds its block count up)
   const long long blocks = (rows + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
-  return (size_t)blocks * cols * sizeof(float);
+  return (size_t)(blocks + 4096) * cols * sizeof(float);
 }
 
-extern "C" int sdb_colsum_bf16(const void* x, long long ld, long long rows, int cols, float* out, void* workspace,
-                               size_t ws_bytes, cudaStream_t stream) {
-  SDB_CHECK_ARG(cols % 8 == 0 && ld % 8 == 0 && rows > 0, "sdb_colsum_bf16: cols/ld must be multiples of 8");
-  if (ws_bytes < sdb_colsum_workspace_bytes(rows, cols))
-    return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_colsum_bf16: workspace too small");
-  const int blocks = (int)((rows + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock);
+extern "C" int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long rows_per_seg, int cols, float* out_total,
+                               void* out_seg_bf16, void* workspace, size_t ws_bytes, cudaStream_t stream) {
+  SDB_CHECK_ARG(cols % 8 == 0 && ld % 8 == 0 && rows_per_seg > 0 && nseg > 0 && nseg <= 4096,
+                "sdb_colsum_bf16: cols/ld must be multiples of 8, 1 <= nseg <= 4096");
+  const int bps = (int)((rows_per_seg + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock);
+  const size_t need = (size_t)nseg * bps * cols * sizeof(float);
+  if (ws_bytes < need) return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_colsum_bf16: workspace %zu < %zu", ws_bytes, need);
   float* part = reinterpret_cast<float*>(workspace);
-  colsum_partial_kernel<<<blocks, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld, rows, cols, part);
+  colsum_partial_kernel<<<nseg * bps, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld, rows_per_seg, bps,
+                                                        cols, part);
   SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(partial)");
-  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, stream>>>(part, blocks, cols, out);
+  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, stream>>>(part, nseg, bps, cols, out_total,
+                                                              reinterpret_cast<__nv_bfloat16*>(out_seg_bf16));
   SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(final)");
   return SDB_OK;
 }

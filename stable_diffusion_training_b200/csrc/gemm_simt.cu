@@ -15,7 +15,7 @@ struct SimtParams {
   int tap_src[SDB_MAX_TAPS], tap_dh[SDB_MAX_TAPS], tap_dw[SDB_MAX_TAPS], tap_brow[SDB_MAX_TAPS];
   int W, H, NI, M, N, K;
   void* d;
-  long long ldd;
+  long long ldd, dsW, dsH, dsN;
   const float* bias;
   const __nv_bfloat16* temb;
   long long ldt;
@@ -58,7 +58,8 @@ __global__ void __launch_bounds__(256) simt_fwd_kernel(const SimtParams p) {
     if (p.bias) acc += p.bias[n];
     if (p.temb) acc += __bfloat162float(p.temb[(long long)img * p.ldt + n]);
     if (p.residual) acc += __bfloat162float(p.residual[pix * p.ldr + n]);
-    reinterpret_cast<__nv_bfloat16*>(p.d)[pix * p.ldd + n] = __float2bfloat16_rn(acc);
+    reinterpret_cast<__nv_bfloat16*>(p.d)[(long long)img * p.dsN + (long long)h * p.dsH + (long long)w * p.dsW + n] =
+        __float2bfloat16_rn(acc);
   }
 }
 
@@ -116,6 +117,11 @@ extern "C" int sdb_gemm_simt(const sdb_gemm_desc* d, cudaStream_t stream) {
   p.W = d->outW; p.H = d->outH; p.NI = d->outN;
   p.M = d->M; p.N = d->N; p.K = d->K;
   p.d = d->d; p.ldd = d->ldd;
+  if (d->d_strideW || d->d_strideH || d->d_strideN) {
+    p.dsW = d->d_strideW; p.dsH = d->d_strideH; p.dsN = d->d_strideN;
+  } else {
+    p.dsW = d->ldd; p.dsH = d->ldd * d->outW; p.dsN = d->ldd * d->outW * d->outH;
+  }
   p.bias = d->bias;
   p.temb = reinterpret_cast<const __nv_bfloat16*>(d->temb); p.ldt = d->ldt;
   p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual); p.ldr = d->ldr;

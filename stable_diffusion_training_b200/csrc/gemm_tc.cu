@@ -43,7 +43,7 @@ struct alignas(64) TcParams {
   int stages;
   uint32_t b_stage_bytes, stage_bytes;
   void* d;
-  long long ldd;
+  long long ldd, dsW, dsH, dsN;
   const float* bias;
   const __nv_bfloat16* temb;
   long long ldt;
@@ -239,7 +239,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const int w = ti.w0 + wi, h = ti.h0 + hi, n = ti.n0 + ni;
         const bool valid = (w < p.W) && (h < p.H) && (n < p.NI);
         const long long grow = ((long long)n * p.H + h) * p.W + w;
-        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.d) + grow * p.ldd + ti.n_off;
+        __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.d) + (long long)n * p.dsN + (long long)h * p.dsH +
+                             (long long)w * p.dsW + ti.n_off;
         const __nv_bfloat16* res = p.residual ? p.residual + grow * p.ldr + ti.n_off : nullptr;
         const float* bias = p.bias ? p.bias + ti.n_off : nullptr;
         const __nv_bfloat16* temb = p.temb ? p.temb + (long long)n * p.ldt + ti.n_off : nullptr;
@@ -402,6 +403,11 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
   p.N = d->N; p.BN = d->block_n;
   p.tiles_n = sdb::ceil_div(p.N, p.BN);
   p.d = d->d; p.ldd = d->ldd;
+  if (d->d_strideW || d->d_strideH || d->d_strideN) {
+    p.dsW = d->d_strideW; p.dsH = d->d_strideH; p.dsN = d->d_strideN;
+  } else {
+    p.dsW = d->ldd; p.dsH = d->ldd * d->outW; p.dsN = d->ldd * d->outW * d->outH;
+  }
   p.bias = d->bias;
   p.temb = reinterpret_cast<const __nv_bfloat16*>(d->temb); p.ldt = d->ldt;
   p.residual = reinterpret_cast<const __nv_bfloat16*>(d->residual); p.ldr = d->ldr;
@@ -416,6 +422,7 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
 
   if (!wgrad) {
     SDB_CHECK_ARG(d->K > 0, "sdb_gemm_tc: K must be positive");
+    SDB_CHECK_ARG(p.dsW % 8 == 0 && p.dsH % 8 == 0 && p.dsN % 8 == 0, "sdb_gemm_tc: output strides must be multiples of 8");
     SDB_CHECK_ARG(d->N % 8 == 0 && d->ldd % 8 == 0 && (((uintptr_t)d->d) & 15) == 0,
                   "sdb_gemm_tc: N (%d) and ldd (%lld) must be multiples of 8 and D 16-byte aligned", d->N, d->ldd);
     SDB_CHECK_ARG(d->residual == nullptr || (d->ldr % 8 == 0 && (((uintptr_t)d->residual) & 15) == 0),

@@ -77,7 +77,7 @@ def _set_taps(desc: GemmDesc, taps) -> None:
 
 
 def gemm_fwd(a_views, taps, b: torch.Tensor, b_mn: bool, out: torch.Tensor, pix, K: int, N: int, *, bias=None,
-             temb=None, residual=None, impl="tc") -> None:
+             temb=None, residual=None, impl="tc", d_offset: int = 0, d_strides=None) -> None:
     """out[pixel, n] = sum_taps A_src[pixel + shift, :K] @ Bop[tap] (+ bias + temb[img] + residual)."""
     W, H, NI = pix
     d = GemmDesc()
@@ -95,8 +95,10 @@ def gemm_fwd(a_views, taps, b: torch.Tensor, b_mn: bool, out: torch.Tensor, pix,
     d.block_n = _pick_block_n(N, b_mn, m_tiles)
     d.splits = 1
     out2 = out.view(-1, out.shape[-1])
-    d.d = out2.data_ptr()
+    d.d = out2.data_ptr() + d_offset * out2.element_size()
     d.ldd = out2.stride(0)
+    if d_strides is not None:
+        d.d_strideW, d.d_strideH, d.d_strideN = d_strides
     d.bias = _lib.ptr(bias)
     if temb is not None:
         d.temb = temb.data_ptr()
@@ -209,6 +211,60 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, *, out=None, impl="tc") -> 
         out = torch.empty((3, 3, Cin, Cout), device=x.device, dtype=torch.float32)
     gemm_wgrad([_view_nhwc(x)], _conv_taps(Cin, False), _view_nhwc(dy), out.view(9 * Cin, Cout), (W, H, B), Cin, Cout,
                impl=impl)
+    return out
+
+
+# ---- 3x3 stride-2 convolution (FlaxDownsample2D): the input is read through four parity sub-grids -----------------
+def _parity_views(x: torch.Tensor):
+    """x NHWC [B,H,W,C] (H, W even) -> 4 views x[:, ph::2, pw::2, :], index ph*2+pw."""
+    B, H, W, Cc = x.shape
+    es = x.element_size()
+    return [View4(x.data_ptr() + (ph * x.stride(1) + pw * x.stride(2)) * es, Cc, W // 2, H // 2, B, 2 * x.stride(2),
+                  2 * x.stride(1), x.stride(0)) for ph in (0, 1) for pw in (0, 1)]
+
+
+def _s2_taps(cin: int):
+    # output (ho, wo) reads input (2ho + kh - 1, 2wo + kw - 1): kh=0 -> parity 1 shifted by -1, kh=1 -> parity 0,
+    # kh=2 -> parity 1 (the -1 row of output 0 is the zero padding: TMA out-of-bounds fill)
+    par = {0: (1, -1), 1: (0, 0), 2: (1, 0)}
+    return [(par[kh][0] * 2 + par[kw][0], par[kh][1], par[kw][1], (kh * 3 + kw) * cin)
+            for kh in range(3) for kw in range(3)]
+
+
+def conv3x3_s2(x, w, *, bias=None, out=None, impl="tc"):
+    B, H, W, Cin = x.shape
+    Cout = w.shape[3]
+    if out is None:
+        out = torch.empty((B, H // 2, W // 2, Cout), device=x.device, dtype=BF16)
+    gemm_fwd(_parity_views(x), _s2_taps(Cin), w.view(9 * Cin, Cout), True, out, (W // 2, H // 2, B), Cin, Cout,
+             bias=bias, impl=impl)
+    return out
+
+
+def conv3x3_s2_wgrad(x, dy, *, out=None, impl="tc"):
+    B, H, W, Cin = x.shape
+    Cout = dy.shape[3]
+    if out is None:
+        out = torch.empty((3, 3, Cin, Cout), device=x.device, dtype=torch.float32)
+    gemm_wgrad(_parity_views(x), _s2_taps(Cin), _view_nhwc(dy), out.view(9 * Cin, Cout), (W // 2, H // 2, B), Cin,
+               Cout, impl=impl)
+    return out
+
+
+def conv3x3_s2_dgrad(dy, w, *, out=None, impl="tc"):
+    """dx[2a+ph, 2c+pw] = sum over the taps of matching parity of dy[a+dh, c+dw] @ w[kh,kw]^T — one launch per output
+    parity class, each writing its strided sub-grid of dx (exact FLOPs, no zero-insertion)."""
+    B, Ho, Wo, Cout = dy.shape
+    Cin = w.shape[2]
+    H, W = 2 * Ho, 2 * Wo
+    if out is None:
+        out = torch.empty((B, H, W, Cin), device=dy.device, dtype=BF16)
+    sel = {0: [(1, 0)], 1: [(0, 1), (2, 0)]}  # parity -> [(k, shift)]
+    for ph in (0, 1):
+        for pw in (0, 1):
+            taps = [(0, dh, dw, (kh * 3 + kw) * Cin) for kh, dh in sel[ph] for kw, dw in sel[pw]]
+            gemm_fwd([_view_nhwc(dy)], taps, w.view(9 * Cin, Cout), False, out, (Wo, Ho, B), Cout, Cin, impl=impl,
+                     d_offset=(ph * W + pw) * Cin, d_strides=(2 * Cin, 2 * W * Cin, H * W * Cin))
     return out
 
 
@@ -363,11 +419,13 @@ def add_(a, b):
     return a
 
 
-def colsum(x2d, out):
+def colsum(x2d, out=None, *, nseg: int = 1, out_seg=None):
+    """out[c] = sum_r x[r, c] (fp32, bias gradient); out_seg[s, c] (bf16) = the same per segment of rows/nseg rows."""
     rows, cols = x2d.shape
     ws = workspace(x2d.device)
-    _lib.check(_L().sdb_colsum_bf16(x2d.data_ptr(), x2d.stride(0), rows, cols, out.data_ptr(), ws.data_ptr(),
-                                    ws.numel(), _lib.stream_ptr()), "sdb_colsum_bf16")
+    _lib.check(_L().sdb_colsum_bf16(x2d.data_ptr(), x2d.stride(0), nseg, rows // nseg, cols, _lib.ptr(out),
+                                    _lib.ptr(out_seg), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
+               "sdb_colsum_bf16")
     return out
 
 

@@ -82,3 +82,47 @@ def test_conv3x3_fwd_dgrad_wgrad(cuda, B, H, W, Cin, Cout):
     ref_dw = wt.grad.permute(2, 3, 1, 0)
     err = (dw - ref_dw).abs().max().item()
     assert err <= 2e-3 * max(1.0, ref_dw.abs().max().item()), err
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(2, 16, 16, 64, 64), (2, 32, 32, 320, 320), (1, 8, 8, 128, 128)])
+def test_conv3x3_stride2(cuda, B, H, W, Cin, Cout):
+    x = _rand((B, H, W, Cin), cuda, seed=1)
+    w = _rand((3, 3, Cin, Cout), cuda, 1.0 / (9 * Cin) ** 0.5, seed=2)
+    bias = torch.randn(Cout, device=cuda)
+    y = ops.conv3x3_s2(x, w, bias=bias)
+    torch.cuda.synchronize()
+    xt = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wt = w.float().permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    ref = torch.nn.functional.conv2d(xt, wt, bias, stride=2, padding=1)
+    _close(y, ref.permute(0, 2, 3, 1))
+    dy = _rand((B, H // 2, W // 2, Cout), cuda, seed=3)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = ops.conv3x3_s2_dgrad(dy, w)
+    dw = ops.conv3x3_s2_wgrad(x, dy)
+    torch.cuda.synchronize()
+    _close(dx, xt.grad.permute(0, 2, 3, 1), atol=5e-2)
+    ref_dw = wt.grad.permute(2, 3, 1, 0)
+    err = (dw - ref_dw).abs().max().item()
+    assert err <= 2e-3 * max(1.0, ref_dw.abs().max().item()), err
+
+
+@pytest.mark.parametrize("Cin,Cout", [(4, 320), (320, 4), (4, 32)])
+def test_conv3x3_simt_small_channels(cuda, Cin, Cout):
+    """conv_in / conv_out shapes (4 channels) run on the CUDA-core kernel."""
+    B, H, W = 2, 16, 16
+    x = _rand((B, H, W, Cin), cuda, seed=1)
+    w = _rand((3, 3, Cin, Cout), cuda, 1.0 / (9 * Cin) ** 0.5, seed=2)
+    bias = torch.randn(Cout, device=cuda)
+    y = ops.conv3x3(x, w, bias=bias, impl="simt")
+    xt = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wt = w.float().permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    ref = torch.nn.functional.conv2d(xt, wt, bias, padding=1)
+    _close(y, ref.permute(0, 2, 3, 1))
+    dy = _rand((B, H, W, Cout), cuda, seed=3)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = ops.conv3x3_dgrad(dy, w, impl="simt")
+    dw = ops.conv3x3_wgrad(x, dy, impl="simt")
+    torch.cuda.synchronize()
+    _close(dx, xt.grad.permute(0, 2, 3, 1), atol=5e-2)
+    ref_dw = wt.grad.permute(2, 3, 1, 0)
+    assert (dw - ref_dw).abs().max().item() <= 2e-3 * max(1.0, ref_dw.abs().max().item())

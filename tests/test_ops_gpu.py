@@ -104,8 +104,14 @@ def _attn_ref(q, k, v, heads, kbias2):
 def test_attention_fwd_bwd(cuda, B, heads, Sq, Skv, d, bias):
     C = heads * d
     # q/k/v as column slices of a fused buffer -> exercises row strides
-    qkv = _rand((B, max(Sq, Skv), 3 * C), cuda, 1.0, 1)
-    q, k, v = qkv[:, :Sq, :C], qkv[:, :Skv, C:2 * C], qkv[:, :Skv, 2 * C:]
+    # (batch stride must be S * row stride: the kernels take [B*S, ld] buffers)
+    if Sq == Skv:
+        qkv = _rand((B, Sq, 3 * C), cuda, 1.0, 1)
+        q, k, v = qkv[:, :, :C], qkv[:, :, C:2 * C], qkv[:, :, 2 * C:]
+    else:
+        q = _rand((B, Sq, C), cuda, 1.0, 1)
+        kv = _rand((B, Skv, 2 * C), cuda, 1.0, 3)
+        k, v = kv[:, :, :C], kv[:, :, C:]
     dO = _rand((B, Sq, C), cuda, 1.0, 2)
     kb = None
     if bias:
@@ -144,6 +150,10 @@ def test_data_movement(cuda):
     out = torch.empty(320, device=cuda)
     ops.colsum(big, out)
     assert torch.allclose(out, big.float().sum(0), rtol=1e-4, atol=1e-2)
+    seg = torch.empty((5, 320), device=cuda, dtype=torch.bfloat16)
+    ops.colsum(big, out, nseg=5, out_seg=seg)
+    assert torch.allclose(out, big.float().sum(0), rtol=1e-4, atol=1e-2)
+    _close(seg, big.float().view(5, 1000, 320).sum(1), what="segmented colsum")
     t = torch.tensor([0, 1, 500, 999], dtype=torch.int32, device=cuda)
     emb = ops.timestep_embedding(t, 320)
     f = torch.exp(-math.log(10000.0) * torch.arange(160, device=cuda, dtype=torch.float32) / 160)
