@@ -55,6 +55,11 @@ size_t sdb_sumsq_workspace_bytes(void);
 int sdb_global_norm(const float* x, long long n, void* workspace, size_t ws_bytes, float* gnorm_out, int accumulate,
                     cudaStream_t stream);
 
+/* Per-leaf pieces of the optax chain for the generic pytree API (optax.clip_by_global_norm, optax.apply_updates). */
+int sdb_clip_by_global_norm_f32(const float* g, float* out, long long n, const float* gnorm_dev, double max_norm,
+                                cudaStream_t stream);
+int sdb_add_f32(const float* a, const float* b, float* out, long long n, cudaStream_t stream);
+
 /* ---- schedulers (schedulers/scheduling_utils_flax.py:316-343; scheduling_ddpm_flax.py:196-297) ---- */
 int sdb_add_noise(const float* original_samples, const float* noise, const int* timesteps, const float* alphas_cumprod,
                   float* noisy, int batch, long long per_sample, cudaStream_t stream);

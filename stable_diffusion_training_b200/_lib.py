@@ -52,6 +52,8 @@ SIGNATURES = {
     "sdb_lion_fp32_update": (_I, [_P, _P, _P, _P, _P, _LL, _D, _D, _D, _D, _I, _P, _D, _I, _P]),
     "sdb_sumsq_workspace_bytes": (_SZ, []),
     "sdb_global_norm": (_I, [_P, _LL, _P, _SZ, _P, _I, _P]),
+    "sdb_clip_by_global_norm_f32": (_I, [_P, _P, _LL, _P, _D, _P]),
+    "sdb_add_f32": (_I, [_P, _P, _P, _LL, _P]),
     "sdb_add_noise": (_I, [_P, _P, _P, _P, _P, _I, _LL, _P]),
     "sdb_get_velocity": (_I, [_P, _P, _P, _P, _P, _I, _LL, _P]),
     "sdb_ddpm_step": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _F, _I, _I, _P]),

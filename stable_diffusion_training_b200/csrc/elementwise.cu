@@ -179,6 +179,23 @@ __global__ void colsum_final_kernel(const float* __restrict__ part, int nseg, in
   if (out_total != nullptr) out_total[c] = tot;
 }
 
+// any (small) column count, no alignment requirement: one block per column
+__global__ void __launch_bounds__(256)
+colsum_narrow_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows, float* __restrict__ out) {
+  const int c = blockIdx.x;
+  float acc = 0.f;
+  for (long long r = threadIdx.x; r < rows; r += 256) acc += __bfloat162float(x[r * ld + c]);
+  acc = sdb::warp_sum(acc);
+  __shared__ float s[8];
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += s[i];
+    out[c] = t;
+  }
+}
+
 __global__ void silu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float v = __bfloat162float(x[i]);
@@ -278,6 +295,11 @@ extern "C" size_t sdb_colsum_workspace_bytes(long long rows, int cols) {
 
 extern "C" int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long rows_per_seg, int cols, float* out_total,
                                void* out_seg_bf16, void* workspace, size_t ws_bytes, cudaStream_t stream) {
+  if ((cols % 8 != 0 || ld % 8 != 0) && nseg == 1 && out_seg_bf16 == nullptr && cols <= 64 && out_total != nullptr) {
+    colsum_narrow_kernel<<<cols, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld, rows_per_seg, out_total);
+    SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(narrow)");
+    return SDB_OK;
+  }
   SDB_CHECK_ARG(cols % 8 == 0 && ld % 8 == 0 && rows_per_seg > 0 && nseg > 0 && nseg <= 4096,
                 "sdb_colsum_bf16: cols/ld must be multiples of 8, 1 <= nseg <= 4096");
   const int bps = (int)((rows_per_seg + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock);

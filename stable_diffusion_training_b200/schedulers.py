@@ -1,0 +1,249 @@
+"""DDPM scheduler behind the reference's surface (/root/reference/schedulers/scheduling_ddpm_flax.py:36-300,
+scheduling_utils_flax.py:188-343): FlaxDDPMScheduler with create_state / add_noise / get_velocity / step /
+set_timesteps / scale_model_input / __len__, the immutable CommonSchedulerState / DDPMSchedulerState dataclasses and
+FlaxDDPMSchedulerOutput. Same argument names, defaults and exceptions.
+
+State creation (1000-element schedules) is init-time host arithmetic in fp32 NumPy in the reference's op order; the
+per-sample arithmetic (add_noise, get_velocity, step) runs in libsdb200.so on CUDA tensors.
+"""
+from __future__ import annotations
+
+import dataclasses
+import math
+from dataclasses import dataclass
+from types import SimpleNamespace
+from typing import Optional, Tuple, Union
+
+import numpy as np
+import torch
+
+from . import _lib
+
+_F = np.float32
+
+
+def broadcast_to_shape_from_left(x: torch.Tensor, shape) -> torch.Tensor:
+    assert len(shape) >= x.dim()
+    return x.reshape(tuple(x.shape) + (1,) * (len(shape) - x.dim())).expand(*shape)
+
+
+def betas_for_alpha_bar(num_diffusion_timesteps: int, max_beta=0.999) -> np.ndarray:
+    def alpha_bar(time_step):
+        return math.cos((time_step + 0.008) / 1.008 * math.pi / 2) ** 2
+
+    betas = []
+    for i in range(num_diffusion_timesteps):
+        t1 = i / num_diffusion_timesteps
+        t2 = (i + 1) / num_diffusion_timesteps
+        betas.append(min(1 - alpha_bar(t2) / alpha_bar(t1), max_beta))
+    return np.array(betas, dtype=_F)
+
+
+def _linspace(start, stop, num) -> np.ndarray:
+    # jnp.linspace in fp32: start*(1-s) + stop*s, s = iota(num-1)/(num-1), endpoint appended exactly
+    s = np.arange(num - 1, dtype=_F) / _F(num - 1)
+    body = _F(start) * (_F(1) - s) + _F(stop) * s
+    return np.append(body, _F(stop)).astype(_F)
+
+
+def rescale_betas(betas: np.ndarray) -> np.ndarray:
+    """Rescales betas to have zero terminal SNR (scheduling_utils_flax.py:222-263, arXiv 2305.08891 alg. 1)."""
+    alphas = _F(1) - betas
+    alphas_bar = np.cumprod(alphas, dtype=_F)
+    alphas_bar_sqrt = np.sqrt(alphas_bar)
+    a0 = alphas_bar_sqrt[0].copy()
+    aT = alphas_bar_sqrt[-1].copy()
+    alphas_bar_sqrt = alphas_bar_sqrt - aT
+    alphas_bar_sqrt = alphas_bar_sqrt * a0 / (a0 - aT)
+    alphas_bar = alphas_bar_sqrt * alphas_bar_sqrt
+    alphas = alphas_bar[1:] / alphas_bar[:-1]
+    alphas = np.concatenate([alphas_bar[0:1], alphas])
+    return (_F(1) - alphas).astype(_F)
+
+
+@dataclass(frozen=True)
+class CommonSchedulerState:
+    alphas: torch.Tensor
+    betas: torch.Tensor
+    alphas_cumprod: torch.Tensor
+
+    @classmethod
+    def create(cls, scheduler):
+        config = scheduler.config
+        n = config.num_train_timesteps
+        if config.trained_betas is not None:
+            betas = np.asarray(config.trained_betas, dtype=_F)
+        elif config.beta_schedule == "linear":
+            betas = _linspace(config.beta_start, config.beta_end, n)
+        elif config.beta_schedule == "scaled_linear":
+            b = _linspace(config.beta_start ** 0.5, config.beta_end ** 0.5, n)
+            betas = (b * b).astype(_F)
+        elif config.beta_schedule == "zero_snr_scaled_linear":
+            b = _linspace(config.beta_start ** 0.5, config.beta_end ** 0.5, n)
+            betas = rescale_betas((b * b).astype(_F))
+        elif config.beta_schedule == "squaredcos_cap_v2":
+            betas = betas_for_alpha_bar(n)
+        else:
+            raise NotImplementedError(
+                f"beta_schedule {config.beta_schedule} is not implemented for scheduler {scheduler.__class__.__name__}")
+        alphas = (_F(1.0) - betas).astype(_F)
+        alphas_cumprod = np.cumprod(alphas, dtype=_F)
+        dev = scheduler.device
+        return cls(alphas=torch.from_numpy(alphas).to(dev), betas=torch.from_numpy(betas).to(dev),
+                   alphas_cumprod=torch.from_numpy(alphas_cumprod).to(dev))
+
+
+@dataclass(frozen=True)
+class DDPMSchedulerState:
+    common: CommonSchedulerState
+    init_noise_sigma: torch.Tensor
+    timesteps: torch.Tensor
+    num_inference_steps: Optional[int] = None
+
+    @classmethod
+    def create(cls, common, init_noise_sigma, timesteps):
+        return cls(common=common, init_noise_sigma=init_noise_sigma, timesteps=timesteps)
+
+    def replace(self, **kw):
+        return dataclasses.replace(self, **kw)
+
+
+@dataclass
+class FlaxSchedulerOutput:
+    prev_sample: torch.Tensor
+
+
+@dataclass
+class FlaxDDPMSchedulerOutput(FlaxSchedulerOutput):
+    state: DDPMSchedulerState
+
+
+def _noise_mix(fn_name, state: CommonSchedulerState, a, noise, timesteps):
+    l = _lib.lib()
+    a = a.contiguous()
+    noise = noise.contiguous()
+    t = timesteps.to(torch.int32).contiguous()
+    out = torch.empty_like(a)
+    B = a.shape[0]
+    _lib.check(getattr(l, fn_name)(a.data_ptr(), noise.data_ptr(), t.data_ptr(), state.alphas_cumprod.data_ptr(),
+                                   out.data_ptr(), B, a.numel() // B, _lib.stream_ptr()), fn_name)
+    return out
+
+
+def add_noise_common(state: CommonSchedulerState, original_samples, noise, timesteps):
+    """sqrt(ac[t]) * x0 + sqrt(1 - ac[t]) * noise   (scheduling_utils_flax.py:332-337)."""
+    return _noise_mix("sdb_add_noise", state, original_samples, noise, timesteps)
+
+
+def get_velocity_common(state: CommonSchedulerState, sample, noise, timesteps):
+    """sqrt(ac[t]) * noise - sqrt(1 - ac[t]) * sample   (scheduling_utils_flax.py:340-343)."""
+    return _noise_mix("sdb_get_velocity", state, sample, noise, timesteps)
+
+
+class FlaxDDPMScheduler:
+    """scheduling_ddpm_flax.py:55-300."""
+
+    has_state = True
+
+    def __init__(self, num_train_timesteps: int = 1000, beta_start: float = 0.0001, beta_end: float = 0.02,
+                 beta_schedule: str = "linear", trained_betas=None, variance_type: str = "fixed_small",
+                 clip_sample: bool = True, prediction_type: str = "epsilon", dtype=torch.float32, device="cuda"):
+        if dtype not in (torch.float32, "float32"):
+            raise NotImplementedError("FlaxDDPMScheduler: only dtype float32 (the reference default) is built")
+        self.dtype = torch.float32
+        self.device = torch.device(device)
+        self.config = SimpleNamespace(num_train_timesteps=num_train_timesteps, beta_start=beta_start, beta_end=beta_end,
+                                      beta_schedule=beta_schedule, trained_betas=trained_betas,
+                                      variance_type=variance_type, clip_sample=clip_sample,
+                                      prediction_type=prediction_type)
+        self._host = None  # host copies of the schedules for the scalar arithmetic of step()
+
+    def create_state(self, common: Optional[CommonSchedulerState] = None) -> DDPMSchedulerState:
+        if common is None:
+            common = CommonSchedulerState.create(self)
+        init_noise_sigma = torch.tensor(1.0, dtype=self.dtype, device=self.device)
+        timesteps = torch.arange(0, self.config.num_train_timesteps, device=self.device).flip(0)
+        return DDPMSchedulerState.create(common=common, init_noise_sigma=init_noise_sigma, timesteps=timesteps)
+
+    def scale_model_input(self, state, sample, timestep: Optional[int] = None):
+        return sample
+
+    def set_timesteps(self, state: DDPMSchedulerState, num_inference_steps: int, shape: Tuple = ()):
+        step_ratio = self.config.num_train_timesteps // num_inference_steps
+        timesteps = (torch.arange(0, num_inference_steps, device=self.device) * step_ratio).flip(0)
+        return state.replace(num_inference_steps=num_inference_steps, timesteps=timesteps)
+
+    def _host_tables(self, state):
+        if self._host is None or self._host[0] is not state.common:
+            c = state.common
+            self._host = (c, c.alphas.cpu().numpy(), c.betas.cpu().numpy(), c.alphas_cumprod.cpu().numpy())
+        return self._host[1:]
+
+    def _get_variance(self, state, t, predicted_variance=None, variance_type=None):
+        alphas, betas, ac = self._host_tables(state)
+        alpha_prod_t = ac[t]
+        alpha_prod_t_prev = ac[t - 1] if t > 0 else _F(1.0)
+        variance = _F(_F(_F(1) - alpha_prod_t_prev) / _F(_F(1) - alpha_prod_t)) * betas[t]
+        if variance_type is None:
+            variance_type = self.config.variance_type
+        if variance_type == "fixed_small":
+            variance = np.maximum(variance, _F(1e-20))
+        elif variance_type == "fixed_small_log":
+            variance = np.log(np.maximum(variance, _F(1e-20)))
+        elif variance_type == "fixed_large":
+            variance = betas[t]
+        elif variance_type == "fixed_large_log":
+            variance = np.log(betas[t])
+        elif variance_type == "learned":
+            return predicted_variance
+        elif variance_type == "learned_range":
+            raise NotImplementedError("learned_range variance needs the model's variance head (not on the SD path)")
+        return _F(variance)
+
+    def step(self, state: DDPMSchedulerState, model_output, timestep: int, sample, key=None, return_dict: bool = True
+             ) -> Union[FlaxDDPMSchedulerOutput, Tuple]:
+        """Reverse-diffusion step (scheduling_ddpm_flax.py:196-279). `key`: None (seed 0), an int seed or a
+        torch.Generator for the N(0,1) draw (jax.random keys do not exist here)."""
+        t = int(timestep)
+        ptype = self.config.prediction_type
+        if ptype not in ("epsilon", "sample", "v_prediction"):
+            raise ValueError(f"prediction_type given as {ptype} must be one of `epsilon`, `sample` "
+                             " for the FlaxDDPMScheduler.")
+        if self.config.variance_type in ("learned", "learned_range"):
+            raise NotImplementedError("learned variance types are not on the SD training path")
+        alphas, betas, ac = self._host_tables(state)
+        alpha_prod_t = ac[t]
+        alpha_prod_t_prev = ac[t - 1] if t > 0 else _F(1.0)
+        beta_prod_t = _F(_F(1) - alpha_prod_t)
+        beta_prod_t_prev = _F(_F(1) - alpha_prod_t_prev)
+        x0_coeff = _F(_F(np.sqrt(alpha_prod_t_prev) * betas[t]) / beta_prod_t)
+        sample_coeff = _F(_F(np.sqrt(alphas[t]) * beta_prod_t_prev) / beta_prod_t)
+        model_output = model_output.contiguous()
+        sample = sample.contiguous()
+        noise = None
+        sigma = 0.0
+        if t > 0:
+            gen = key
+            if not isinstance(gen, torch.Generator):
+                gen = torch.Generator(device=sample.device)
+                gen.manual_seed(0 if key is None else int(key))
+            noise = torch.randn(model_output.shape, generator=gen, device=sample.device, dtype=torch.float32)
+            sigma = float(np.sqrt(self._get_variance(state, t)))
+        prev = torch.empty_like(sample)
+        _lib.check(_lib.lib().sdb_ddpm_step(model_output.data_ptr(), sample.data_ptr(), _lib.ptr(noise), prev.data_ptr(),
+                                            sample.numel(), float(np.sqrt(alpha_prod_t)), float(np.sqrt(beta_prod_t)),
+                                            float(x0_coeff), float(sample_coeff), sigma,
+                                            ("epsilon", "sample", "v_prediction").index(ptype),
+                                            int(bool(self.config.clip_sample)), _lib.stream_ptr()), "sdb_ddpm_step")
+        if not return_dict:
+            return (prev, state)
+        return FlaxDDPMSchedulerOutput(prev_sample=prev, state=state)
+
+    def add_noise(self, state: DDPMSchedulerState, original_samples, noise, timesteps):
+        return add_noise_common(state.common, original_samples, noise, timesteps)
+
+    def get_velocity(self, state: DDPMSchedulerState, sample, noise, timesteps):
+        return get_velocity_common(state.common, sample, noise, timesteps)
+
+    def __len__(self):
+        return self.config.num_train_timesteps
