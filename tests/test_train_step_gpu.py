@@ -73,10 +73,15 @@ def test_tiny_train_step_matches_oracle(cuda, ptype, Hh, L):
     assert abs(loss_gpu - float(loss64)) <= max(3 * abs(float(loss16) - float(loss64)), 2e-3 * abs(float(loss64)))
     assert err <= 3 * yard, (err, yard)
     # per-leaf check on the big leaves: no leaf may be wildly off (catches a wrong-wiring bug that a global norm hides)
+    # (absolute errors: some leaves have an exactly-zero true gradient, e.g. time_emb_proj in front of a GroupNorm
+    #  with one channel per group, where only rounding noise remains)
+    gscale = float(np.linalg.norm(v64))
     for n in names:
         if g64[n].numel() >= 1024:
-            e, y = _rel(g_gpu[n], g64[n].numpy()), _rel(g16[n].numpy(), g64[n].numpy())
-            assert e <= max(6 * y, 0.05), (n, e, y)
+            t = g64[n].numpy().astype(np.float64)
+            e = float(np.linalg.norm(g_gpu[n].astype(np.float64) - t))
+            y = float(np.linalg.norm(g16[n].numpy().astype(np.float64) - t))
+            assert e <= max(6 * y, 0.05 * float(np.linalg.norm(t)), 1e-3 * gscale), (n, e, y)
 
     # ---- criterion 2: optimizer bit-exact given the GPU's own fp32 gradients ----
     gn = np.float32(state.arena.gnorm.item())
@@ -88,9 +93,8 @@ def test_tiny_train_step_matches_oracle(cuda, ptype, Hh, L):
     n_q = 0
     for n in names:
         g = OL.clip_leaf(g_gpu[n], gn, 1.0)
-        st0 = OL.init_state(params_np[n].shape, bool(qm[n]))
-        want_p, want_s, _ = OL.lion_leaf_update(g.reshape(-1), p_before[n].reshape(-1),
-                                                st0 if not qm[n] else st0, wd_flag=bool(wd[n]))
+        st0 = OL.init_state((g.size,), bool(qm[n]))
+        want_p, want_s, _ = OL.lion_leaf_update(g.reshape(-1), p_before[n].reshape(-1), st0, wd_flag=bool(wd[n]))
         got_p = state.arena.p[n].detach().cpu().numpy().reshape(-1)
         assert np.array_equal(got_p.view(np.uint32), want_p.view(np.uint32)), n
         if qm[n]:
