@@ -1,0 +1,412 @@
+#!/usr/bin/env python
+"""bench.py — UNet train samples/sec at 512^2 (64x64x4 latents), SD-1.5 UNet, batch 8 per GPU (BASELINE.json configs[1]).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config sd15|sd21|tiny] [--batch B]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+One "step" = one pass of the hot path (add_noise -> UNet fwd -> MSE -> UNet bwd -> [bucketed NCCL all-reduce] ->
+clip + 8-bit Lion + apply) over one synthetic batch. Prints ONE JSON line on rank 0:
+  value        whole-job samples/s with the batch already resident in HBM (CUDA events, max over ranks)
+  e2e          the same through the public train_step call with HOST (pinned) batches: H2D copy of latents / noise /
+               timesteps / context and a D2H read of the loss inside the timed region, every step
+  roofline     tensor-pipe roofline of the step (algorithmic matmul FLOPs) + the HBM roofline of the Lion
+               optimizer kernels timed alone ("kernels" sub-object)
+  cpu_baseline the oracle (CPU restatement of the reference: torch-CPU fp32 UNet + NumPy Lion; JAX is not installable
+               here) timed on this box's host cores on a bounded sample of the same workload
+--impl reference times that CPU restatement as the reference arm (the reference itself is JAX/TPU code and cannot run).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "unet_train_samples_per_sec_512px"
+UNIT = "samples/s"
+# algorithmic matmul-class FLOPs per trained sample (forward x3), SURVEY.md 8(d)
+TRAIN_FLOP_PER_SAMPLE = {"sd15": 2.4098e12, "sd21": 6.4473e12, "tiny": 3.3166e9}
+WORKLOADS = {
+    "sd15": dict(name="SD-1.5 UNet (860M) train_step, 64x64x4 latents, ctx 77x768, eps-pred, Lion-8bit", H=64, L=77, batch=8),
+    "sd21": dict(name="SD-2.x UNet train_step, 96x96x4 latents, ctx 77x1024, v-pred, Lion-8bit", H=96, L=77, batch=4),
+    "tiny": dict(name="tiny UNet (32/64) train_step, 32x32x4 latents, ctx 77x32", H=32, L=77, batch=2),
+}
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sustained=d.get("bf16_tflops_sustained", d["bf16_tflops"]),
+                    source="measured (MEASURED_PEAKS.json)")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, source="fallback (B200_PROFILING.md)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def host_batches(cfg_name, cfg, B, n, seed, pin):
+    import numpy as np
+    import torch
+    w = WORKLOADS[cfg_name]
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(n):
+        b = {"latents": torch.from_numpy(rng.standard_normal((B, 4, w["H"], w["H"]), dtype=np.float32)),
+             "noise": torch.from_numpy(rng.standard_normal((B, 4, w["H"], w["H"]), dtype=np.float32)),
+             "timesteps": torch.from_numpy(rng.integers(0, 1000, B).astype(np.int32)),
+             "encoder_hidden_states": torch.from_numpy(
+                 rng.standard_normal((B, w["L"], cfg.cross_attention_dim), dtype=np.float32))}
+        if pin:
+            b = {k: v.pin_memory() for k, v in b.items()}
+        out.append(b)
+    return out
+
+
+def fast_params(cfg, seed=0):
+    """Synthetic random-init weights with the distributions of SURVEY.md 8(d) generated on the device (the 860M-element
+    NumPy generator of the tests takes ~10 s per rank; the benchmark only needs the same shapes and statistics)."""
+    import torch
+    from stable_diffusion_training_b200 import unet as PU
+    g = torch.Generator(device="cuda")
+    g.manual_seed(seed)
+    out = {}
+    for name, shape in PU.param_shapes(cfg).items():
+        parts = name.split("/")
+        leaf, parent = parts[-1], parts[-2]
+        r = torch.randn(shape, generator=g, device="cuda", dtype=torch.float32)
+        if leaf == "kernel":
+            fan_in = 1
+            for d in shape[:-1]:
+                fan_in *= d
+            r.mul_(1.0 / math.sqrt(fan_in))
+        elif leaf == "scale":
+            r.mul_(0.1).add_(1.0)
+        elif parent.startswith("norm") or parent == "conv_norm_out":
+            r.mul_(0.1)
+        else:
+            r.mul_(0.02)
+        out[name] = r
+    return out
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from stable_diffusion_training_b200 import _lib
+    from stable_diffusion_training_b200 import lion_quant as LQ
+    from stable_diffusion_training_b200 import parallel
+    from stable_diffusion_training_b200 import training_utils as TU
+    from stable_diffusion_training_b200 import unet as PU
+
+    rank, local, world = parallel.init_process_group_from_env("nccl")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    L = _lib.lib()
+    _lib.check(L.sdb_check_device(local), "sdb_check_device")
+    cfg = {"sd15": PU.SD15, "sd21": PU.SD21, "tiny": PU.TINY}[args.config]
+    w = WORKLOADS[args.config]
+    B = args.batch or w["batch"]
+    ptype = "v_prediction" if args.config == "sd21" else "epsilon"
+
+    params = LQ.unflatten_dict(fast_params(cfg, 0))
+    model = TU.UNetModel(cfg)
+    state = TU.TrainState.create(apply_fn=model.apply, params=params, tx=TU.create_lion_optimizer(params), device=dev)
+    del params
+    if world > 1:
+        parallel.attach(state)
+    sched = TU.default_scheduler(dev, "scaled_linear", ptype)
+    step_fn = TU.compile_train_step(state, sched) if args.graph else \
+        (lambda s, b, r: TU.train_step(s, b, r, frozen_noise_scheduler_state=sched))
+
+    nb = 4
+    hb = host_batches(args.config, cfg, B, nb, 1 + rank, pin=True)
+    db = [{k: v.to(dev) for k, v in b.items()} for b in hb]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident leg ("value") ----
+    for i in range(args.warmup):
+        state, m = step_fn(state, db[i % nb], i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = L.sdb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        state, m = step_fn(state, db[i % nb], i)
+    e1.record()
+    barrier()
+    launches = L.sdb_launch_count() - n0
+    if args.graph:
+        launches = getattr(step_fn, "launches_per_replay", 0) * args.steps
+    ms = e0.elapsed_time(e1)
+    loss_last = float(m["loss"])
+    t = torch.tensor([ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+
+    # ---- end-to-end leg: host batches, H2D + D2H inside the timed region ----
+    h2d = sum(v.numel() * v.element_size() for v in hb[0].values())
+    for i in range(2):
+        state, m = step_fn(state, {k: v.to(dev, non_blocking=True) for k, v in hb[i % nb].items()}, i)
+        float(m["loss"])
+    barrier()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        batch = {k: v.to(dev, non_blocking=True) for k, v in hb[i % nb].items()}
+        state, m = step_fn(state, batch, i)
+        loss_host = float(m["loss"])  # D2H read of the step's result
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+
+    out = None
+    if rank == 0:
+        peaks = measured_peaks()
+        sps = world * B * args.steps / (ms_total / 1e3)
+        flops = TRAIN_FLOP_PER_SAMPLE[args.config] * B  # per rank per step
+        step_ms = ms_total / args.steps
+        ach_tf = flops / (step_ms / 1e3) / 1e12
+        kernels = kernel_rooflines(state, peaks) if not args.no_kernels else {}
+        out = {
+            "metric": METRIC, "value": round(sps, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": w["name"], "batch_per_gpu": B, "global_batch": B * world,
+                       "parallelism": f"dp{world}", "weights": "random-init (SURVEY 8(d) distributions)",
+                       "l2": "working set (1.7 GB bf16 weights + activations) >> 126 MB L2; 4 rotating batches",
+                       "cuda_graph": bool(args.graph), "loss_last": loss_last},
+            "e2e": {"value": round(world * B * args.steps / e2e_s, 3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": 4, "loss_last": loss_host},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "achieved": round(ach_tf, 2), "peak": peaks["tf_sustained"],
+                         "unit": "TFLOP/s", "frac": round(ach_tf / peaks["tf_sustained"], 4), "traffic": None,
+                         "of": peaks["source"] + ", sustained bf16 (kernel timed inside a long step)",
+                         "what": "whole train step: algorithmic matmul FLOPs/step / step time", "kernels": kernels},
+        }
+        if not args.no_cpu:
+            out["cpu_baseline"] = cpu_baseline(args.config, budget_s=args.cpu_budget)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def kernel_rooflines(state, peaks):
+    """Live CUDA-event timing of the dominant kernels, each alone on the launching stream with the L2 flushed between
+    iterations: (1) the 8-bit Lion update over the whole arena (HBM bound, 14.5 B/quantised element + 20 B/fp32-state
+    element); (2) the tcgen05 implicit-GEMM conv3x3 320->320 @ 64x64, batch 8 (tensor bound)."""
+    import torch
+    from stable_diffusion_training_b200 import ops
+    res = {}
+    a = state.arena
+    dev = a.device
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    h = state.hyper
+
+    def timed(fn, iters=10):
+        for _ in range(3):
+            fn()
+        ts = []
+        for _ in range(iters):
+            flush.zero_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        ts.sort()
+        return sum(ts) / len(ts)
+
+    a.grad.normal_(0, 3.4e-5)
+    lr = h["learning_rate"](0) if callable(h["learning_rate"]) else h["learning_rate"]
+    ms = timed(lambda: a.optimizer_step(lr=float(lr), b1=h["b1"], b2=h["b2"], wd=h["weight_decay"], max_norm=None))
+    nq = a.n_quant
+    nf = a.n_total - a.n_quant
+    by = nq * (4 + 8 + 2 + 8 / 16) + nf * 20   # shadow bf16 write excluded from the algorithmic count
+    res["lion8_update"] = {"bound": "hbm", "bytes": by, "ms": round(ms, 4), "achieved": round(by / ms / 1e6, 1),
+                           "peak": peaks["hbm"], "unit": "GB/s", "frac": round(by / ms / 1e6 / peaks["hbm"], 4)}
+    ms = timed(lambda: a.optimizer_step(lr=float(lr), b1=h["b1"], b2=h["b2"], wd=h["weight_decay"], max_norm=1.0))
+    by2 = by + a.n_total * 4
+    res["clip_norm_plus_lion8"] = {"bound": "hbm", "bytes": by2, "ms": round(ms, 4), "achieved": round(by2 / ms / 1e6, 1),
+                                   "peak": peaks["hbm"], "unit": "GB/s", "frac": round(by2 / ms / 1e6 / peaks["hbm"], 4)}
+    for (Bn, Hh, cin, cout) in ((8, 64, 320, 320), (8, 32, 640, 640), (8, 16, 1280, 1280)):
+        x = torch.randn(Bn, Hh, Hh, cin, device=dev).to(torch.bfloat16)
+        wgt = (torch.randn(3, 3, cin, cout, device=dev) * 0.02).to(torch.bfloat16)
+        bias = torch.zeros(cout, device=dev)
+        out = torch.empty(Bn, Hh, Hh, cout, device=dev, dtype=torch.bfloat16)
+        fl = 2.0 * Bn * Hh * Hh * cout * 9 * cin
+        ms = timed(lambda: ops.conv3x3(x, wgt, bias=bias, out=out))
+        res[f"conv3x3_fwd_{cin}x{cout}@{Hh}"] = {"bound": "tensor", "flops": fl, "ms": round(ms, 4),
+                                                "achieved": round(fl / ms / 1e9, 1), "peak": peaks["tf_burst"],
+                                                "unit": "TFLOP/s", "frac": round(fl / ms / 1e9 / peaks["tf_burst"], 4)}
+    return res
+
+
+# ---------------------------------------------------------------------------------------------------------------
+def cpu_baseline(config: str, budget_s: float = 30.0, steps: int = 1):
+    """The oracle timed as the CPU baseline: torch-CPU fp32 restatement of the reference UNet train step on ONE sample of
+    the workload (fwd + bwd + loss, all host threads) + NumPy 8-bit Lion on a 1/16 subset of the leaves scaled to
+    the full set. kind = "port" (the reference is JAX and cannot be imported on this box)."""
+    import numpy as np
+    import torch
+    from oracle import lion as OL
+    from oracle import sched as OS
+    from oracle import unet as OU
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = {"sd15": OU.SD15, "sd21": OU.SD21, "tiny": OU.TINY}[config]
+    w = WORKLOADS[config]
+    Bs = 1 if config != "tiny" else w["batch"]
+    g = torch.Generator().manual_seed(0)
+    params = {}
+    for name, shape in OU.param_shapes(cfg).items():
+        fan = 1
+        for d in shape[:-1]:
+            fan *= d
+        params[name] = torch.randn(shape, generator=g) * (1.0 / math.sqrt(max(fan, 1)) if name.endswith("kernel") else 0.02)
+        if name.endswith("scale"):
+            params[name] += 1.0
+    ac = OS.common_state("scaled_linear", 0.00085, 0.012)["alphas_cumprod"]
+    lat = torch.randn(Bs, 4, w["H"], w["H"], generator=g)
+    nz = torch.randn(Bs, 4, w["H"], w["H"], generator=g)
+    ts = torch.randint(0, 1000, (Bs,), generator=g)
+    ctx = torch.randn(Bs, w["L"], cfg.cross_attention_dim, generator=g)
+    ptype = "v_prediction" if config == "sd21" else "epsilon"
+    times = []
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        loss, grads, _ = OU.loss_and_grads(cfg, params, lat, nz, ts, ctx, ac, prediction_type=ptype, mode="fp32")
+        t_unet = time.perf_counter() - t0
+        names = sorted(params)
+        sub = names[::16]
+        frac = sum(params[n].numel() for n in sub) / sum(params[n].numel() for n in names)
+        t0 = time.perf_counter()
+        for n in sub:
+            gl = grads[n].numpy().reshape(-1)
+            q = n.endswith("kernel") and gl.size % 16 == 0
+            st = OL.init_state((gl.size,), q)
+            OL.lion_leaf_update(gl, params[n].numpy().reshape(-1), st, wd_flag=n.endswith("kernel"))
+        t_lion = (time.perf_counter() - t0) / max(frac, 1e-9)
+        times.append(t_unet + t_lion)
+        del grads
+    t = sorted(times)[len(times) // 2]
+    return {"value": round(Bs / t, 5), "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{Bs} sample(s) of the workload through the oracle (torch-CPU fp32 UNet fwd+bwd+loss {t_unet:.1f} s, "
+                      f"{cores} threads) + NumPy Lion-8bit on 1/16 of the leaves scaled to all ({t_lion:.1f} s); "
+                      f"JAX/Flax reference not installable here", "seconds_per_step": round(t, 2)}
+
+
+def run_reference(args):
+    """Reference arm: the reference's own train step is JAX/Flax on TPU and cannot be imported or installed on this box
+    (no jax / flax / optax / diffusers wheels, no network); the arm therefore times the CPU restatement (oracle port) on
+    the host cores. Rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return None
+    w = WORKLOADS[args.config]
+    B = args.batch or w["batch"]
+    steps = max(1, min(args.steps, 3))
+    for _ in range(min(args.warmup, 1)):
+        cpu_baseline(args.config, steps=1)
+    cb = cpu_baseline(args.config, steps=steps)
+    return {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+            "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": round(1e3 * cb["seconds_per_step"], 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": w["name"], "batch_per_gpu": B, "global_batch": B * args.gpus,
+                       "note": "CPU restatement of the reference (oracle port); each step = a bounded 1-sample pass"},
+            "cpu_baseline": cb, "gpu_launches": 0,
+            "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="sd15", choices=list(WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--graph", type=int, default=0, help="replay the step from a CUDA graph")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline leg")
+    ap.add_argument("--cpu-budget", type=float, default=30.0)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if out is not None:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

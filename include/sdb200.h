@@ -32,6 +32,8 @@ typedef struct CUstream_st* cudaStream_t;
 const char* sdb_last_error_string(void);
 int sdb_abi_version(void);
 int sdb_check_device(int device); /* fails unless the device is compute capability 10.x */
+long long sdb_launch_count(void); /* kernels this library has launched in this process (monotonic; bench.py's
+                                     gpu_launches is the difference across the timed region) */
 
 /* ---- 8-bit Lion (lion_quant.py:20-156, chain 201-211; optax clip/apply as wired at training_utils.py:355-382, 732)
  * One launch over a flat fp32 segment. Block b of 16 consecutive elements has int8 codes[16*b .. 16*b+15] and the

@@ -48,6 +48,7 @@ SIGNATURES = {
     "sdb_last_error_string": (C.c_char_p, []),
     "sdb_abi_version": (_I, []),
     "sdb_check_device": (_I, [_I]),
+    "sdb_launch_count": (_LL, []),
     "sdb_lion8_update": (_I, [_P, _P, _P, _P, _P, _P, _LL, _I, _D, _D, _D, _D, _I, _P, _D, _I, _P]),
     "sdb_lion_fp32_update": (_I, [_P, _P, _P, _P, _P, _LL, _D, _D, _D, _D, _I, _P, _D, _I, _P]),
     "sdb_sumsq_workspace_bytes": (_SZ, []),

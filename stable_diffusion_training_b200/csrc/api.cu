@@ -2,6 +2,7 @@
 #include "sdb_common.cuh"
 #include "../../include/sdb200.h"
 #include <cstring>
+#include <atomic>
 
 static thread_local char g_err[512] = "";
 
@@ -12,6 +13,10 @@ int sdb_set_error(int code, const char* fmt, ...) {
   va_end(ap);
   return code;
 }
+
+static std::atomic<long long> g_launches{0};
+void sdb_note_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+extern "C" long long sdb_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" const char* sdb_last_error_string(void) { return g_err; }
 

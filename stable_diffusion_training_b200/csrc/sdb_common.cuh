@@ -17,6 +17,7 @@ enum SdbStatus : int {
 };
 
 int sdb_set_error(int code, const char* fmt, ...);
+void sdb_note_launch();  // bumps the counter behind sdb_launch_count() (api.cu)
 
 #define SDB_CHECK_ARG(cond, ...)                                   \
   do {                                                             \
@@ -26,6 +27,7 @@ int sdb_set_error(int code, const char* fmt, ...);
 #define SDB_CUDA_LAUNCH_CHECK(name)                                                      \
   do {                                                                                   \
     cudaError_t e__ = cudaGetLastError();                                                \
+    sdb_note_launch();                                                                   \
     if (e__ != cudaSuccess)                                                              \
       return sdb_set_error(SDB_ERR_CUDA, "%s: launch failed: %s", name, cudaGetErrorString(e__)); \
   } while (0)

@@ -1,0 +1,159 @@
+"""Data-parallel gradient mean for the denoising train step: one process per GPU, bucketed NCCL all-reduce over
+NVLink 5 / NVSwitch, issued on a communication stream while backward still runs.
+
+Replaces what the reference gets implicitly from GSPMD: the batch is sharded on the "data_parallel" mesh axis and
+everything else is replicated (/root/reference/training_utils.py:35-37, 835-840, 852-931), so XLA inserts an all-reduce
+(mean) of the fp32 gradients and of the scalar loss. Here:
+
+  * the per-rank loss gradient is pre-scaled by 1/world (train_step passes loss_grad_scale), so a SUM all-reduce of the
+    gradient arena yields the mean over the global batch — identical to the 1-rank result on the concatenated batch;
+  * the arena is cut into contiguous buckets along its own order, which inside each segment is the order in which
+    backward finishes the leaves (training_utils.ParamArena), so buckets become ready front to back;
+  * Graph.backward() reports finished leaves (unet.Graph.backward(on_grads=...)); when the last leaf of a bucket is in,
+    an event is recorded on the compute stream, the communication stream waits on it and enqueues the all-reduce;
+  * finish() flushes what is left, reduces the scalar loss, and makes the compute stream wait for the communication
+    stream — the optimizer (replicated, bit-identical on every rank) then runs on reduced gradients.
+
+No collective is issued when world_size == 1. The class works on any torch tensor + process group (the CPU tests run
+it with gloo, world_size 2); streams/events are used only for CUDA tensors.
+"""
+from __future__ import annotations
+
+import os
+from typing import Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+DEFAULT_BUCKET_BYTES = 64 << 20
+
+
+def build_buckets(ranges: Dict[str, Tuple[int, int]], bucket_elems: int) -> List[Tuple[int, int, List[str]]]:
+    """Cut the flat arena into contiguous [start, end) buckets on leaf boundaries, in arena order; every bucket holds
+    at least `bucket_elems` elements except possibly the last. Leaves larger than a bucket get their own."""
+    leaves = sorted(ranges.items(), key=lambda kv: kv[1][0])
+    out: List[Tuple[int, int, List[str]]] = []
+    cur: List[str] = []
+    start = None
+    end = 0
+    for name, (s, e) in leaves:
+        if start is None:
+            start = s
+        cur.append(name)
+        end = e
+        if end - start >= bucket_elems:
+            out.append((start, end, cur))
+            cur, start = [], None
+    if cur:
+        out.append((start, end, cur))
+    # buckets tile the range they span: the alignment padding between leaves rides along with the bucket before it
+    fixed = [(s, out[i + 1][0] if i + 1 < len(out) else e, names) for i, (s, e, names) in enumerate(out)]
+    return fixed
+
+
+class GradReducer:
+    def __init__(self, grad_flat: torch.Tensor, ranges: Dict[str, Tuple[int, int]], *, group=None,
+                 bucket_bytes: int = DEFAULT_BUCKET_BYTES, total_elems: Optional[int] = None):
+        self.grad = grad_flat
+        self.group = group
+        self.world_size = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.buckets = build_buckets(ranges, max(1, bucket_bytes // grad_flat.element_size()))
+        if total_elems is not None and self.buckets:  # trailing padding of the arena belongs to the last bucket
+            s, e, names = self.buckets[-1]
+            self.buckets[-1] = (s, max(e, total_elems), names)
+        self.bucket_of = {n: i for i, (_, _, names) in enumerate(self.buckets) for n in names}
+        self.cuda = grad_flat.is_cuda
+        self.comm_stream = torch.cuda.Stream(device=grad_flat.device) if self.cuda else None
+        self._pending: List[int] = []
+        self._next = 0            # buckets are issued strictly in index order (identical on every rank)
+        self._ready: List[bool] = []
+        self.issued_order: List[int] = []
+        self.bytes_reduced = 0
+
+    # ---- one step ----
+    def begin(self, _graph=None) -> None:
+        self._pending = [len(names) for _, _, names in self.buckets]
+        self._ready = [False] * len(self.buckets)
+        self._next = 0
+        self.issued_order = []
+
+    def on_param_grad(self, names: Sequence[str]) -> None:
+        for n in names:
+            b = self.bucket_of.get(n)
+            if b is None:
+                continue
+            self._pending[b] -= 1
+            if self._pending[b] == 0:
+                self._ready[b] = True
+        self._issue_ready()
+
+    def _issue_ready(self, force: bool = False) -> None:
+        while self._next < len(self.buckets) and (force or self._ready[self._next]):
+            self._all_reduce_bucket(self._next)
+            self._next += 1
+
+    def _all_reduce_bucket(self, b: int) -> None:
+        s, e, _ = self.buckets[b]
+        self.issued_order.append(b)
+        if self.world_size == 1:
+            return
+        view = self.grad[s:e]
+        self.bytes_reduced += view.numel() * view.element_size()
+        if self.cuda:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(self.grad.device))
+            self.comm_stream.wait_event(ev)
+            with torch.cuda.stream(self.comm_stream):
+                dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+        else:
+            dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+
+    def finish(self, loss: torch.Tensor) -> torch.Tensor:
+        """Flush the remaining buckets, average the loss over ranks, join the communication stream."""
+        self._issue_ready(force=True)
+        if self.world_size > 1:
+            if self.cuda:
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.grad.device))
+                self.comm_stream.wait_event(ev)
+                with torch.cuda.stream(self.comm_stream):
+                    dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
+                    loss.mul_(1.0 / self.world_size)
+                torch.cuda.current_stream(self.grad.device).wait_stream(self.comm_stream)
+            else:
+                dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
+                loss.mul_(1.0 / self.world_size)
+        return loss
+
+
+def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES) -> GradReducer:
+    """Give a TrainState its data-parallel reducer (train_step then shards nothing itself: each rank is handed its own
+    slice of the global batch, as the reference's PartitionSpec("data_parallel", None) does)."""
+    a = state.arena
+    ranges = {}
+    for n, shape in a.shapes.items():
+        numel = 1
+        for d in shape:
+            numel *= int(d)
+        ranges[n] = (a.offset[n], a.offset[n] + numel)
+    state.dp = GradReducer(a.grad, ranges, group=group, bucket_bytes=bucket_bytes, total_elems=a.n_total)
+    return state.dp
+
+
+def init_process_group_from_env(backend: Optional[str] = None) -> Tuple[int, int, int]:
+    """torchrun-style rendezvous (RANK / LOCAL_RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT). Returns
+    (rank, local_rank, world_size); a single process without those variables is world_size 1 and no group."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, rank=rank, world_size=world, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend, rank=rank, world_size=world)
+    return rank, local, world

@@ -214,9 +214,14 @@ class Graph:
         else:
             ops.add_(t.g, g)
 
-    def backward(self) -> None:
-        for fn in reversed(self.tape):
+    def backward(self, on_grads=None) -> None:
+        """Replay the tape in reverse. `on_grads(names)` is called right after the closure that finishes the gradients
+        of those parameter leaves has been enqueued (every leaf is used once per forward, so 'finished' is exact):
+        the data-parallel reducer starts a bucket's all-reduce from it while the rest of backward still runs."""
+        for fn, names in reversed(self.tape):
             fn()
+            if on_grads is not None and names:
+                on_grads(names)
         self.tape = []
 
     def _kbias(self, sq: int, skv: int, device):
@@ -247,7 +252,7 @@ class Graph:
             if res is not None:
                 self._acc(res, dy)
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, [name + "/kernel"] + ([name + "/bias"] if bias else [])))
         return y
 
     def conv3x3(self, x: T, name: str, temb: Optional[T] = None, res: Optional[T] = None, stride: int = 1) -> T:
@@ -289,7 +294,7 @@ class Graph:
             if res is not None:
                 self._acc(res, dy)
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, [name + "/kernel", name + "/bias"]))
         return y
 
     def groupnorm(self, x: T, name: str, silu: bool) -> T:
@@ -304,7 +309,7 @@ class Graph:
                                     self.G[name + "/scale"], self.G[name + "/bias"], silu=silu,
                                     dx_add=None if x.g is None else x.g.view(B, -1, C)).view(-1, C)
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, [name + "/scale", name + "/bias"]))
         return y
 
     def layernorm(self, x: T, name: str) -> T:
@@ -316,7 +321,7 @@ class Graph:
             x.g = ops.layernorm_bwd(x.v, y.g, stats, gamma, self.G[name + "/scale"], self.G[name + "/bias"],
                                     dx_add=x.g)
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, [name + "/scale", name + "/bias"]))
         return y
 
     def geglu(self, u: T) -> T:
@@ -325,7 +330,7 @@ class Graph:
         def bwd():
             self._acc(u, ops.geglu_bwd(u.v, y.g))
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, None))
         return y
 
     def silu(self, x: T) -> T:
@@ -334,7 +339,7 @@ class Graph:
         def bwd():
             self._acc(x, ops.silu_bwd(x.v, y.g))
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, None))
         return y
 
     def attention_core(self, q: T, k: T, v: T, B: int, heads: int) -> T:
@@ -351,7 +356,7 @@ class Graph:
             self._acc(k, dk.view(-1, C))
             self._acc(v, dv.view(-1, C))
             o.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, None))
         return o
 
     def attention(self, x: T, ctx: T, name: str, B: int, heads: int, res: T) -> T:
@@ -376,7 +381,7 @@ class Graph:
                 else:
                     ops.copy2d(sl, t.g, accumulate=True)
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, None))
         return y
 
     def upsample(self, x: T) -> T:
@@ -387,7 +392,7 @@ class Graph:
         def bwd():
             self._acc(x, ops.upsample2x_bwd(y.g.view(B, 2 * H, 2 * W, C)).view(-1, C))
             y.g = None
-        self.tape.append(bwd)
+        self.tape.append((bwd, None))
         return y
 
     # -------- composite blocks (diffusers 0.21.4 FlaxResnetBlock2D / FlaxTransformer2DModel) --------
@@ -467,7 +472,7 @@ class UNet:
                 x = g.conv3x3(g.groupnorm(x, op[1], silu=True), op[2])
         return x
 
-    def backward(self, pred: T, dpred: torch.Tensor) -> None:
+    def backward(self, pred: T, dpred: torch.Tensor, on_grads=None) -> None:
         pred.g = dpred
-        self.graph.backward()
+        self.graph.backward(on_grads)
         self.graph = None
