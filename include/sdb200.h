@@ -147,6 +147,21 @@ int sdb_gemm_tc(const sdb_gemm_desc* desc, cudaStream_t stream);
  * Same descriptor, same semantics; no alignment or divisibility constraints. */
 int sdb_gemm_simt(const sdb_gemm_desc* desc, cudaStream_t stream);
 
+/* 3x3 stride-1 pad-1 convolutions with a 4-channel side — FlaxUNet2DConditionModel.conv_in (4 -> C) and .conv_out
+ * (C -> 4) [diffusers 0.21.4; training_utils.py:678-684]: K = 4 per tap / N = 4 cannot fill a tcgen05 tile and the
+ * layers are memory-bound, so they run on CUDA cores. NHWC bf16 activations, HWIO bf16 weights, fp32 bias / dW.
+ * C: the wide channel count (multiple of 8, <= 904). wgrad zeroes dw itself (cudaMemsetAsync) and accumulates with red. */
+int sdb_conv3x3_c4in_fwd(const void* x4, const void* w_hwio, const float* bias, void* y, int B, int H, int W, int C,
+                         cudaStream_t stream);
+int sdb_conv3x3_c4out_fwd(const void* x, const void* w_hwio, const float* bias, void* y4, int B, int H, int W, int C,
+                          cudaStream_t stream);
+int sdb_conv3x3_c4out_dgrad(const void* dy4, const void* w_hwio, void* dx, int B, int H, int W, int C,
+                            cudaStream_t stream);
+/* c4_is_input = 1: conv_in  (c4 = x [B,H,W,4],  wide = dy [B,H,W,C]) -> dw [3,3,4,C]
+ * c4_is_input = 0: conv_out (c4 = dy [B,H,W,4], wide = x  [B,H,W,C]) -> dw [3,3,C,4] */
+int sdb_conv3x3_c4_wgrad(const void* wide, const void* c4, float* dw, int B, int H, int W, int C, int c4_is_input,
+                         cudaStream_t stream);
+
 /* ---- normalisation / activation (flax.linen GroupNorm, LayerNorm, nn.gelu as used by diffusers-0.21.4
  * FlaxResnetBlock2D / FlaxTransformer2DModel / FlaxBasicTransformerBlock / FlaxGEGLU [upstream, un-vendored], reached
  * from training_utils.py:678-684). bf16 "pixels x channels" tensors, fp32 parameters and statistics.

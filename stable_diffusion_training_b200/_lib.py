@@ -62,6 +62,10 @@ SIGNATURES = {
     "sdb_mse_fwd_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _SZ, _P]),
     "sdb_gemm_tc": (_I, [C.POINTER(GemmDesc), _P]),
     "sdb_gemm_simt": (_I, [C.POINTER(GemmDesc), _P]),
+    "sdb_conv3x3_c4in_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "sdb_conv3x3_c4out_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "sdb_conv3x3_c4out_dgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),
+    "sdb_conv3x3_c4_wgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "sdb_groupnorm_workspace_bytes": (_SZ, [_I, _I, _I]),
     "sdb_groupnorm_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _F, _I, _P, _SZ, _P]),
     "sdb_groupnorm_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _SZ, _P]),

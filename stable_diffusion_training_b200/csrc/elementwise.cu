@@ -129,40 +129,58 @@ __global__ void add_bf16_kernel(const uint4* __restrict__ a, const uint4* __rest
   }
 }
 
+constexpr int kColsumMinRows = 32;
 // column sums of a bf16 [nseg * rows_per_seg, cols] matrix (row stride ld), per segment and in total:
 // stage 1 -> part[seg][block][cols]; stage 2 -> out_total[c] (fp32) and/or out_seg[seg][c] (bf16).
-constexpr int kColsumRowsPerBlock = 256;
+// grid: x = seg * bps + row block (rpb rows each), y = 256-column chunk; rpb is chosen by the host so that the grid
+// fills the 148 SMs even for short, wide matrices (2048 x 10240 FF gradients).
 __global__ void __launch_bounds__(256)
-colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows_per_seg, int bps, int cols,
-                      float* __restrict__ part) {
-  // thread (ty, tx): tx over 8-wide column vectors (32 per pass), ty over 8 row lanes
+colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows_per_seg, int bps, int rpb,
+                      int cols, float* __restrict__ part) {
+  // thread (ty, tx): tx over 8-wide column vectors (32 per chunk), ty over 8 row lanes
   __shared__ float s[8][256 + 8];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int seg = blockIdx.x / bps, blk = blockIdx.x - seg * bps;
-  const long long r0 = seg * rows_per_seg + (long long)blk * kColsumRowsPerBlock;
-  const long long r1 = min((seg + 1) * rows_per_seg, r0 + kColsumRowsPerBlock);
-  for (int c0 = 0; c0 < cols; c0 += 256) {
-    const int c = c0 + tx * 8;
-    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (c < cols) {
-      for (long long r = r0 + ty; r < r1; r += 8) {
-        float f[8];
-        unpack8(sdb::ld_u4(x + r * ld + c), f);
+  const long long r0 = seg * rows_per_seg + (long long)blk * rpb;
+  const long long r1 = min((seg + 1) * rows_per_seg, r0 + rpb);
+  const int c0 = blockIdx.y * 256;
+  const int c = c0 + tx * 8;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c < cols) {
+    long long r = r0 + ty;
+    for (; r + 24 < r1; r += 32) {  // 4 independent 128-bit loads in flight per thread
+      const uint4 v0 = sdb::ld_u4(x + r * ld + c), v1 = sdb::ld_u4(x + (r + 8) * ld + c);
+      const uint4 v2 = sdb::ld_u4(x + (r + 16) * ld + c), v3 = sdb::ld_u4(x + (r + 24) * ld + c);
+      float f[8];
+      unpack8(v0, f);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] += f[k];
-      }
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      unpack8(v1, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      unpack8(v2, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+      unpack8(v3, f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
     }
+    for (; r < r1; r += 8) {
+      float f[8];
+      unpack8(sdb::ld_u4(x + r * ld + c), f);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) s[ty][tx * 8 + k] = acc[k];
-    __syncthreads();
-    const int cc = c0 + threadIdx.x;
-    if (cc < cols) {
-      float t = 0.f;
-#pragma unroll
-      for (int j = 0; j < 8; ++j) t += s[j][threadIdx.x];
-      part[(size_t)blockIdx.x * cols + cc] = t;
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
     }
-    __syncthreads();
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) s[ty][tx * 8 + k] = acc[k];
+  __syncthreads();
+  const int cc = c0 + threadIdx.x;
+  if (cc < cols) {
+    float t = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t += s[j][threadIdx.x];
+    part[(size_t)blockIdx.x * cols + cc] = t;
   }
 }
 __global__ void colsum_final_kernel(const float* __restrict__ part, int nseg, int bps, int cols,
@@ -289,7 +307,7 @@ extern "C" int sdb_add_bf16(const void* a, const void* b, void* out, long long n
 
 extern "C" size_t sdb_colsum_workspace_bytes(long long rows, int cols) {
   // upper bound for any segmentation of `rows` rows (each segment rounds its block count up)
-  const long long blocks = (rows + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock;
+  const long long blocks = (rows + kColsumMinRows - 1) / kColsumMinRows;
   return (size_t)(blocks + 4096) * cols * sizeof(float);
 }
 
@@ -302,12 +320,17 @@ extern "C" int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long 
   }
   SDB_CHECK_ARG(cols % 8 == 0 && ld % 8 == 0 && rows_per_seg > 0 && nseg > 0 && nseg <= 4096,
                 "sdb_colsum_bf16: cols/ld must be multiples of 8, 1 <= nseg <= 4096");
-  const int bps = (int)((rows_per_seg + kColsumRowsPerBlock - 1) / kColsumRowsPerBlock);
+  const int col_chunks = (cols + 255) / 256;
+  int rpb = 256;  // halve the rows per block until the grid covers ~2 waves (or the block gets too short)
+  while (rpb > kColsumMinRows &&
+         (long long)nseg * ((rows_per_seg + rpb - 1) / rpb) * col_chunks < 2 * sdb::kNumSMs)
+    rpb >>= 1;
+  const int bps = (int)((rows_per_seg + rpb - 1) / rpb);
   const size_t need = (size_t)nseg * bps * cols * sizeof(float);
   if (ws_bytes < need) return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_colsum_bf16: workspace %zu < %zu", ws_bytes, need);
   float* part = reinterpret_cast<float*>(workspace);
-  colsum_partial_kernel<<<nseg * bps, 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld, rows_per_seg, bps,
-                                                        cols, part);
+  colsum_partial_kernel<<<dim3(nseg * bps, col_chunks), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld,
+                                                                          rows_per_seg, bps, rpb, cols, part);
   SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(partial)");
   colsum_final_kernel<<<(cols + 255) / 256, 256, 0, stream>>>(part, nseg, bps, cols, out_total,
                                                               reinterpret_cast<__nv_bfloat16*>(out_seg_bf16));

@@ -125,39 +125,47 @@ gn_partial_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __re
   }
 }
 
-// GroupNorm pass 2 (one block per sample): reduce chunks -> per-channel totals -> per-group scalars.
+// GroupNorm pass 2 (one block per (group, sample)): reduce chunks -> per-channel totals -> per-group scalars.
+// Warp w owns channels w, w+8, ... of the group; lanes stride over the chunk partials.
 //   BWD = false: stats[b][g] = (mean, rstd)
 //   BWD = true : chan_tot[b][c] = (sum dz, sum dz*xhat); grp[b][g] = (mean_g(gamma*dz), mean_g(gamma*dz*xhat))
 template <bool BWD>
 __global__ void __launch_bounds__(256)
 gn_finalize_kernel(const float2* __restrict__ part, const float* __restrict__ gamma, float2* __restrict__ out_grp,
                    float2* __restrict__ chan_tot, GnShape s, float eps) {
-  extern __shared__ float2 s_chan[];  // [C]
-  const int b = blockIdx.x;
-  for (int c = threadIdx.x; c < s.C; c += blockDim.x) {
+  __shared__ float2 s_w[8];
+  const int g = blockIdx.x, b = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float g0 = 0.f, g1 = 0.f;
+  for (int ci = warp; ci < s.cpg; ci += 8) {
+    const int c = g * s.cpg + ci;
     float t0 = 0.f, t1 = 0.f;
-    for (int j = 0; j < s.chunks; ++j) {
+    for (int j = lane; j < s.chunks; j += 32) {
       const float2 p = part[((size_t)b * s.chunks + j) * s.C + c];
       t0 += p.x; t1 += p.y;
     }
+    t0 = sdb::warp_sum(t0);
+    t1 = sdb::warp_sum(t1);
     if (BWD) {
-      chan_tot[(size_t)b * s.C + c] = make_float2(t0, t1);
-      const float g = gamma[c];
-      t0 *= g; t1 *= g;
+      if (lane == 0) chan_tot[(size_t)b * s.C + c] = make_float2(t0, t1);
+      const float gm = gamma[c];
+      t0 *= gm; t1 *= gm;
     }
-    s_chan[c] = make_float2(t0, t1);
+    g0 += t0; g1 += t1;
   }
+  if (lane == 0) s_w[warp] = make_float2(g0, g1);
   __syncthreads();
-  if (threadIdx.x < kGroups) {
+  if (threadIdx.x == 0) {
     float t0 = 0.f, t1 = 0.f;
-    for (int c = threadIdx.x * s.cpg; c < (threadIdx.x + 1) * s.cpg; ++c) { t0 += s_chan[c].x; t1 += s_chan[c].y; }
+#pragma unroll
+    for (int w = 0; w < 8; ++w) { t0 += s_w[w].x; t1 += s_w[w].y; }
     const float inv_n = 1.0f / ((float)s.HW * (float)s.cpg);
     if (!BWD) {
       const float mean = t0 * inv_n;
       const float var = fmaxf(0.0f, t1 * inv_n - mean * mean);
-      out_grp[b * kGroups + threadIdx.x] = make_float2(mean, rsqrtf(var + eps));
+      out_grp[b * kGroups + g] = make_float2(mean, rsqrtf(var + eps));
     } else {
-      out_grp[b * kGroups + threadIdx.x] = make_float2(t0 * inv_n, t1 * inv_n);
+      out_grp[b * kGroups + g] = make_float2(t0 * inv_n, t1 * inv_n);
     }
   }
 }
@@ -357,14 +365,24 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
 }
 
 // out[which][c] = sum_blocks part[block][which][c]   (which 0 -> dgamma, 1 -> dbeta)
-__global__ void colsum_finalize_kernel(const float* __restrict__ part, int nblocks, int width, float* __restrict__ out0,
-                                       float* __restrict__ out1, int C) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= width) return;
+__global__ void __launch_bounds__(256)
+colsum_finalize_kernel(const float* __restrict__ part, int nblocks, int width, float* __restrict__ out0,
+                       float* __restrict__ out1, int C) {
+  // 32 columns per block, 8 row slices per column
+  __shared__ float s[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
   float t = 0.f;
-  for (int j = 0; j < nblocks; ++j) t += part[(size_t)j * width + c];
-  if (c < C) out0[c] = t;
-  else out1[c - C] = t;
+  if (c < width)
+    for (int j = ty; j < nblocks; j += 8) t += part[(size_t)j * width + c];
+  s[ty][tx] = t;
+  __syncthreads();
+  if (ty == 0 && c < width) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j) t += s[j][tx];
+    if (c < C) out0[c] = t;
+    else out1[c - C] = t;
+  }
 }
 
 int ln_grid(int rows) {
@@ -462,7 +480,7 @@ extern "C" int sdb_groupnorm_fwd(const void* x, const float* gamma, const float*
   if (s.KC == 1) gn_partial_kernel<1, false, false><<<grid, threads, sm, stream>>>(xp, nullptr, nullptr, nullptr, nullptr, part, s);
   else gn_partial_kernel<2, false, false><<<grid, threads, sm, stream>>>(xp, nullptr, nullptr, nullptr, nullptr, part, s);
   SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_fwd(partial)");
-  gn_finalize_kernel<false><<<B, 256, s.C * sizeof(float2), stream>>>(part, nullptr, st, nullptr, s, eps);
+  gn_finalize_kernel<false><<<dim3(kGroups, B), 256, 0, stream>>>(part, nullptr, st, nullptr, s, eps);
   SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_fwd(finalize)");
 #define GN_APPLY(KC_, SILU_) \
   gn_apply_kernel<KC_, false, SILU_><<<grid, threads, 0, stream>>>(xp, nullptr, st, nullptr, gamma, beta, nullptr, yp, s)
@@ -497,7 +515,7 @@ extern "C" int sdb_groupnorm_bwd(const void* x, const void* dy, const float* sta
   else { if (silu) GN_PART(2, true); else GN_PART(2, false); }
 #undef GN_PART
   SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(partial)");
-  gn_finalize_kernel<true><<<B, 256, s.C * sizeof(float2), stream>>>(part, gamma, grp, chan_tot, s, 0.f);
+  gn_finalize_kernel<true><<<dim3(kGroups, B), 256, 0, stream>>>(part, gamma, grp, chan_tot, s, 0.f);
   SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(finalize)");
   gn_param_grad_kernel<<<(C + 255) / 256, 256, 0, stream>>>(chan_tot, dgamma, dbeta, B, C);
   SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(param)");
@@ -573,7 +591,7 @@ extern "C" int sdb_layernorm_bwd(const void* x, const void* dy, const float* sta
   }
 #undef LN_B
   SDB_CUDA_LAUNCH_CHECK("sdb_layernorm_bwd");
-  colsum_finalize_kernel<<<(2 * C + 255) / 256, 256, 0, stream>>>(part, grid, 2 * C, dgamma, dbeta, C);
+  colsum_finalize_kernel<<<(2 * C + 31) / 32, 256, 0, stream>>>(part, grid, 2 * C, dgamma, dbeta, C);
   SDB_CUDA_LAUNCH_CHECK("sdb_layernorm_bwd(finalize)");
   return SDB_OK;
 }

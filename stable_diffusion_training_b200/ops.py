@@ -214,6 +214,43 @@ def conv3x3_wgrad(x: torch.Tensor, dy: torch.Tensor, *, out=None, impl="tc") -> 
     return out
 
 
+# ---- conv_in (4 -> C) / conv_out (C -> 4): CUDA-core kernels (csrc/conv_small.cu) -----------------------------------
+def conv3x3_c4in(x4, w, *, bias=None, out=None):
+    B, H, W, _ = x4.shape
+    Cc = w.shape[3]
+    out = torch.empty((B, H, W, Cc), device=x4.device, dtype=BF16) if out is None else out
+    _lib.check(_lib.lib().sdb_conv3x3_c4in_fwd(x4.data_ptr(), w.data_ptr(), _lib.ptr(bias), out.data_ptr(), B, H, W, Cc,
+                                               _lib.stream_ptr()), "sdb_conv3x3_c4in_fwd")
+    return out
+
+
+def conv3x3_c4out(x, w, *, bias=None, out=None):
+    B, H, W, Cc = x.shape
+    out = torch.empty((B, H, W, 4), device=x.device, dtype=BF16) if out is None else out
+    _lib.check(_lib.lib().sdb_conv3x3_c4out_fwd(x.data_ptr(), w.data_ptr(), _lib.ptr(bias), out.data_ptr(), B, H, W, Cc,
+                                                _lib.stream_ptr()), "sdb_conv3x3_c4out_fwd")
+    return out
+
+
+def conv3x3_c4out_dgrad(dy4, w, *, out=None):
+    B, H, W, _ = dy4.shape
+    Cc = w.shape[2]
+    out = torch.empty((B, H, W, Cc), device=dy4.device, dtype=BF16) if out is None else out
+    _lib.check(_lib.lib().sdb_conv3x3_c4out_dgrad(dy4.data_ptr(), w.data_ptr(), out.data_ptr(), B, H, W, Cc,
+                                                  _lib.stream_ptr()), "sdb_conv3x3_c4out_dgrad")
+    return out
+
+
+def conv3x3_c4_wgrad(x, dy, *, out):
+    """dw HWIO fp32 for conv_in (x has 4 channels) or conv_out (dy has 4 channels)."""
+    B, H, W, cin = x.shape
+    c4_is_input = cin == 4
+    wide, c4 = (dy, x) if c4_is_input else (x, dy)
+    _lib.check(_lib.lib().sdb_conv3x3_c4_wgrad(wide.data_ptr(), c4.data_ptr(), out.data_ptr(), B, H, W, wide.shape[3],
+                                               int(c4_is_input), _lib.stream_ptr()), "sdb_conv3x3_c4_wgrad")
+    return out
+
+
 # ---- 3x3 stride-2 convolution (FlaxDownsample2D): the input is read through four parity sub-grids -----------------
 def _parity_views(x: torch.Tensor):
     """x NHWC [B,H,W,C] (H, W even) -> 4 views x[:, ph::2, pw::2, :], index ph*2+pw."""

@@ -203,7 +203,8 @@ class FlaxDDPMScheduler:
     def step(self, state: DDPMSchedulerState, model_output, timestep: int, sample, key=None, return_dict: bool = True
              ) -> Union[FlaxDDPMSchedulerOutput, Tuple]:
         """Reverse-diffusion step (scheduling_ddpm_flax.py:196-279). `key`: None (seed 0), an int seed or a
-        torch.Generator for the N(0,1) draw (jax.random keys do not exist here)."""
+        torch.Generator for the N(0,1) draw (jax.random keys do not exist here); a float32 tensor of the sample's
+        shape is used AS the draw (parity tests inject the reference's noise that way)."""
         t = int(timestep)
         ptype = self.config.prediction_type
         if ptype not in ("epsilon", "sample", "v_prediction"):
@@ -223,11 +224,14 @@ class FlaxDDPMScheduler:
         noise = None
         sigma = 0.0
         if t > 0:
-            gen = key
-            if not isinstance(gen, torch.Generator):
-                gen = torch.Generator(device=sample.device)
-                gen.manual_seed(0 if key is None else int(key))
-            noise = torch.randn(model_output.shape, generator=gen, device=sample.device, dtype=torch.float32)
+            if isinstance(key, torch.Tensor) and key.shape == model_output.shape:
+                noise = key.to(device=sample.device, dtype=torch.float32).contiguous()
+            else:
+                gen = key
+                if not isinstance(gen, torch.Generator):
+                    gen = torch.Generator(device=sample.device)
+                    gen.manual_seed(0 if key is None else int(key))
+                noise = torch.randn(model_output.shape, generator=gen, device=sample.device, dtype=torch.float32)
             sigma = float(np.sqrt(self._get_variance(state, t)))
         prev = torch.empty_like(sample)
         _lib.check(_lib.lib().sdb_ddpm_step(model_output.data_ptr(), sample.data_ptr(), _lib.ptr(noise), prev.data_ptr(),

@@ -260,9 +260,15 @@ class Graph:
         w = self.W[name + "/kernel"]
         cin, cout = w.shape[2], w.shape[3]
         x4 = x.v.view(B, H, W, cin)
-        small = cin < 16 or cout < 16  # conv_in / conv_out: CUDA-core kernel
+        small = cin < 16 or cout < 16  # conv_in / conv_out: CUDA-core kernels
         impl = "simt" if small else "tc"
-        if stride == 1:
+        c4 = stride == 1 and temb is None and res is None and ((cin == 4 and cout % 8 == 0 and 8 <= cout <= 904) or
+                                                                (cout == 4 and cin % 8 == 0 and 8 <= cin <= 904))
+        if c4:
+            fn = ops.conv3x3_c4in if cin == 4 else ops.conv3x3_c4out
+            y4 = fn(x4, w, bias=self.P[name + "/bias"])
+            geom = (B, H, W)
+        elif stride == 1:
             y4 = ops.conv3x3(x4, w, bias=self.P[name + "/bias"], temb=None if temb is None else temb.v,
                              residual=None if res is None else res.v.view(B, H, W, cout), impl=impl)
             geom = (B, H, W)
@@ -280,7 +286,11 @@ class Graph:
                 self._acc(temb, dt)
             else:
                 ops.colsum(dy, self.G[name + "/bias"])
-            if stride == 1:
+            if c4:
+                ops.conv3x3_c4_wgrad(x4, dy4, out=self.G[name + "/kernel"])
+                if x.rg:
+                    self._acc(x, ops.conv3x3_c4out_dgrad(dy4, w).view(-1, cin))
+            elif stride == 1:
                 ops.conv3x3_wgrad(x4, dy4, out=self.G[name + "/kernel"], impl=impl)
                 if x.rg:
                     if x.g is None or small:
