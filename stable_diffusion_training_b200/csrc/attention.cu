@@ -29,7 +29,6 @@
 namespace {
 
 constexpr uint32_t kAtom128 = 128 * 128;  // bytes of a [128 rows x 64 bf16] swizzle atom column
-constexpr int kThreads = 192;
 
 __device__ __forceinline__ float u2f(uint32_t v) { return __uint_as_float(v); }
 
@@ -52,78 +51,97 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, uint32_t atom_by
 }
 
 // =============================================== forward ===============================================
+// 320 threads: warps 0-7 = softmax (two warps per TMEM lane quarter: warp w and w+4 own the same 32 query rows and
+// split the 128 keys of a block in halves), warp 8 = tcgen05.mma issuer + TMEM owner, warp 9 = TMA producer.
+// S is double-buffered in TMEM and P in shared memory, so QK^T of block j+1 and PV of block j-1 run on the tensor pipe
+// while the softmax warps (the MUFU-bound resource: 128x128 exp2 per block) work on block j.
+constexpr int kFwdThreads = 320;
+constexpr int kMaxBiasBlocks = 16;  // per-key bias (cross-attention quirk / masks given by the caller): Skv <= 2048
+
 struct FwdParams {
   CUtensorMap mapQ, mapK, mapV;
   __nv_bfloat16* o;
   long long ldo;
   float* lse2;
   const float* kbias2;
-  int B, H, Sq, Skv, d, dpad, atoms, stages, nkb;
+  int B, H, Sq, Skv, d, dpad, atoms, kstages, vstages, nkb;
   float scale2;
-  uint32_t tmem_cols;
 };
 
-__global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_constant__ FwdParams p) {
+__global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_constant__ FwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
   const uint32_t tile_bytes = (uint32_t)p.atoms * kAtom128;
   uint8_t* sQ = smem;
   uint8_t* sK = sQ + tile_bytes;
-  uint8_t* sV = sK + (size_t)p.stages * tile_bytes;
-  uint8_t* sP = sV + (size_t)p.stages * tile_bytes;
-  float* sKb = reinterpret_cast<float*>(sP + 2 * kAtom128);
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sKb + 128);
+  uint8_t* sV = sK + (size_t)p.kstages * tile_bytes;
+  uint8_t* sP = sV + (size_t)p.vstages * tile_bytes;             // [2][2 atoms]
+  float* sX = reinterpret_cast<float*>(sP + 4 * kAtom128);       // [2 buf][2 half][128] row-max exchange
+  float* sL = sX + 512;                                          // [2 half][128] row-sum exchange
+  float* sKb = sL + 256;                                         // [nkb*128] per-key bias (only when kbias2 != null)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKb + (p.kbias2 ? p.nkb * 128 : 0));
   uint64_t* barQ = bars;
-  uint64_t* kv_full = bars + 1;
-  uint64_t* kv_empty = bars + 3;
-  uint64_t* bar_S = bars + 5;
-  uint64_t* bar_P = bars + 6;
-  uint64_t* bar_PV = bars + 7;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* k_full = bars + 1;
+  uint64_t* k_empty = bars + 3;
+  uint64_t* v_full = bars + 5;
+  uint64_t* v_empty = bars + 7;
+  uint64_t* bar_S = bars + 9;
+  uint64_t* bar_P = bars + 11;
+  uint64_t* bar_PV = bars + 13;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
 
-  if (warp == 5 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     ptx::tma_prefetch_desc(&p.mapQ);
     ptx::tma_prefetch_desc(&p.mapK);
     ptx::tma_prefetch_desc(&p.mapV);
     ptx::mbar_init(barQ, 1);
     for (int s = 0; s < 2; ++s) {
-      ptx::mbar_init(&kv_full[s], 1);
-      ptx::mbar_init(&kv_empty[s], 1);
+      ptx::mbar_init(&k_full[s], 1);
+      ptx::mbar_init(&k_empty[s], 1);
+      ptx::mbar_init(&v_full[s], 1);
+      ptx::mbar_init(&v_empty[s], 1);
+      ptx::mbar_init(&bar_S[s], 1);
+      ptx::mbar_init(&bar_P[s], 256);
     }
-    ptx::mbar_init(bar_S, 1);
-    ptx::mbar_init(bar_P, 128);
     ptx::mbar_init(bar_PV, 1);
     ptx::fence_barrier_init();
   }
-  if (warp == 4) {
-    ptx::tmem_alloc(tmem_ptr_smem, p.tmem_cols);
+  if (warp == 8) {
+    ptx::tmem_alloc(tmem_ptr_smem, 512);
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
-  const uint32_t tS = tmem_base;         // 128 columns
-  const uint32_t tO = tmem_base + 128u;  // dpad columns
+  const uint32_t tS = tmem_base;         // 2 x 128 columns
+  const uint32_t tO = tmem_base + 256u;  // dpad columns
 
-  if (warp == 5) {
+  if (warp == 9) {
     // ===================== TMA producer =====================
     if (lane == 0) {
       ptx::mbar_expect_tx(barQ, tile_bytes);
       tma_tile(sQ, &p.mapQ, barQ, p.atoms, kAtom128, q0, h, b);
+      auto load_k = [&](int j) {
+        const int s = j % p.kstages, n = j / p.kstages;
+        ptx::mbar_wait(&k_empty[s], (uint32_t)((n & 1) ^ 1));
+        ptx::mbar_expect_tx(&k_full[s], tile_bytes);
+        tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &k_full[s], p.atoms, kAtom128, j * 128, h, b);
+      };
+      load_k(0);
       for (int j = 0; j < p.nkb; ++j) {
-        const int s = j % p.stages, n = j / p.stages;
-        ptx::mbar_wait(&kv_empty[s], (uint32_t)((n & 1) ^ 1));
-        ptx::mbar_expect_tx(&kv_full[s], 2 * tile_bytes);
-        tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &kv_full[s], p.atoms, kAtom128, j * 128, h, b);
-        tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &kv_full[s], p.atoms, kAtom128, j * 128, h, b);
+        if (j + 1 < p.nkb) load_k(j + 1);  // K runs one block ahead of V: S(j+1) is issued before PV(j)
+        const int s = j % p.vstages, n = j / p.vstages;
+        ptx::mbar_wait(&v_empty[s], (uint32_t)((n & 1) ^ 1));
+        ptx::mbar_expect_tx(&v_full[s], tile_bytes);
+        tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &v_full[s], p.atoms, kAtom128, j * 128, h, b);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     // ===================== MMA issuer =====================
     if (lane == 0) {
       const uint32_t idescS = ptx::umma_idesc_bf16(128, 0, 0);
@@ -131,70 +149,87 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
       const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
       const int ksteps = p.dpad / 16;
       auto issue_S = [&](int j) {
-        const int s = j % p.stages, n = j / p.stages;
-        ptx::mbar_wait(&kv_full[s], (uint32_t)(n & 1));
+        const int s = j % p.kstages, n = j / p.kstages;
+        ptx::mbar_wait(&k_full[s], (uint32_t)(n & 1));
         ptx::tc_fence_after();
         const uint32_t aK = ptx::smem_u32(sK + (size_t)s * tile_bytes);
+        const uint32_t t = tS + (uint32_t)(j & 1) * 128u;
         for (int k = 0; k < ksteps; ++k)
-          ptx::umma_bf16(tS, desc_kmajor(aQ, kAtom128, k), desc_kmajor(aK, kAtom128, k), idescS, k > 0 ? 1u : 0u);
-        ptx::umma_commit(bar_S);
+          ptx::umma_bf16(t, desc_kmajor(aQ, kAtom128, k), desc_kmajor(aK, kAtom128, k), idescS, k > 0 ? 1u : 0u);
+        ptx::umma_commit(&k_empty[s]);
+        ptx::umma_commit(&bar_S[j & 1]);
       };
       ptx::mbar_wait(barQ, 0);
       issue_S(0);
       for (int j = 0; j < p.nkb; ++j) {
-        const int s = j % p.stages;
-        ptx::mbar_wait(bar_P, (uint32_t)(j & 1));
+        // S buffer (j+1)&1 was last read by softmax(j-1), whose completion (bar_P) was observed in iteration j-1
+        if (j + 1 < p.nkb) issue_S(j + 1);
+        ptx::mbar_wait(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
+        const int s = j % p.vstages, n = j / p.vstages;
+        ptx::mbar_wait(&v_full[s], (uint32_t)(n & 1));
         ptx::tc_fence_after();
         const uint32_t aV = ptx::smem_u32(sV + (size_t)s * tile_bytes);
+        const uint32_t aPj = aP + (uint32_t)(j & 1) * 2u * kAtom128;
 #pragma unroll
         for (int k = 0; k < 8; ++k)
-          ptx::umma_bf16(tO, desc_kmajor(aP, kAtom128, k), desc_mnmajor(aV, kAtom128, k), idescO,
+          ptx::umma_bf16(tO, desc_kmajor(aPj, kAtom128, k), desc_mnmajor(aV, kAtom128, k), idescO,
                          (j > 0 || k > 0) ? 1u : 0u);
-        ptx::umma_commit(&kv_empty[s]);
+        ptx::umma_commit(&v_empty[s]);
         ptx::umma_commit(bar_PV);
-        if (j + 1 < p.nkb) issue_S(j + 1);
       }
     }
   } else {
-    // ===================== softmax / epilogue: thread = query row =====================
-    const int row = threadIdx.x;
-    const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+    // ===================== softmax / epilogue: thread = (query row, key half) =====================
+    const int q4 = warp & 3, half = warp >> 2;
+    const int row = q4 * 32 + lane;
+    const uint32_t lane_base = ((uint32_t)(q4 * 32)) << 16;
+    if (p.kbias2 != nullptr) {
+      for (int i = threadIdx.x; i < p.nkb * 128; i += 256) sKb[i] = (i < p.Skv) ? p.kbias2[i] : -INFINITY;
+      ptx::named_bar_sync(1, 256);
+    }
     float m_used = -INFINITY, l = 0.f;
     for (int j = 0; j < p.nkb; ++j) {
-      ptx::mbar_wait(bar_S, (uint32_t)(j & 1));
+      ptx::mbar_wait(&bar_S[j & 1], (uint32_t)((j >> 1) & 1));
       ptx::tc_fence_after();
-      const bool use_kb = (p.kbias2 != nullptr) || (j * 128 + 128 > p.Skv);
-      if (use_kb) {
-        const int key = j * 128 + row;
-        sKb[row] = (key < p.Skv) ? (p.kbias2 ? p.kbias2[key] : 0.f) : -INFINITY;
-        ptx::named_bar_sync(1, 128);
-      }
-      // pass 1: row max of the scaled, biased scores (log2 domain)
+      const uint32_t tSj = tS + (uint32_t)(j & 1) * 128u + lane_base + (uint32_t)half * 64u;
+      const int key0 = j * 128 + half * 64;
+      // element modes: 0 plain, 1 tail mask computed inline, 2 per-key bias from shared memory
+      const int emode = (p.kbias2 != nullptr) ? 2 : ((j * 128 + 128 > p.Skv) ? 1 : 0);
+      const float* kb = sKb + key0;
+      // pass 1: row max of the scaled, biased scores (log2 domain) over this thread's 64 keys
       float mx = -INFINITY;
 #pragma unroll 1
-      for (int cc = 0; cc < 4; ++cc) {
+      for (int cc = 0; cc < 2; ++cc) {
         uint32_t v[32];
-        ptx::tmem_ld_32x32(tS + lane_base + cc * 32, v);
+        ptx::tmem_ld_32x32(tSj + cc * 32, v);
         ptx::tmem_ld_wait();
-        if (use_kb) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(u2f(v[i]), p.scale2, sKb[cc * 32 + i]));
-        } else {
+        if (emode == 0) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) mx = fmaxf(mx, u2f(v[i]) * p.scale2);
+        } else if (emode == 1) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            mx = fmaxf(mx, (key0 + cc * 32 + i < p.Skv) ? u2f(v[i]) * p.scale2 : -INFINITY);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(u2f(v[i]), p.scale2, kb[cc * 32 + i]));
         }
       }
+      float* xbuf = sX + (j & 1) * 256;
+      xbuf[half * 128 + row] = mx;
+      ptx::named_bar_sync(1, 256);
+      mx = fmaxf(mx, xbuf[(half ^ 1) * 128 + row]);
       if (j == 0) {
         m_used = mx;
       } else {
-        ptx::mbar_wait(bar_PV, (uint32_t)((j - 1) & 1));  // O complete, P buffer free
+        ptx::mbar_wait(bar_PV, (uint32_t)((j - 1) & 1));  // O holds blocks 0..j-1; P buffer j&1 is free again
         ptx::tc_fence_after();
         const bool need = mx > m_used + 8.0f;
         if (__any_sync(0xffffffffu, need)) {
           const float alpha = need ? ptx::ex2_approx(m_used - mx) : 1.0f;
           if (need) m_used = mx;
           l *= alpha;
-          for (int c0 = 0; c0 < p.dpad; c0 += 16) {
+          for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {  // the two warps of a row interleave 16-column chunks
             uint32_t v[16];
             ptx::tmem_ld_32x16(tO + lane_base + c0, v);
             ptx::tmem_ld_wait();
@@ -205,21 +240,25 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
           ptx::tmem_st_wait();
         }
       }
-      // pass 2: P = exp2(s - m), bf16, into the swizzled A-operand tile
+      // pass 2: P = exp2(s - m), bf16, into the swizzled A-operand tile (atom = key half)
+      uint8_t* atom = sP + (size_t)(j & 1) * 2 * kAtom128 + (size_t)half * kAtom128;
 #pragma unroll 1
-      for (int cc = 0; cc < 4; ++cc) {
+      for (int cc = 0; cc < 2; ++cc) {
         uint32_t v[32];
-        ptx::tmem_ld_32x32(tS + lane_base + cc * 32, v);
+        ptx::tmem_ld_32x32(tSj + cc * 32, v);
         ptx::tmem_ld_wait();
         float pv[32];
-        if (use_kb) {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) pv[i] = ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, sKb[cc * 32 + i] - m_used));
-        } else {
+        if (emode == 0) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) pv[i] = ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, -m_used));
+        } else if (emode == 1) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            pv[i] = (key0 + cc * 32 + i < p.Skv) ? ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, -m_used)) : 0.f;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; ++i) pv[i] = ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, kb[cc * 32 + i] - m_used));
         }
-        uint8_t* atom = sP + (cc >> 1) * kAtom128;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint4 o;
@@ -227,23 +266,26 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
           o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
           o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
           o.w = sdb::pack_bf16x2(pv[c * 8 + 6], pv[c * 8 + 7]);
-          st_swz(atom, row, (cc & 1) * 4 + c, o);
+          st_swz(atom, row, cc * 4 + c, o);
         }
 #pragma unroll
         for (int i = 0; i < 32; ++i) l += pv[i];
       }
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(bar_P);
+      ptx::mbar_arrive(&bar_P[j & 1]);
     }
     // ---- epilogue: O / l -> global, lse ----
+    sL[half * 128 + row] = l;
+    ptx::named_bar_sync(1, 256);
+    l += sL[(half ^ 1) * 128 + row];
     ptx::mbar_wait(bar_PV, (uint32_t)((p.nkb - 1) & 1));
     ptx::tc_fence_after();
     const int q = q0 + row;
     const bool valid = q < p.Sq;
     const float inv_l = 1.0f / l;
     __nv_bfloat16* orow = p.o + ((long long)b * p.Sq + q) * p.ldo + (long long)h * p.d;
-    for (int c0 = 0; c0 < p.dpad; c0 += 16) {
+    for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {
       uint32_t v[16];
       ptx::tmem_ld_32x16(tO + lane_base + c0, v);
       ptx::tmem_ld_wait();
@@ -261,18 +303,26 @@ __global__ void __launch_bounds__(kThreads, 1) attn_fwd_kernel(const __grid_cons
         }
       }
     }
-    if (valid) p.lse2[((long long)b * p.H + h) * p.Sq + q] = m_used + log2f(l);
+    if (valid && half == 0) p.lse2[((long long)b * p.H + h) * p.Sq + q] = m_used + log2f(l);
   }
 
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, p.tmem_cols);
+    ptx::tmem_dealloc(tmem_base, 512);
   }
 }
 
 // =============================================== backward ===============================================
+// 320 threads: warps 0-7 = compute (warp w and w+4 own the same 32 rows and split the columns of a block in halves; no
+// row reductions are needed in backward because lse and D are inputs), warp 8 = tcgen05.mma issuer + TMEM owner,
+// warp 9 = TMA producer. With nbuf = 2 (head dim <= 128) S / dP are double-buffered in TMEM and P^T / dS^T in shared
+// memory, so the tensor pipe computes block i+1's scores and block i-1's accumulations while the compute warps run
+// the exp2 / dS arithmetic of block i.
+constexpr int kBwdThreads = 320;
+constexpr int kBwdMaxStages = 4;
+
 struct BwdParams {
   CUtensorMap mapR1, mapR2, mapC1, mapC2;
   const float* lse2;
@@ -283,11 +333,11 @@ struct BwdParams {
   __nv_bfloat16* out2;
   long long ld2;
   int mode;  // 0: rows = keys (out1 = dK, out2 = dV); 1: rows = queries (out1 = dQ)
-  int B, H, Sq, Skv, Srow, Scol, d, dpad, atoms, bc, stages, ncb;
+  int B, H, Sq, Skv, Srow, Scol, d, dpad, atoms, bc, stages, ncb, nbuf;
   float scale2, scale;
 };
 
-__global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_constant__ BwdParams p) {
+__global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_constant__ BwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -299,38 +349,40 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
   uint8_t* sR2 = sR1 + rtile;
   uint8_t* sC1 = sR2 + rtile;
   uint8_t* sC2 = sC1 + (size_t)p.stages * ctile;
-  uint8_t* sPT = sC2 + (size_t)p.stages * ctile;
-  uint8_t* sDS = sPT + ptile;
-  float* sColA = reinterpret_cast<float*>(sDS + ptile);  // [2][128]
-  float* sColB = sColA + 256;                            // [2][128]
+  uint8_t* sPT = sC2 + (size_t)p.stages * ctile;                // [nbuf]
+  uint8_t* sDS = sPT + (size_t)p.nbuf * ptile;                  // [nbuf]
+  float* sColA = reinterpret_cast<float*>(sDS + (size_t)p.nbuf * ptile);  // [2][128]
+  float* sColB = sColA + 256;                                             // [2][128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sColB + 256);
   uint64_t* barR = bars;
-  uint64_t* c_full = bars + 1;
-  uint64_t* c_empty = bars + 3;
-  uint64_t* bar_SdP = bars + 5;
-  uint64_t* bar_PdS = bars + 6;
-  uint64_t* bar_acc = bars + 7;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* c_full = bars + 1;                     // [kBwdMaxStages]
+  uint64_t* c_empty = c_full + kBwdMaxStages;      // [kBwdMaxStages]
+  uint64_t* bar_SdP = c_empty + kBwdMaxStages;     // [2]
+  uint64_t* bar_PdS = bar_SdP + 2;                 // [2]
+  uint64_t* bar_acc = bar_PdS + 2;                 // [2]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_acc + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
 
-  if (warp == 5 && lane == 0) {
+  if (warp == 9 && lane == 0) {
     ptx::tma_prefetch_desc(&p.mapR1);
     ptx::tma_prefetch_desc(&p.mapR2);
     ptx::tma_prefetch_desc(&p.mapC1);
     ptx::tma_prefetch_desc(&p.mapC2);
     ptx::mbar_init(barR, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < kBwdMaxStages; ++s) {
       ptx::mbar_init(&c_full[s], 1);
       ptx::mbar_init(&c_empty[s], 1);
     }
-    ptx::mbar_init(bar_SdP, 1);
-    ptx::mbar_init(bar_PdS, 128);
-    ptx::mbar_init(bar_acc, 1);
+    for (int s = 0; s < 2; ++s) {
+      ptx::mbar_init(&bar_SdP[s], 1);
+      ptx::mbar_init(&bar_PdS[s], 256);
+      ptx::mbar_init(&bar_acc[s], 1);
+    }
     ptx::fence_barrier_init();
   }
-  if (warp == 4) {
+  if (warp == 8) {
     ptx::tmem_alloc(tmem_ptr_smem, 512);
     ptx::tmem_relinquish();
   }
@@ -338,12 +390,12 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  // [S0 | dP0 | (S1 | dP1) | A1 | A2]
   const uint32_t tS = tmem_base;
-  const uint32_t tdP = tmem_base + (uint32_t)p.bc;
-  const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc;
+  const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc * (uint32_t)p.nbuf;
   const uint32_t tA2 = tA1 + (uint32_t)p.dpad;
 
-  if (warp == 5) {
+  if (warp == 9) {
     if (lane == 0) {
       ptx::mbar_expect_tx(barR, 2 * rtile);
       tma_tile(sR1, &p.mapR1, barR, p.atoms, kAtom128, r0, h, b);
@@ -356,28 +408,41 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
         tma_tile(sC2 + (size_t)s * ctile, &p.mapC2, &c_full[s], p.atoms, catom, i * p.bc, h, b);
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == 8) {
     if (lane == 0) {
       const uint32_t idescS = ptx::umma_idesc_bf16(p.bc, 0, 0);
       const uint32_t idescA = ptx::umma_idesc_bf16(p.dpad, 0, 1);
       const uint32_t aR1 = ptx::smem_u32(sR1), aR2 = ptx::smem_u32(sR2);
-      const uint32_t aPT = ptx::smem_u32(sPT), aDS = ptx::smem_u32(sDS);
       const int ksteps = p.dpad / 16;
-      ptx::mbar_wait(barR, 0);
-      for (int i = 0; i < p.ncb; ++i) {
+      const int k2 = p.bc / 16;
+      auto issue_SdP = [&](int i) {
         const int s = i % p.stages, n = i / p.stages;
         ptx::mbar_wait(&c_full[s], (uint32_t)(n & 1));
         ptx::tc_fence_after();
         const uint32_t aC1 = ptx::smem_u32(sC1 + (size_t)s * ctile);
         const uint32_t aC2 = ptx::smem_u32(sC2 + (size_t)s * ctile);
+        const int buf = i % p.nbuf;
+        const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc;
+        const uint32_t tdPi = tSi + (uint32_t)p.bc;
         for (int k = 0; k < ksteps; ++k)
-          ptx::umma_bf16(tS, desc_kmajor(aR1, kAtom128, k), desc_kmajor(aC1, catom, k), idescS, k > 0 ? 1u : 0u);
+          ptx::umma_bf16(tSi, desc_kmajor(aR1, kAtom128, k), desc_kmajor(aC1, catom, k), idescS, k > 0 ? 1u : 0u);
         for (int k = 0; k < ksteps; ++k)
-          ptx::umma_bf16(tdP, desc_kmajor(aR2, kAtom128, k), desc_kmajor(aC2, catom, k), idescS, k > 0 ? 1u : 0u);
-        ptx::umma_commit(bar_SdP);
-        ptx::mbar_wait(bar_PdS, (uint32_t)(i & 1));
+          ptx::umma_bf16(tdPi, desc_kmajor(aR2, kAtom128, k), desc_kmajor(aC2, catom, k), idescS, k > 0 ? 1u : 0u);
+        ptx::umma_commit(&bar_SdP[buf]);
+      };
+      ptx::mbar_wait(barR, 0);
+      issue_SdP(0);
+      for (int i = 0; i < p.ncb; ++i) {
+        // double-buffered: S/dP buffer (i+1)&1 was last read by compute(i-1), observed through bar_PdS in iteration i-1
+        if (p.nbuf == 2 && i + 1 < p.ncb) issue_SdP(i + 1);
+        const int s = i % p.stages;
+        const int buf = i % p.nbuf;
+        ptx::mbar_wait(&bar_PdS[buf], (uint32_t)((i / p.nbuf) & 1));
         ptx::tc_fence_after();
-        const int k2 = p.bc / 16;
+        const uint32_t aC1 = ptx::smem_u32(sC1 + (size_t)s * ctile);
+        const uint32_t aC2 = ptx::smem_u32(sC2 + (size_t)s * ctile);
+        const uint32_t aDS = ptx::smem_u32(sDS + (size_t)buf * ptile);
+        const uint32_t aPT = ptx::smem_u32(sPT + (size_t)buf * ptile);
         for (int k = 0; k < k2; ++k)
           ptx::umma_bf16(tA1, desc_kmajor(aDS, kAtom128, k), desc_mnmajor(aC1, catom, k), idescA,
                          (i > 0 || k > 0) ? 1u : 0u);
@@ -387,13 +452,15 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
                            (i > 0 || k > 0) ? 1u : 0u);
         }
         ptx::umma_commit(&c_empty[s]);
-        ptx::umma_commit(bar_acc);
+        ptx::umma_commit(&bar_acc[buf]);
+        if (p.nbuf == 1 && i + 1 < p.ncb) issue_SdP(i + 1);
       }
     }
   } else {
-    // ===================== compute threads: thread = row =====================
-    const int row = threadIdx.x;
-    const uint32_t lane_base = ((uint32_t)(warp * 32)) << 16;
+    // ===================== compute threads: thread = (row, column half) =====================
+    const int q4 = warp & 3, half = warp >> 2;
+    const int row = q4 * 32 + lane;
+    const uint32_t lane_base = ((uint32_t)(q4 * 32)) << 16;
     const int r = r0 + row;
     const long long bh = (long long)b * p.H + h;
     float rowA, rowD = 0.f;  // mode 0: rowA = key bias; mode 1: rowA = -lse2[q], rowD = D[q]
@@ -403,40 +470,59 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
       rowA = (r < p.Sq) ? -p.lse2[bh * p.Sq + r] : -INFINITY;
       rowD = (r < p.Sq) ? p.dvec[bh * p.Sq + r] : 0.f;
     }
+    // per-column metadata of block i, fetched one block ahead into registers by the first bc threads
+    float nA = 0.f, nB = 0.f;
+    auto fetch_cols = [&](int i) {
+      if ((int)threadIdx.x < p.bc && i < p.ncb) {
+        const int c = i * p.bc + (int)threadIdx.x;
+        if (p.mode == 0) {
+          nA = (c < p.Sq) ? -p.lse2[bh * p.Sq + c] : -INFINITY;
+          nB = (c < p.Sq) ? p.dvec[bh * p.Sq + c] : 0.f;
+        } else {
+          nA = (c < p.Skv) ? (p.kbias2 ? p.kbias2[c] : 0.f) : -INFINITY;
+          nB = 0.f;
+        }
+      }
+    };
+    fetch_cols(0);
+    const int hc = p.bc / 2;        // columns per thread per block
+    const int ncc = hc / 32;        // 32-column chunks per thread
     for (int i = 0; i < p.ncb; ++i) {
       float* cA = sColA + (i & 1) * 128;
       float* cB = sColB + (i & 1) * 128;
-      if (row < p.bc) {
-        const int c = i * p.bc + row;
-        if (p.mode == 0) {
-          cA[row] = (c < p.Sq) ? -p.lse2[bh * p.Sq + c] : -INFINITY;
-          cB[row] = (c < p.Sq) ? p.dvec[bh * p.Sq + c] : 0.f;
-        } else {
-          cA[row] = (c < p.Skv) ? (p.kbias2 ? p.kbias2[c] : 0.f) : -INFINITY;
-          cB[row] = 0.f;
-        }
+      if ((int)threadIdx.x < p.bc) {
+        cA[threadIdx.x] = nA;
+        cB[threadIdx.x] = nB;
       }
-      ptx::named_bar_sync(1, 128);
-      ptx::mbar_wait(bar_SdP, (uint32_t)(i & 1));
+      ptx::named_bar_sync(1, 256);
+      fetch_cols(i + 1);
+      const int buf = i % p.nbuf;
+      ptx::mbar_wait(&bar_SdP[buf], (uint32_t)((i / p.nbuf) & 1));
       ptx::tc_fence_after();
-      if (i > 0) ptx::mbar_wait(bar_acc, (uint32_t)((i - 1) & 1));  // P^T / dS^T tiles free again
+      if (i >= p.nbuf) ptx::mbar_wait(&bar_acc[buf], (uint32_t)(((i - p.nbuf) / p.nbuf) & 1));  // P^T/dS^T[buf] free
+      const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + lane_base;
+      const uint32_t tdPi = tSi + (uint32_t)p.bc;
+      uint8_t* tileP = sPT + (size_t)buf * ptile;
+      uint8_t* tileD = sDS + (size_t)buf * ptile;
 #pragma unroll 1
-      for (int cc = 0; cc < p.bc / 32; ++cc) {
+      for (int cc = 0; cc < ncc; ++cc) {
+        const int col0 = half * hc + cc * 32;
         uint32_t sv[32], dv[32];
-        ptx::tmem_ld_32x32(tS + lane_base + cc * 32, sv);
-        ptx::tmem_ld_32x32(tdP + lane_base + cc * 32, dv);
+        ptx::tmem_ld_32x32(tSi + col0, sv);
+        ptx::tmem_ld_32x32(tdPi + col0, dv);
         ptx::tmem_ld_wait();
         float pv[32], ds[32];
 #pragma unroll
         for (int k = 0; k < 32; ++k) {
-          const float a = cA[cc * 32 + k] + rowA;  // bias - lse (either order); -inf masks
+          const float a = cA[col0 + k] + rowA;  // bias - lse (either order); -inf masks
           const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, a));
-          const float dd = (p.mode == 0) ? cB[cc * 32 + k] : rowD;
+          const float dd = (p.mode == 0) ? cB[col0 + k] : rowD;
           pv[k] = pk;
           ds[k] = pk * (u2f(dv[k]) - dd) * p.scale;
         }
-        uint8_t* atomP = sPT + (cc >> 1) * kAtom128;
-        uint8_t* atomD = sDS + (cc >> 1) * kAtom128;
+        uint8_t* atomP = tileP + (col0 >> 6) * kAtom128;
+        uint8_t* atomD = tileD + (col0 >> 6) * kAtom128;
+        const int chunk0 = (col0 & 63) >> 3;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
           uint4 o;
@@ -444,30 +530,33 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
           o.y = sdb::pack_bf16x2(ds[c * 8 + 2], ds[c * 8 + 3]);
           o.z = sdb::pack_bf16x2(ds[c * 8 + 4], ds[c * 8 + 5]);
           o.w = sdb::pack_bf16x2(ds[c * 8 + 6], ds[c * 8 + 7]);
-          st_swz(atomD, row, (cc & 1) * 4 + c, o);
+          st_swz(atomD, row, chunk0 + c, o);
           if (p.mode == 0) {
             o.x = sdb::pack_bf16x2(pv[c * 8 + 0], pv[c * 8 + 1]);
             o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
             o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
             o.w = sdb::pack_bf16x2(pv[c * 8 + 6], pv[c * 8 + 7]);
-            st_swz(atomP, row, (cc & 1) * 4 + c, o);
+            st_swz(atomP, row, chunk0 + c, o);
           }
         }
       }
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
-      ptx::mbar_arrive(bar_PdS);
+      ptx::mbar_arrive(&bar_PdS[buf]);
     }
-    // ---- drain the accumulators ----
-    ptx::mbar_wait(bar_acc, (uint32_t)((p.ncb - 1) & 1));
-    ptx::tc_fence_after();
+    // ---- drain the accumulators (commits complete in order: the last one covers all) ----
+    {
+      const int last = p.ncb - 1;
+      ptx::mbar_wait(&bar_acc[last % p.nbuf], (uint32_t)((last / p.nbuf) & 1));
+      ptx::tc_fence_after();
+    }
     const bool valid = r < p.Srow;
     for (int which = 0; which < (p.mode == 0 ? 2 : 1); ++which) {
       const uint32_t tA = which == 0 ? tA1 : tA2;
       __nv_bfloat16* base = which == 0 ? p.out1 : p.out2;
       const long long ld = which == 0 ? p.ld1 : p.ld2;
       __nv_bfloat16* orow = base + ((long long)b * p.Srow + r) * ld + (long long)h * p.d;
-      for (int c0 = 0; c0 < p.dpad; c0 += 16) {
+      for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {
         uint32_t v[16];
         ptx::tmem_ld_32x16(tA + lane_base + c0, v);
         ptx::tmem_ld_wait();
@@ -490,7 +579,7 @@ __global__ void __launch_bounds__(kThreads, 1) attn_bwd_kernel(const __grid_cons
 
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == 8) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 512);
   }
@@ -589,12 +678,18 @@ extern "C" int sdb_attn_fwd(const void* q, long long ldq, const void* k, long lo
   p.atoms = (d + 63) / 64;
   p.nkb = (Skv + 127) / 128;
   p.scale2 = scale * 1.4426950408889634f;
-  p.tmem_cols = (128 + p.dpad <= 256) ? 256 : 512;
+  if (kbias2 != nullptr && p.nkb > kMaxBiasBlocks)
+    return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_fwd: a per-key bias supports Skv <= %d (got %d)",
+                         kMaxBiasBlocks * 128, Skv);
   const size_t tile = (size_t)p.atoms * kAtom128;
-  const size_t fixed = tile + 2 * kAtom128 + 128 * sizeof(float) + 128 /*barriers*/ + 1024 /*align*/;
-  p.stages = (fixed + 4 * tile <= 220 * 1024 && p.nkb > 1) ? 2 : 1;
-  const size_t smem_bytes = fixed + (size_t)p.stages * 2 * tile;
-  if (smem_bytes > 227 * 1024) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_fwd: head dim %d needs too much smem", d);
+  const size_t fixed = tile + 4 * kAtom128 + (512 + 256) * sizeof(float) +
+                       (kbias2 ? (size_t)p.nkb * 128 * sizeof(float) : 0) + 128 /*barriers*/ + 1024 /*align*/;
+  const size_t budget = 227 * 1024;
+  p.kstages = p.vstages = (p.nkb > 1) ? 2 : 1;
+  if (fixed + (size_t)(p.kstages + p.vstages) * tile > budget) p.vstages = 1;
+  if (fixed + (size_t)(p.kstages + p.vstages) * tile > budget) p.kstages = 1;
+  const size_t smem_bytes = fixed + (size_t)(p.kstages + p.vstages) * tile;
+  if (smem_bytes > budget) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_fwd: head dim %d needs too much smem", d);
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
@@ -603,7 +698,7 @@ extern "C" int sdb_attn_fwd(const void* q, long long ldq, const void* k, long lo
   if (attr_err != cudaSuccess)
     return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
   dim3 grid((Sq + 127) / 128, H, B);
-  attn_fwd_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
+  attn_fwd_kernel<<<grid, kFwdThreads, smem_bytes, stream>>>(p);
   SDB_CUDA_LAUNCH_CHECK("sdb_attn_fwd");
   return SDB_OK;
 }
@@ -647,7 +742,8 @@ extern "C" int sdb_attn_bwd(const void* q, long long ldq, const void* k, long lo
     p.B = B; p.H = H; p.Sq = Sq; p.Skv = Skv; p.d = d;
     p.dpad = (d + 15) & ~15;
     p.atoms = (d + 63) / 64;
-    p.bc = (p.dpad > 128) ? 64 : 128;
+    p.bc = 64;
+    p.nbuf = (p.dpad <= 128) ? 2 : 1;
     p.Srow = mode == 0 ? Skv : Sq;
     p.Scol = mode == 0 ? Sq : Skv;
     p.ncb = (p.Scol + p.bc - 1) / p.bc;
@@ -672,13 +768,22 @@ extern "C" int sdb_attn_bwd(const void* q, long long ldq, const void* k, long lo
     const size_t rtile = (size_t)p.atoms * kAtom128;
     const size_t ctile = (size_t)p.atoms * p.bc * 128;
     const size_t ptile = (size_t)(p.bc / 64) * kAtom128;
-    const size_t fixed = 2 * rtile + 2 * ptile + 512 * sizeof(float) + 128 + 1024;
-    p.stages = (fixed + 4 * ctile <= 220 * 1024 && p.ncb > 1) ? 2 : 1;
+    int stages = 1;
+    size_t fixed = 0;
+    for (;;) {
+      fixed = 2 * rtile + 2 * (size_t)p.nbuf * ptile + 512 * sizeof(float) + 256 /*barriers*/ + 1024 /*align*/;
+      stages = (int)((227 * 1024 - (long long)fixed) / (long long)(2 * ctile));
+      if (stages > kBwdMaxStages) stages = kBwdMaxStages;
+      if (stages > p.ncb) stages = p.ncb;
+      // the double-buffered schedule issues S/dP of block i+1 before block i's operands are released: needs 2 stages
+      if (p.nbuf == 2 && p.ncb > 1 && stages < 2) { p.nbuf = 1; continue; }
+      break;
+    }
+    if (stages < 1) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_bwd: head dim %d needs too much smem", d);
+    p.stages = stages;
     const size_t smem_bytes = fixed + (size_t)p.stages * 2 * ctile;
-    if (smem_bytes > 227 * 1024)
-      return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_bwd: head dim %d needs too much smem", d);
     dim3 grid((p.Srow + 127) / 128, H, B);
-    attn_bwd_kernel<<<grid, kThreads, smem_bytes, stream>>>(p);
+    attn_bwd_kernel<<<grid, kBwdThreads, smem_bytes, stream>>>(p);
     SDB_CUDA_LAUNCH_CHECK("sdb_attn_bwd");
   }
   return SDB_OK;

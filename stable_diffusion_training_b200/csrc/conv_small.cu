@@ -72,14 +72,19 @@ c4_to_wide_kernel(const __nv_bfloat16* __restrict__ a4, const __nv_bfloat16* __r
 }
 
 // ---------------------------------------------------------------------------------------------------------------
-// conv_out forward: one warp per pixel, lanes over 8-channel vectors. smem: w[9][C][4] fp32 (HWIO order as is).
+// conv_out forward: one warp per pixel, lanes over 8-channel vectors.
 __global__ void __launch_bounds__(256)
 wide_to_c4_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w, const float* __restrict__ bias,
                   __nv_bfloat16* __restrict__ out, int B, int H, int W, int C) {
-  extern __shared__ float s_w[];  // [9][C][4]
-  for (int i = threadIdx.x; i < 36 * C; i += blockDim.x) s_w[i] = __bfloat162float(w[i]);
-  __syncthreads();
+  // smem weights as [tap][i = channel % 8][v = channel / 8][4]: the lanes of a warp (consecutive v) read consecutive
+  // float4 -> conflict-free LDS.128
+  extern __shared__ float s_w[];
   const int nv = C / 8;
+  for (int i = threadIdx.x; i < 36 * C; i += blockDim.x) {
+    const int j = i & 3, c = (i >> 2) % C, tap = i / (4 * C);
+    s_w[(((tap * 8 + (c & 7)) * nv) + (c >> 3)) * 4 + j] = __bfloat162float(w[i]);
+  }
+  __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long npix = (long long)B * H * W;
   for (long long pix = (long long)blockIdx.x * 8 + warp; pix < npix; pix += (long long)gridDim.x * 8) {
@@ -95,7 +100,7 @@ wide_to_c4_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __re
         unpack8(sdb::ld_u4(row + v * 8), xv);
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const float4 wv = *reinterpret_cast<const float4*>(&s_w[(tap * C + v * 8 + i) * 4]);
+          const float4 wv = *reinterpret_cast<const float4*>(&s_w[((tap * 8 + i) * nv + v) * 4]);
           acc[0] = fmaf(xv[i], wv.x, acc[0]); acc[1] = fmaf(xv[i], wv.y, acc[1]);
           acc[2] = fmaf(xv[i], wv.z, acc[2]); acc[3] = fmaf(xv[i], wv.w, acc[3]);
         }

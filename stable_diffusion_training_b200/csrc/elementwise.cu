@@ -183,18 +183,29 @@ colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long lo
     part[(size_t)blockIdx.x * cols + cc] = t;
   }
 }
-__global__ void colsum_final_kernel(const float* __restrict__ part, int nseg, int bps, int cols,
-                                    float* __restrict__ out_total, __nv_bfloat16* __restrict__ out_seg) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= cols) return;
+// 32 columns per block; 8 row-block slices per column, combined through shared memory (fixed order: deterministic)
+__global__ void __launch_bounds__(256)
+colsum_final_kernel(const float* __restrict__ part, int nseg, int bps, int cols, float* __restrict__ out_total,
+                    __nv_bfloat16* __restrict__ out_seg) {
+  __shared__ float s[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
   float tot = 0.f;
   for (int sgm = 0; sgm < nseg; ++sgm) {
     float t = 0.f;
-    for (int j = 0; j < bps; ++j) t += part[((size_t)sgm * bps + j) * cols + c];
-    if (out_seg != nullptr) out_seg[(size_t)sgm * cols + c] = __float2bfloat16_rn(t);
-    tot += t;
+    if (c < cols)
+      for (int j = ty; j < bps; j += 8) t += part[((size_t)sgm * bps + j) * cols + c];
+    s[ty][tx] = t;
+    __syncthreads();
+    if (ty == 0) {
+#pragma unroll
+      for (int j = 1; j < 8; ++j) t += s[j][tx];
+      if (c < cols && out_seg != nullptr) out_seg[(size_t)sgm * cols + c] = __float2bfloat16_rn(t);
+      tot += t;
+    }
+    __syncthreads();
   }
-  if (out_total != nullptr) out_total[c] = tot;
+  if (ty == 0 && c < cols && out_total != nullptr) out_total[c] = tot;
 }
 
 // any (small) column count, no alignment requirement: one block per column
@@ -332,7 +343,7 @@ extern "C" int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long 
   colsum_partial_kernel<<<dim3(nseg * bps, col_chunks), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld,
                                                                           rows_per_seg, bps, rpb, cols, part);
   SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(partial)");
-  colsum_final_kernel<<<(cols + 255) / 256, 256, 0, stream>>>(part, nseg, bps, cols, out_total,
+  colsum_final_kernel<<<(cols + 31) / 32, 256, 0, stream>>>(part, nseg, bps, cols, out_total,
                                                               reinterpret_cast<__nv_bfloat16*>(out_seg_bf16));
   SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16(final)");
   return SDB_OK;

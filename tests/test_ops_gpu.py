@@ -100,7 +100,8 @@ def _attn_ref(q, k, v, heads, kbias2):
     (1, 2, 128, 128, 64, False), (2, 2, 256, 256, 16, False), (2, 2, 1024, 77, 32, False), (2, 8, 1024, 1024, 40, False),
     (1, 8, 4096, 4096, 40, False), (2, 8, 1024, 77, 80, False), (2, 8, 256, 256, 160, False), (2, 8, 256, 77, 160, False),
     (2, 8, 64, 64, 160, False), (2, 8, 64, 77, 160, True), (2, 5, 576, 576, 64, False), (2, 4, 144, 227, 64, True),
-    (1, 2, 300, 200, 40, True)])
+    (1, 2, 300, 200, 40, True), (1, 2, 300, 1100, 40, False), (1, 1, 130, 2048, 40, True), (1, 2, 1100, 300, 80, False),
+    (1, 3, 200, 1000, 160, False)])
 def test_attention_fwd_bwd(cuda, B, heads, Sq, Skv, d, bias):
     C = heads * d
     # q/k/v as column slices of a fused buffer -> exercises row strides
@@ -150,6 +151,10 @@ def test_data_movement(cuda):
     out = torch.empty(320, device=cuda)
     ops.colsum(big, out)
     assert torch.allclose(out, big.float().sum(0), rtol=1e-4, atol=1e-2)
+    wide = _rand((2048, 10240), cuda, 1.0, 7)  # short and wide: the FF gradient shape
+    outw = torch.empty(10240, device=cuda)
+    ops.colsum(wide, outw)
+    assert torch.allclose(outw, wide.float().sum(0), rtol=1e-4, atol=2e-2)
     seg = torch.empty((5, 320), device=cuda, dtype=torch.bfloat16)
     ops.colsum(big, out, nseg=5, out_seg=seg)
     assert torch.allclose(out, big.float().sum(0), rtol=1e-4, atol=1e-2)
