@@ -50,6 +50,22 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, uint32_t atom_by
   return ptx::umma_desc_sw128(base + (uint32_t)kstep * 2048u, atom_bytes, 1024u);
 }
 
+// Issue `ksteps` K = 16 MMAs from precomputed base descriptors. The smem address field is the low 14 bits of the
+// descriptor (16-byte units), so stepping along K is an integer add: +2 per step inside a 64-column swizzle atom and a
+// jump to the next atom every 4 steps (K-major), or +128 per 16 K-rows (MN-major). Keeping this loop free of divisions
+// and descriptor re-encoding matters: ONE thread issues every MMA of the CTA, and its latency is on the critical path.
+template <bool B_MN>
+__device__ __forceinline__ void mma_ksteps(uint32_t tmem_d, uint64_t dA, uint32_t a_atom16, uint64_t dB, uint32_t b_atom16,
+                                           uint32_t idesc, int ksteps, uint32_t acc_first) {
+  uint32_t offA = 0, offB = 0;
+  for (int k = 0; k < ksteps; ++k) {
+    ptx::umma_bf16(tmem_d, dA + offA, dB + offB, idesc, k > 0 ? 1u : acc_first);
+    const bool wrap = (k & 3) == 3;
+    offA += wrap ? a_atom16 - 6u : 2u;
+    offB += B_MN ? 128u : (wrap ? b_atom16 - 6u : 2u);
+  }
+}
+
 // =============================================== forward ===============================================
 // 320 threads: warps 0-7 = softmax (two warps per TMEM lane quarter: warp w and w+4 own the same 32 query rows and
 // split the 128 keys of a block in halves), warp 8 = tcgen05.mma issuer + TMEM owner, warp 9 = TMA producer.
@@ -146,18 +162,22 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
     if (lane == 0) {
       const uint32_t idescS = ptx::umma_idesc_bf16(128, 0, 0);
       const uint32_t idescO = ptx::umma_idesc_bf16(p.dpad, 0, 1);
-      const uint32_t aQ = ptx::smem_u32(sQ), aP = ptx::smem_u32(sP);
+      const uint64_t dQ = ptx::umma_desc_sw128(ptx::smem_u32(sQ), 0u, 1024u);
+      const uint64_t dK0 = ptx::umma_desc_sw128(ptx::smem_u32(sK), 0u, 1024u);
+      const uint64_t dV0 = ptx::umma_desc_sw128(ptx::smem_u32(sV), kAtom128, 1024u);  // MN-major: LBO = atom stride
+      const uint64_t dP0 = ptx::umma_desc_sw128(ptx::smem_u32(sP), 0u, 1024u);
+      const uint32_t tile16 = tile_bytes >> 4, atom16 = kAtom128 >> 4;
       const int ksteps = p.dpad / 16;
+      int ks = 0, vs = 0;
+      uint32_t kph = 0, vph = 0;
       auto issue_S = [&](int j) {
-        const int s = j % p.kstages, n = j / p.kstages;
-        ptx::mbar_wait(&k_full[s], (uint32_t)(n & 1));
+        ptx::mbar_wait(&k_full[ks], kph);
         ptx::tc_fence_after();
-        const uint32_t aK = ptx::smem_u32(sK + (size_t)s * tile_bytes);
-        const uint32_t t = tS + (uint32_t)(j & 1) * 128u;
-        for (int k = 0; k < ksteps; ++k)
-          ptx::umma_bf16(t, desc_kmajor(aQ, kAtom128, k), desc_kmajor(aK, kAtom128, k), idescS, k > 0 ? 1u : 0u);
-        ptx::umma_commit(&k_empty[s]);
+        mma_ksteps<false>(tS + (uint32_t)(j & 1) * 128u, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS, ksteps,
+                          0u);
+        ptx::umma_commit(&k_empty[ks]);
         ptx::umma_commit(&bar_S[j & 1]);
+        if (++ks == p.kstages) { ks = 0; kph ^= 1u; }
       };
       ptx::mbar_wait(barQ, 0);
       issue_S(0);
@@ -165,17 +185,13 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
         // S buffer (j+1)&1 was last read by softmax(j-1), whose completion (bar_P) was observed in iteration j-1
         if (j + 1 < p.nkb) issue_S(j + 1);
         ptx::mbar_wait(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
-        const int s = j % p.vstages, n = j / p.vstages;
-        ptx::mbar_wait(&v_full[s], (uint32_t)(n & 1));
+        ptx::mbar_wait(&v_full[vs], vph);
         ptx::tc_fence_after();
-        const uint32_t aV = ptx::smem_u32(sV + (size_t)s * tile_bytes);
-        const uint32_t aPj = aP + (uint32_t)(j & 1) * 2u * kAtom128;
-#pragma unroll
-        for (int k = 0; k < 8; ++k)
-          ptx::umma_bf16(tO, desc_kmajor(aPj, kAtom128, k), desc_mnmajor(aV, kAtom128, k), idescO,
-                         (j > 0 || k > 0) ? 1u : 0u);
-        ptx::umma_commit(&v_empty[s]);
+        mma_ksteps<true>(tO, dP0 + (uint32_t)(j & 1) * 2u * atom16, atom16, dV0 + (uint32_t)vs * tile16, 0u, idescO, 8,
+                         j > 0 ? 1u : 0u);
+        ptx::umma_commit(&v_empty[vs]);
         ptx::umma_commit(bar_PV);
+        if (++vs == p.vstages) { vs = 0; vph ^= 1u; }
       }
     }
   } else {
@@ -196,23 +212,27 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       // element modes: 0 plain, 1 tail mask computed inline, 2 per-key bias from shared memory
       const int emode = (p.kbias2 != nullptr) ? 2 : ((j * 128 + 128 > p.Skv) ? 1 : 0);
       const float* kb = sKb + key0;
-      // pass 1: row max of the scaled, biased scores (log2 domain) over this thread's 64 keys
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int cc = 0; cc < 2; ++cc) {
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(tSj + cc * 32, v);
-        ptx::tmem_ld_wait();
-        if (emode == 0) {
+      // pass 1: this thread's 64 scores stay in registers for pass 2; row max in the log2 domain with four
+      // independent max chains (a single chain of 64 dependent FMNMX is pure latency at 2 warps per scheduler)
+      uint32_t sv[64];
+      ptx::tmem_ld_32x32(tSj, *reinterpret_cast<uint32_t(*)[32]>(&sv[0]));
+      ptx::tmem_ld_32x32(tSj + 32, *reinterpret_cast<uint32_t(*)[32]>(&sv[32]));
+      ptx::tmem_ld_wait();
+      float mx;
+      {
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (emode == 0) {  // scale2 > 0: max of the raw scores, scaled once
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, u2f(v[i]) * p.scale2);
+          for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], u2f(sv[i]));
+          mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale2;
         } else if (emode == 1) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            mx = fmaxf(mx, (key0 + cc * 32 + i < p.Skv) ? u2f(v[i]) * p.scale2 : -INFINITY);
+          for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], (key0 + i < p.Skv) ? u2f(sv[i]) : -INFINITY);
+          mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale2;
         } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) mx = fmaxf(mx, fmaf(u2f(v[i]), p.scale2, kb[cc * 32 + i]));
+          for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], fmaf(u2f(sv[i]), p.scale2, kb[i]));
+          mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
         }
       }
       float* xbuf = sX + (j & 1) * 256;
@@ -240,37 +260,28 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
           ptx::tmem_st_wait();
         }
       }
-      // pass 2: P = exp2(s - m), bf16, into the swizzled A-operand tile (atom = key half)
+      // pass 2: P = exp2(s - m), bf16, into the swizzled A-operand tile (atom = key half); four partial row sums
       uint8_t* atom = sP + (size_t)(j & 1) * 2 * kAtom128 + (size_t)half * kAtom128;
-#pragma unroll 1
-      for (int cc = 0; cc < 2; ++cc) {
-        uint32_t v[32];
-        ptx::tmem_ld_32x32(tSj + cc * 32, v);
-        ptx::tmem_ld_wait();
-        float pv[32];
-        if (emode == 0) {
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int i = 0; i < 32; ++i) pv[i] = ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, -m_used));
-        } else if (emode == 1) {
+      for (int c = 0; c < 8; ++c) {
+        float pv[8];
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            pv[i] = (key0 + cc * 32 + i < p.Skv) ? ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, -m_used)) : 0.f;
-        } else {
-#pragma unroll
-          for (int i = 0; i < 32; ++i) pv[i] = ptx::ex2_approx(fmaf(u2f(v[i]), p.scale2, kb[cc * 32 + i] - m_used));
+        for (int e = 0; e < 8; ++e) {
+          const int i = c * 8 + e;
+          if (emode == 0) pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used));
+          else if (emode == 1) pv[e] = (key0 + i < p.Skv) ? ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used)) : 0.f;
+          else pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, kb[i] - m_used));
+          l4[e & 3] += pv[e];
         }
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          uint4 o;
-          o.x = sdb::pack_bf16x2(pv[c * 8 + 0], pv[c * 8 + 1]);
-          o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
-          o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
-          o.w = sdb::pack_bf16x2(pv[c * 8 + 6], pv[c * 8 + 7]);
-          st_swz(atom, row, cc * 4 + c, o);
-        }
-#pragma unroll
-        for (int i = 0; i < 32; ++i) l += pv[i];
+        uint4 o;
+        o.x = sdb::pack_bf16x2(pv[0], pv[1]);
+        o.y = sdb::pack_bf16x2(pv[2], pv[3]);
+        o.z = sdb::pack_bf16x2(pv[4], pv[5]);
+        o.w = sdb::pack_bf16x2(pv[6], pv[7]);
+        st_swz(atom, row, c, o);
       }
+      l += (l4[0] + l4[1]) + (l4[2] + l4[3]);
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(&bar_P[j & 1]);
@@ -337,6 +348,7 @@ struct BwdParams {
   float scale2, scale;
 };
 
+template <int MODE, int NBUF>
 __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_constant__ BwdParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
@@ -350,8 +362,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   uint8_t* sC1 = sR2 + rtile;
   uint8_t* sC2 = sC1 + (size_t)p.stages * ctile;
   uint8_t* sPT = sC2 + (size_t)p.stages * ctile;                // [nbuf]
-  uint8_t* sDS = sPT + (size_t)p.nbuf * ptile;                  // [nbuf]
-  float* sColA = reinterpret_cast<float*>(sDS + (size_t)p.nbuf * ptile);  // [2][128]
+  uint8_t* sDS = sPT + (size_t)NBUF * ptile;                    // [NBUF]
+  float* sColA = reinterpret_cast<float*>(sDS + (size_t)NBUF * ptile);    // [2][128]
   float* sColB = sColA + 256;                                             // [2][128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sColB + 256);
   uint64_t* barR = bars;
@@ -392,7 +404,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   const uint32_t tmem_base = *tmem_ptr_smem;
   // [S0 | dP0 | (S1 | dP1) | A1 | A2]
   const uint32_t tS = tmem_base;
-  const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc * (uint32_t)p.nbuf;
+  const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc * (uint32_t)NBUF;
   const uint32_t tA2 = tA1 + (uint32_t)p.dpad;
 
   if (warp == 9) {
@@ -412,48 +424,46 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     if (lane == 0) {
       const uint32_t idescS = ptx::umma_idesc_bf16(p.bc, 0, 0);
       const uint32_t idescA = ptx::umma_idesc_bf16(p.dpad, 0, 1);
-      const uint32_t aR1 = ptx::smem_u32(sR1), aR2 = ptx::smem_u32(sR2);
+      const uint64_t dR1 = ptx::umma_desc_sw128(ptx::smem_u32(sR1), 0u, 1024u);
+      const uint64_t dR2 = ptx::umma_desc_sw128(ptx::smem_u32(sR2), 0u, 1024u);
+      const uint64_t dC1k = ptx::umma_desc_sw128(ptx::smem_u32(sC1), 0u, 1024u);      // column tiles as K-major B (scores)
+      const uint64_t dC2k = ptx::umma_desc_sw128(ptx::smem_u32(sC2), 0u, 1024u);
+      const uint64_t dC1m = ptx::umma_desc_sw128(ptx::smem_u32(sC1), catom, 1024u);   // ... and as MN-major B (accumulate)
+      const uint64_t dC2m = ptx::umma_desc_sw128(ptx::smem_u32(sC2), catom, 1024u);
+      const uint64_t dDS0 = ptx::umma_desc_sw128(ptx::smem_u32(sDS), 0u, 1024u);
+      const uint64_t dPT0 = ptx::umma_desc_sw128(ptx::smem_u32(sPT), 0u, 1024u);
+      const uint32_t atom16 = kAtom128 >> 4, catom16 = catom >> 4, ctile16 = ctile >> 4, ptile16 = ptile >> 4;
       const int ksteps = p.dpad / 16;
       const int k2 = p.bc / 16;
+      int ss = 0, as = 0;       // stage of the next S/dP issue, of the next accumulate
+      uint32_t sph = 0;
       auto issue_SdP = [&](int i) {
-        const int s = i % p.stages, n = i / p.stages;
-        ptx::mbar_wait(&c_full[s], (uint32_t)(n & 1));
+        ptx::mbar_wait(&c_full[ss], sph);
         ptx::tc_fence_after();
-        const uint32_t aC1 = ptx::smem_u32(sC1 + (size_t)s * ctile);
-        const uint32_t aC2 = ptx::smem_u32(sC2 + (size_t)s * ctile);
-        const int buf = i % p.nbuf;
+        const int buf = i & (NBUF - 1);
         const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc;
-        const uint32_t tdPi = tSi + (uint32_t)p.bc;
-        for (int k = 0; k < ksteps; ++k)
-          ptx::umma_bf16(tSi, desc_kmajor(aR1, kAtom128, k), desc_kmajor(aC1, catom, k), idescS, k > 0 ? 1u : 0u);
-        for (int k = 0; k < ksteps; ++k)
-          ptx::umma_bf16(tdPi, desc_kmajor(aR2, kAtom128, k), desc_kmajor(aC2, catom, k), idescS, k > 0 ? 1u : 0u);
+        mma_ksteps<false>(tSi, dR1, atom16, dC1k + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
+        mma_ksteps<false>(tSi + (uint32_t)p.bc, dR2, atom16, dC2k + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
         ptx::umma_commit(&bar_SdP[buf]);
+        if (++ss == p.stages) { ss = 0; sph ^= 1u; }
       };
       ptx::mbar_wait(barR, 0);
       issue_SdP(0);
       for (int i = 0; i < p.ncb; ++i) {
         // double-buffered: S/dP buffer (i+1)&1 was last read by compute(i-1), observed through bar_PdS in iteration i-1
-        if (p.nbuf == 2 && i + 1 < p.ncb) issue_SdP(i + 1);
-        const int s = i % p.stages;
-        const int buf = i % p.nbuf;
-        ptx::mbar_wait(&bar_PdS[buf], (uint32_t)((i / p.nbuf) & 1));
+        if (NBUF == 2 && i + 1 < p.ncb) issue_SdP(i + 1);
+        const int buf = i & (NBUF - 1);
+        ptx::mbar_wait(&bar_PdS[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
         ptx::tc_fence_after();
-        const uint32_t aC1 = ptx::smem_u32(sC1 + (size_t)s * ctile);
-        const uint32_t aC2 = ptx::smem_u32(sC2 + (size_t)s * ctile);
-        const uint32_t aDS = ptx::smem_u32(sDS + (size_t)buf * ptile);
-        const uint32_t aPT = ptx::smem_u32(sPT + (size_t)buf * ptile);
-        for (int k = 0; k < k2; ++k)
-          ptx::umma_bf16(tA1, desc_kmajor(aDS, kAtom128, k), desc_mnmajor(aC1, catom, k), idescA,
-                         (i > 0 || k > 0) ? 1u : 0u);
-        if (p.mode == 0) {
-          for (int k = 0; k < k2; ++k)
-            ptx::umma_bf16(tA2, desc_kmajor(aPT, kAtom128, k), desc_mnmajor(aC2, catom, k), idescA,
-                           (i > 0 || k > 0) ? 1u : 0u);
-        }
-        ptx::umma_commit(&c_empty[s]);
+        mma_ksteps<true>(tA1, dDS0 + (uint32_t)buf * ptile16, atom16, dC1m + (uint32_t)as * ctile16, 0u, idescA, k2,
+                         i > 0 ? 1u : 0u);
+        if (MODE == 0)
+          mma_ksteps<true>(tA2, dPT0 + (uint32_t)buf * ptile16, atom16, dC2m + (uint32_t)as * ctile16, 0u, idescA, k2,
+                           i > 0 ? 1u : 0u);
+        ptx::umma_commit(&c_empty[as]);
         ptx::umma_commit(&bar_acc[buf]);
-        if (p.nbuf == 1 && i + 1 < p.ncb) issue_SdP(i + 1);
+        if (++as == p.stages) as = 0;
+        if (NBUF == 1 && i + 1 < p.ncb) issue_SdP(i + 1);
       }
     }
   } else {
@@ -463,24 +473,24 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     const uint32_t lane_base = ((uint32_t)(q4 * 32)) << 16;
     const int r = r0 + row;
     const long long bh = (long long)b * p.H + h;
-    float rowA, rowD = 0.f;  // mode 0: rowA = key bias; mode 1: rowA = -lse2[q], rowD = D[q]
-    if (p.mode == 0) {
+    float rowA, rowD = 0.f;  // MODE 0: rowA = key bias; MODE 1: rowA = -lse2[q], rowD = D[q]
+    if (MODE == 0) {
       rowA = (r < p.Skv) ? (p.kbias2 ? p.kbias2[r] : 0.f) : -INFINITY;
     } else {
       rowA = (r < p.Sq) ? -p.lse2[bh * p.Sq + r] : -INFINITY;
       rowD = (r < p.Sq) ? p.dvec[bh * p.Sq + r] : 0.f;
     }
-    // per-column metadata of block i, fetched one block ahead into registers by the first bc threads
+    // per-column metadata of block i, fetched one block ahead into registers by the first bc threads.
+    // MODE 1 needs it only when a key bias is given or the block is cut by Skv (plain blocks skip the LDS entirely).
     float nA = 0.f, nB = 0.f;
     auto fetch_cols = [&](int i) {
       if ((int)threadIdx.x < p.bc && i < p.ncb) {
         const int c = i * p.bc + (int)threadIdx.x;
-        if (p.mode == 0) {
+        if (MODE == 0) {
           nA = (c < p.Sq) ? -p.lse2[bh * p.Sq + c] : -INFINITY;
           nB = (c < p.Sq) ? p.dvec[bh * p.Sq + c] : 0.f;
         } else {
           nA = (c < p.Skv) ? (p.kbias2 ? p.kbias2[c] : 0.f) : -INFINITY;
-          nB = 0.f;
         }
       }
     };
@@ -490,16 +500,17 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     for (int i = 0; i < p.ncb; ++i) {
       float* cA = sColA + (i & 1) * 128;
       float* cB = sColB + (i & 1) * 128;
+      const bool col_meta = (MODE == 0) || (p.kbias2 != nullptr) || ((i + 1) * p.bc > p.Skv);
       if ((int)threadIdx.x < p.bc) {
         cA[threadIdx.x] = nA;
-        cB[threadIdx.x] = nB;
+        if (MODE == 0) cB[threadIdx.x] = nB;
       }
       ptx::named_bar_sync(1, 256);
       fetch_cols(i + 1);
-      const int buf = i % p.nbuf;
-      ptx::mbar_wait(&bar_SdP[buf], (uint32_t)((i / p.nbuf) & 1));
+      const int buf = i & (NBUF - 1);
+      ptx::mbar_wait(&bar_SdP[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
       ptx::tc_fence_after();
-      if (i >= p.nbuf) ptx::mbar_wait(&bar_acc[buf], (uint32_t)(((i - p.nbuf) / p.nbuf) & 1));  // P^T/dS^T[buf] free
+      if (i >= NBUF) ptx::mbar_wait(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));  // P^T/dS^T[buf] free
       const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + lane_base;
       const uint32_t tdPi = tSi + (uint32_t)p.bc;
       uint8_t* tileP = sPT + (size_t)buf * ptile;
@@ -511,14 +522,34 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         ptx::tmem_ld_32x32(tSi + col0, sv);
         ptx::tmem_ld_32x32(tdPi + col0, dv);
         ptx::tmem_ld_wait();
-        float pv[32], ds[32];
+        float pv[32], ds[32];  // dS without the softmax scale: it is applied once when the accumulator is drained
+        if (col_meta) {
+          const float4* cA4 = reinterpret_cast<const float4*>(cA + col0);
+          const float4* cB4 = reinterpret_cast<const float4*>(cB + col0);
 #pragma unroll
-        for (int k = 0; k < 32; ++k) {
-          const float a = cA[col0 + k] + rowA;  // bias - lse (either order); -inf masks
-          const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, a));
-          const float dd = (p.mode == 0) ? cB[col0 + k] : rowD;
-          pv[k] = pk;
-          ds[k] = pk * (u2f(dv[k]) - dd) * p.scale;
+          for (int k4 = 0; k4 < 8; ++k4) {
+            const float4 a4 = cA4[k4];
+            const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+            float bv[4] = {rowD, rowD, rowD, rowD};
+            if (MODE == 0) {
+              const float4 b4 = cB4[k4];
+              bv[0] = b4.x; bv[1] = b4.y; bv[2] = b4.z; bv[3] = b4.w;
+            }
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const int k = k4 * 4 + e;
+              const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, av[e] + rowA));  // bias - lse; -inf masks
+              pv[k] = pk;
+              ds[k] = pk * (u2f(dv[k]) - bv[e]);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, rowA));
+            pv[k] = pk;
+            ds[k] = pk * (u2f(dv[k]) - rowD);
+          }
         }
         uint8_t* atomP = tileP + (col0 >> 6) * kAtom128;
         uint8_t* atomD = tileD + (col0 >> 6) * kAtom128;
@@ -531,7 +562,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
           o.z = sdb::pack_bf16x2(ds[c * 8 + 4], ds[c * 8 + 5]);
           o.w = sdb::pack_bf16x2(ds[c * 8 + 6], ds[c * 8 + 7]);
           st_swz(atomD, row, chunk0 + c, o);
-          if (p.mode == 0) {
+          if (MODE == 0) {
             o.x = sdb::pack_bf16x2(pv[c * 8 + 0], pv[c * 8 + 1]);
             o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
             o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
@@ -547,12 +578,13 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     // ---- drain the accumulators (commits complete in order: the last one covers all) ----
     {
       const int last = p.ncb - 1;
-      ptx::mbar_wait(&bar_acc[last % p.nbuf], (uint32_t)((last / p.nbuf) & 1));
+      ptx::mbar_wait(&bar_acc[last & (NBUF - 1)], (uint32_t)((last >> (NBUF - 1)) & 1));
       ptx::tc_fence_after();
     }
     const bool valid = r < p.Srow;
-    for (int which = 0; which < (p.mode == 0 ? 2 : 1); ++which) {
+    for (int which = 0; which < (MODE == 0 ? 2 : 1); ++which) {
       const uint32_t tA = which == 0 ? tA1 : tA2;
+      const float osc = which == 0 ? p.scale : 1.0f;  // dK / dQ carry the softmax scale; dV does not
       __nv_bfloat16* base = which == 0 ? p.out1 : p.out2;
       const long long ld = which == 0 ? p.ld1 : p.ld2;
       __nv_bfloat16* orow = base + ((long long)b * p.Srow + r) * ld + (long long)h * p.d;
@@ -565,10 +597,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
           for (int c = 0; c < 2; ++c) {
             if (c0 + c * 8 < p.d) {
               uint4 o;
-              o.x = sdb::pack_bf16x2(u2f(v[c * 8 + 0]), u2f(v[c * 8 + 1]));
-              o.y = sdb::pack_bf16x2(u2f(v[c * 8 + 2]), u2f(v[c * 8 + 3]));
-              o.z = sdb::pack_bf16x2(u2f(v[c * 8 + 4]), u2f(v[c * 8 + 5]));
-              o.w = sdb::pack_bf16x2(u2f(v[c * 8 + 6]), u2f(v[c * 8 + 7]));
+              o.x = sdb::pack_bf16x2(u2f(v[c * 8 + 0]) * osc, u2f(v[c * 8 + 1]) * osc);
+              o.y = sdb::pack_bf16x2(u2f(v[c * 8 + 2]) * osc, u2f(v[c * 8 + 3]) * osc);
+              o.z = sdb::pack_bf16x2(u2f(v[c * 8 + 4]) * osc, u2f(v[c * 8 + 5]) * osc);
+              o.w = sdb::pack_bf16x2(u2f(v[c * 8 + 6]) * osc, u2f(v[c * 8 + 7]) * osc);
               sdb::st_u4(orow + c0 + c * 8, o);
             }
           }
@@ -730,7 +762,13 @@ extern "C" int sdb_attn_bwd(const void* q, long long ldq, const void* k, long lo
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    attr_err = cudaFuncSetAttribute(attn_bwd_kernel<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(attn_bwd_kernel<0, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(attn_bwd_kernel<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(attn_bwd_kernel<1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   });
   if (attr_err != cudaSuccess)
     return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_bwd: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
@@ -783,7 +821,10 @@ extern "C" int sdb_attn_bwd(const void* q, long long ldq, const void* k, long lo
     p.stages = stages;
     const size_t smem_bytes = fixed + (size_t)p.stages * 2 * ctile;
     dim3 grid((p.Srow + 127) / 128, H, B);
-    attn_bwd_kernel<<<grid, kBwdThreads, smem_bytes, stream>>>(p);
+    if (mode == 0 && p.nbuf == 2) attn_bwd_kernel<0, 2><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
+    else if (mode == 0) attn_bwd_kernel<0, 1><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
+    else if (p.nbuf == 2) attn_bwd_kernel<1, 2><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
+    else attn_bwd_kernel<1, 1><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
     SDB_CUDA_LAUNCH_CHECK("sdb_attn_bwd");
   }
   return SDB_OK;

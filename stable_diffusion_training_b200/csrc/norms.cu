@@ -13,6 +13,7 @@
 namespace {
 
 constexpr int kGroups = 32;
+constexpr int kGnUnroll = 4;  // rows in flight per thread
 
 struct GnShape {
   int C, HW, B, cpg, nv, TC, RL, KC, chunks, rows_per_chunk;
@@ -82,28 +83,43 @@ gn_partial_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __re
   const __nv_bfloat16* xb = x + (size_t)b * s.HW * s.C;
   const __nv_bfloat16* dyb = BWD ? dy + (size_t)b * s.HW * s.C : nullptr;
   if (rl < s.RL) {
-    for (int r = r0 + rl; r < r1; r += s.RL) {
+    // kGnUnroll rows per trip: all 16-byte loads of a trip are issued before any is consumed (latency hiding; a
+    // thread owns only a handful of rows, so one load in flight at a time leaves the kernel latency-bound)
+    for (int r = r0 + rl; r < r1; r += kGnUnroll * s.RL) {
+      uint4 xr[kGnUnroll][KC], dr[kGnUnroll][KC];
 #pragma unroll
-      for (int k = 0; k < KC; ++k) {
-        const size_t off = (size_t)r * s.C + (size_t)(tc + k * s.TC) * 8;
-        float xv[8];
-        unpack8(sdb::ld_u4(xb + off), xv);
-        if (!BWD) {
+      for (int u = 0; u < kGnUnroll; ++u) {
+        const int rr = r + u * s.RL;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) { a0[k][i] += xv[i]; a1[k][i] = fmaf(xv[i], xv[i], a1[k][i]); }
-        } else {
-          float dv[8];
-          unpack8(sdb::ld_u4(dyb + off), dv);
+        for (int k = 0; k < KC; ++k) {
+          const size_t off = (size_t)rr * s.C + (size_t)(tc + k * s.TC) * 8;
+          xr[u][k] = (rr < r1) ? sdb::ld_u4(xb + off) : make_uint4(0u, 0u, 0u, 0u);
+          if (BWD) dr[u][k] = (rr < r1) ? sdb::ld_u4(dyb + off) : make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float xh = (xv[i] - mu[k][i]) * rs[k][i];
-            float dz = dv[i];
-            if (SILU) {
-              const float z = fmaf(xh, gm[k][i], bt[k][i]);
-              const float sg = sigmoid_f(z);
-              dz *= sg * (1.0f + z * (1.0f - sg));
+      for (int u = 0; u < kGnUnroll; ++u) {
+#pragma unroll
+        for (int k = 0; k < KC; ++k) {
+          float xv[8];
+          unpack8(xr[u][k], xv);
+          if (!BWD) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) { a0[k][i] += xv[i]; a1[k][i] = fmaf(xv[i], xv[i], a1[k][i]); }
+          } else {
+            float dv[8];
+            unpack8(dr[u][k], dv);  // rows past the chunk carry dy = 0: they add nothing
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const float xh = (xv[i] - mu[k][i]) * rs[k][i];
+              float dz = dv[i];
+              if (SILU) {
+                const float z = fmaf(xh, gm[k][i], bt[k][i]);
+                const float sg = sigmoid_f(z);
+                dz *= sg * (1.0f + z * (1.0f - sg));
+              }
+              a0[k][i] += dz; a1[k][i] = fmaf(dz, xh, a1[k][i]);
             }
-            a0[k][i] += dz; a1[k][i] = fmaf(dz, xh, a1[k][i]);
           }
         }
       }
@@ -196,36 +212,55 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
       if (BWD) { const float2 gg = grp[b * kGroups + g]; ga[k][i] = gg.x; gb[k][i] = gg.y; }
     }
   const size_t base = (size_t)b * s.HW * s.C;
-  for (int r = r0 + rl; r < r1; r += s.RL) {
+  for (int r = r0 + rl; r < r1; r += kGnUnroll * s.RL) {
+    uint4 xr[kGnUnroll][KC], dr[kGnUnroll][KC], ar[kGnUnroll][KC];
 #pragma unroll
-    for (int k = 0; k < KC; ++k) {
-      const size_t off = base + (size_t)r * s.C + (size_t)(tc + k * s.TC) * 8;
-      float xv[8], o[8];
-      unpack8(sdb::ld_u4(x + off), xv);
-      if (!BWD) {
+    for (int u = 0; u < kGnUnroll; ++u) {
+      const int rr = r + u * s.RL;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float z = fmaf((xv[i] - mu[k][i]) * rs[k][i], gm[k][i], bt[k][i]);
-          o[i] = SILU ? z * sigmoid_f(z) : z;
-        }
-      } else {
-        float dv[8];
-        unpack8(sdb::ld_u4(dy + off), dv);
-        float av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (add != nullptr) unpack8(sdb::ld_u4(add + off), av);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const float xh = (xv[i] - mu[k][i]) * rs[k][i];
-          float dz = dv[i];
-          if (SILU) {
-            const float z = fmaf(xh, gm[k][i], bt[k][i]);
-            const float sg = sigmoid_f(z);
-            dz *= sg * (1.0f + z * (1.0f - sg));
-          }
-          o[i] = rs[k][i] * (gm[k][i] * dz - ga[k][i] - xh * gb[k][i]) + av[i];
+      for (int k = 0; k < KC; ++k) {
+        const size_t off = base + (size_t)rr * s.C + (size_t)(tc + k * s.TC) * 8;
+        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+        xr[u][k] = (rr < r1) ? sdb::ld_u4(x + off) : z4;
+        if (BWD) {
+          dr[u][k] = (rr < r1) ? sdb::ld_u4(dy + off) : z4;
+          ar[u][k] = (rr < r1 && add != nullptr) ? sdb::ld_u4(add + off) : z4;
         }
       }
-      sdb::st_u4(out + off, pack8(o));
+    }
+#pragma unroll
+    for (int u = 0; u < kGnUnroll; ++u) {
+      const int rr = r + u * s.RL;
+      if (rr >= r1) break;
+#pragma unroll
+      for (int k = 0; k < KC; ++k) {
+        const size_t off = base + (size_t)rr * s.C + (size_t)(tc + k * s.TC) * 8;
+        float xv[8], o[8];
+        unpack8(xr[u][k], xv);
+        if (!BWD) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float z = fmaf((xv[i] - mu[k][i]) * rs[k][i], gm[k][i], bt[k][i]);
+            o[i] = SILU ? z * sigmoid_f(z) : z;
+          }
+        } else {
+          float dv[8], av[8];
+          unpack8(dr[u][k], dv);
+          unpack8(ar[u][k], av);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = (xv[i] - mu[k][i]) * rs[k][i];
+            float dz = dv[i];
+            if (SILU) {
+              const float z = fmaf(xh, gm[k][i], bt[k][i]);
+              const float sg = sigmoid_f(z);
+              dz *= sg * (1.0f + z * (1.0f - sg));
+            }
+            o[i] = rs[k][i] * (gm[k][i] * dz - ga[k][i] - xh * gb[k][i]) + av[i];
+          }
+        }
+        sdb::st_u4(out + off, pack8(o));
+      }
     }
   }
 }

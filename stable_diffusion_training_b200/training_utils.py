@@ -408,3 +408,99 @@ def default_scheduler(device, beta_schedule: str = "scaled_linear", prediction_t
                               num_train_timesteps=1000, prediction_type=prediction_type, device=device)
         _KEY[key] = FrozenModel(call=s, params=s.create_state())
     return _KEY[key]
+
+
+# ---------------------------------------------------------------------------------------------------------------
+class CompiledTrainStep:
+    """train_step captured once per batch shape into a CUDA graph and replayed — the counterpart of the reference's
+    AOT `jax.jit(...).lower(...).compile()` per resolution bucket (training_utils.py:765-983: one executable per
+    pixel shape, looked up by `batch["pixel_values"].shape` at training.py:214-234). A step is ~2 000 kernel launches;
+    replaying them from a graph removes the per-launch host cost and keeps the GPU back-to-back.
+
+    Per shape: the first call runs eagerly (fills the lazily built caches: workspaces, key-bias tables, function
+    attributes), the second call captures and replays, later calls only copy the batch into the graph's static input
+    buffers and replay. Noise / timesteps missing from the batch are drawn OUTSIDE the graph into those buffers.
+    The loss returned in `metrics` is a static device tensor, overwritten by the next call (async, like the reference's
+    futures: the host blocks only when it reads it)."""
+
+    def __init__(self, state: TrainState, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
+                 offset_noise_magnitude: float = 0.0, min_snr_gamma_magnitude: float = 0.0,
+                 perturbation_noise_magnitude: float = 0.0):
+        if min_snr_gamma_magnitude:
+            raise NotImplementedError("CompiledTrainStep: min-SNR weighting gathers on the host; use train_step")
+        lr = state.hyper["learning_rate"]
+        if callable(lr) and lr(0) != lr(1_000_000):
+            raise NotImplementedError("CompiledTrainStep: only a constant learning-rate schedule can be baked in")
+        self.state = state
+        self.sched = frozen_noise_scheduler_state or default_scheduler(state.arena.device)
+        self.offset = float(offset_noise_magnitude)
+        self.perturb = float(perturbation_noise_magnitude)
+        self._entries: Dict[tuple, dict] = {}
+        self.launches_per_replay = 0
+
+    def _eager(self, batch, rng):
+        return train_step(self.state, batch, rng, self.sched, offset_noise_magnitude=self.offset,
+                          perturbation_noise_magnitude=self.perturb)
+
+    def _fill(self, e, batch, rng):
+        dev = self.state.arena.device
+        buf = e["buf"]
+        buf["latents"].copy_(batch["latents"], non_blocking=True)
+        ctx = batch["encoder_hidden_states"]
+        buf["encoder_hidden_states"].copy_(ctx, non_blocking=True)
+        B = buf["latents"].shape[0]
+        gen = None
+        if batch.get("noise") is not None:
+            buf["noise"].copy_(batch["noise"], non_blocking=True)
+        else:
+            gen = _generator(rng, dev)
+            shape = buf["latents"].shape
+            noise = torch.randn(shape, generator=gen, device=dev, dtype=torch.float32)
+            if self.offset:
+                noise = noise + torch.randn((B, shape[1], 1, 1), generator=gen, device=dev) * self.offset
+            if self.perturb:
+                noise = noise + self.perturb * torch.randn(shape, generator=gen, device=dev)
+            buf["noise"].copy_(noise)
+        if batch.get("timesteps") is not None:
+            buf["timesteps"].copy_(batch["timesteps"], non_blocking=True)
+        else:
+            gen = gen or _generator(rng, dev)
+            buf["timesteps"].copy_(torch.randint(0, self.sched.call.config.num_train_timesteps, (B,), generator=gen,
+                                                 device=dev).to(torch.int32))
+
+    def __call__(self, state: TrainState, batch: dict, rng=None):
+        if state is not self.state:
+            raise ValueError("CompiledTrainStep: called with a different TrainState than it was compiled for")
+        key = (tuple(batch["latents"].shape), tuple(batch["encoder_hidden_states"].shape))
+        e = self._entries.get(key)
+        if e is None:
+            self._entries[key] = {"graph": None}
+            return self._eager(batch, rng)  # also the warm-up of every lazily built cache
+        if e["graph"] is None:
+            dev = state.arena.device
+            e["buf"] = {"latents": torch.empty(key[0], dtype=torch.float32, device=dev),
+                        "noise": torch.empty(key[0], dtype=torch.float32, device=dev),
+                        "timesteps": torch.empty((key[0][0],), dtype=torch.int32, device=dev),
+                        "encoder_hidden_states": torch.empty(key[1], dtype=batch["encoder_hidden_states"].dtype,
+                                                             device=dev)}
+            self._fill(e, batch, rng)
+            torch.cuda.synchronize(dev)
+            g = torch.cuda.CUDAGraph()
+            n0 = _lib.lib().sdb_launch_count()
+            host_step = state._host_step
+            with torch.cuda.graph(g):
+                _, metrics = train_step(state, e["buf"], None, self.sched)
+            state._host_step = host_step  # capture enqueued nothing: the replay below is the real step
+            e["launches"] = _lib.lib().sdb_launch_count() - n0
+            e["graph"], e["metrics"] = g, metrics
+            self.launches_per_replay = e["launches"]
+        else:
+            self._fill(e, batch, rng)
+        e["graph"].replay()
+        state._host_step += 1
+        return state, e["metrics"]
+
+
+def compile_train_step(state: TrainState, frozen_noise_scheduler_state: Optional[FrozenModel] = None, **flags
+                       ) -> CompiledTrainStep:
+    return CompiledTrainStep(state, frozen_noise_scheduler_state, **flags)
