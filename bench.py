@@ -397,7 +397,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="sd15", choices=list(WORKLOADS))
     ap.add_argument("--batch", type=int, default=0)
-    ap.add_argument("--graph", type=int, default=0, help="replay the step from a CUDA graph")
+    ap.add_argument("--graph", type=int, default=1, help="replay the step from a CUDA graph (0: eager launches)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline leg")
     ap.add_argument("--cpu-budget", type=float, default=30.0)

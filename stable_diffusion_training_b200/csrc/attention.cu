@@ -144,7 +144,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       tma_tile(sQ, &p.mapQ, barQ, p.atoms, kAtom128, q0, h, b);
       auto load_k = [&](int j) {
         const int s = j % p.kstages, n = j / p.kstages;
-        ptx::mbar_wait(&k_empty[s], (uint32_t)((n & 1) ^ 1));
+        ptx::mbar_wait_sleep(&k_empty[s], (uint32_t)((n & 1) ^ 1));
         ptx::mbar_expect_tx(&k_full[s], tile_bytes);
         tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &k_full[s], p.atoms, kAtom128, j * 128, h, b);
       };
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       for (int j = 0; j < p.nkb; ++j) {
         if (j + 1 < p.nkb) load_k(j + 1);  // K runs one block ahead of V: S(j+1) is issued before PV(j)
         const int s = j % p.vstages, n = j / p.vstages;
-        ptx::mbar_wait(&v_empty[s], (uint32_t)((n & 1) ^ 1));
+        ptx::mbar_wait_sleep(&v_empty[s], (uint32_t)((n & 1) ^ 1));
         ptx::mbar_expect_tx(&v_full[s], tile_bytes);
         tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &v_full[s], p.atoms, kAtom128, j * 128, h, b);
       }
@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       int ks = 0, vs = 0;
       uint32_t kph = 0, vph = 0;
       auto issue_S = [&](int j) {
-        ptx::mbar_wait(&k_full[ks], kph);
+        ptx::mbar_wait_sleep(&k_full[ks], kph);
         ptx::tc_fence_after();
         mma_ksteps<false>(tS + (uint32_t)(j & 1) * 128u, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS, ksteps,
                           0u);
@@ -184,8 +184,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       for (int j = 0; j < p.nkb; ++j) {
         // S buffer (j+1)&1 was last read by softmax(j-1), whose completion (bar_P) was observed in iteration j-1
         if (j + 1 < p.nkb) issue_S(j + 1);
-        ptx::mbar_wait(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
-        ptx::mbar_wait(&v_full[vs], vph);
+        ptx::mbar_wait_sleep(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
+        ptx::mbar_wait_sleep(&v_full[vs], vph);
         ptx::tc_fence_after();
         mma_ksteps<true>(tO, dP0 + (uint32_t)(j & 1) * 2u * atom16, atom16, dV0 + (uint32_t)vs * tile16, 0u, idescO, 8,
                          j > 0 ? 1u : 0u);
@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
     }
     float m_used = -INFINITY, l = 0.f;
     for (int j = 0; j < p.nkb; ++j) {
-      ptx::mbar_wait(&bar_S[j & 1], (uint32_t)((j >> 1) & 1));
+      ptx::mbar_wait_sleep(&bar_S[j & 1], (uint32_t)((j >> 1) & 1), 20);
       ptx::tc_fence_after();
       const uint32_t tSj = tS + (uint32_t)(j & 1) * 128u + lane_base + (uint32_t)half * 64u;
       const int key0 = j * 128 + half * 64;
@@ -242,7 +242,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       if (j == 0) {
         m_used = mx;
       } else {
-        ptx::mbar_wait(bar_PV, (uint32_t)((j - 1) & 1));  // O holds blocks 0..j-1; P buffer j&1 is free again
+        ptx::mbar_wait_sleep(bar_PV, (uint32_t)((j - 1) & 1), 20);  // O holds blocks 0..j-1; P buffer j&1 is free again
         ptx::tc_fence_after();
         const bool need = mx > m_used + 8.0f;
         if (__any_sync(0xffffffffu, need)) {
@@ -414,7 +414,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       tma_tile(sR2, &p.mapR2, barR, p.atoms, kAtom128, r0, h, b);
       for (int i = 0; i < p.ncb; ++i) {
         const int s = i % p.stages, n = i / p.stages;
-        ptx::mbar_wait(&c_empty[s], (uint32_t)((n & 1) ^ 1));
+        ptx::mbar_wait_sleep(&c_empty[s], (uint32_t)((n & 1) ^ 1));
         ptx::mbar_expect_tx(&c_full[s], 2 * ctile);
         tma_tile(sC1 + (size_t)s * ctile, &p.mapC1, &c_full[s], p.atoms, catom, i * p.bc, h, b);
         tma_tile(sC2 + (size_t)s * ctile, &p.mapC2, &c_full[s], p.atoms, catom, i * p.bc, h, b);
@@ -438,7 +438,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       int ss = 0, as = 0;       // stage of the next S/dP issue, of the next accumulate
       uint32_t sph = 0;
       auto issue_SdP = [&](int i) {
-        ptx::mbar_wait(&c_full[ss], sph);
+        ptx::mbar_wait_sleep(&c_full[ss], sph);
         ptx::tc_fence_after();
         const int buf = i & (NBUF - 1);
         const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc;
@@ -453,7 +453,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         // double-buffered: S/dP buffer (i+1)&1 was last read by compute(i-1), observed through bar_PdS in iteration i-1
         if (NBUF == 2 && i + 1 < p.ncb) issue_SdP(i + 1);
         const int buf = i & (NBUF - 1);
-        ptx::mbar_wait(&bar_PdS[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
+        ptx::mbar_wait_sleep(&bar_PdS[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
         ptx::tc_fence_after();
         mma_ksteps<true>(tA1, dDS0 + (uint32_t)buf * ptile16, atom16, dC1m + (uint32_t)as * ctile16, 0u, idescA, k2,
                          i > 0 ? 1u : 0u);
@@ -508,9 +508,9 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       ptx::named_bar_sync(1, 256);
       fetch_cols(i + 1);
       const int buf = i & (NBUF - 1);
-      ptx::mbar_wait(&bar_SdP[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
+      ptx::mbar_wait_sleep(&bar_SdP[buf], (uint32_t)((i >> (NBUF - 1)) & 1), 20);
       ptx::tc_fence_after();
-      if (i >= NBUF) ptx::mbar_wait(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));  // P^T/dS^T[buf] free
+      if (i >= NBUF) ptx::mbar_wait_sleep(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1), 20);  // P^T/dS^T[buf] free
       const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + lane_base;
       const uint32_t tdPi = tSi + (uint32_t)p.bc;
       uint8_t* tileP = sPT + (size_t)buf * ptile;

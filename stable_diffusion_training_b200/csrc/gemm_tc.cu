@@ -141,7 +141,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
         const Tile ti = decode_tile(p, t);
         for (int it = 0; it < ti.num_k; ++it) {
-          ptx::mbar_wait(&empty_bar[stage], phase ^ 1u);
+          ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sb = sa + kAStageBytes;
           if (MODE == SDB_GEMM_FWD) {

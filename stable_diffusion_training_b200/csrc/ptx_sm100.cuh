@@ -35,6 +35,12 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// Polite wait for threads that are not on the critical path (TMA producers running stages ahead, single-thread MMA
+// issuers with a whole compute block of slack, compute warps that ran ahead of their scheduler-mate): a tight
+// try_wait loop competes for issue slots with the issue-bound compute warps on the same SM sub-partition.
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t* bar, uint32_t parity, uint32_t ns = 32) {
+  while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
 
 // ---------------- proxies / fences ----------------
 // generic-proxy smem writes -> visible to the async proxy (TMA / tcgen05.mma operand reads)
