@@ -156,6 +156,7 @@ def run_ours(args):
     from stable_diffusion_training_b200 import training_utils as TU
     from stable_diffusion_training_b200 import unet as PU
 
+    os.environ.setdefault("NCCL_DEBUG", "WARN")  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
     rank, local, world = parallel.init_process_group_from_env("nccl")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)

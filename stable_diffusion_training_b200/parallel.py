@@ -69,6 +69,13 @@ class GradReducer:
         self._ready: List[bool] = []
         self.issued_order: List[int] = []
         self.bytes_reduced = 0
+        # CUDA-graph capture support (training_utils.CompiledTrainStep): collectives are NOT captured. While
+        # `capture` is set, ready buckets are only recorded; every `capture_cut_every` buckets the capturer is asked to
+        # close the current graph segment, and at replay time the recorded buckets are all-reduced eagerly on the
+        # communication stream right after that segment has been enqueued (replay_segment_buckets / replay_finish).
+        self.capture = None          # callable(force: bool) -> None that cuts the graph segment
+        self.capture_cut_every = 8
+        self._deferred: List[int] = []
 
     # ---- one step ----
     def begin(self, _graph=None) -> None:
@@ -95,6 +102,11 @@ class GradReducer:
     def _all_reduce_bucket(self, b: int) -> None:
         s, e, _ = self.buckets[b]
         self.issued_order.append(b)
+        if self.capture is not None:
+            self._deferred.append(b)
+            if len(self._deferred) >= self.capture_cut_every:
+                self.capture(False)
+            return
         if self.world_size == 1:
             return
         view = self.grad[s:e]
@@ -111,6 +123,9 @@ class GradReducer:
     def finish(self, loss: torch.Tensor) -> torch.Tensor:
         """Flush the remaining buckets, average the loss over ranks, join the communication stream."""
         self._issue_ready(force=True)
+        if self.capture is not None:
+            self.capture(True)  # the replayer reduces the remaining buckets and the loss, then joins the streams
+            return loss
         if self.world_size > 1:
             if self.cuda:
                 ev = torch.cuda.Event()
@@ -124,6 +139,40 @@ class GradReducer:
                 dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
                 loss.mul_(1.0 / self.world_size)
         return loss
+
+
+def _replay_buckets(red: GradReducer, buckets: Sequence[int]) -> None:
+    if red.world_size == 1 or not buckets:
+        return
+    dev = red.grad.device
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(dev))
+    red.comm_stream.wait_event(ev)
+    with torch.cuda.stream(red.comm_stream):
+        for b in buckets:
+            s, e, _ = red.buckets[b]
+            dist.all_reduce(red.grad[s:e], op=dist.ReduceOp.SUM, group=red.group)
+
+
+GradReducer.replay_segment_buckets = _replay_buckets
+
+
+def _replay_finish(red: GradReducer, buckets: Sequence[int], loss: torch.Tensor) -> None:
+    """Eager tail of a replayed backward: remaining buckets, loss mean, join of the communication stream."""
+    if red.world_size == 1:
+        return
+    _replay_buckets(red, buckets)
+    dev = red.grad.device
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(dev))
+    red.comm_stream.wait_event(ev)
+    with torch.cuda.stream(red.comm_stream):
+        dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=red.group)
+        loss.mul_(1.0 / red.world_size)
+    torch.cuda.current_stream(dev).wait_stream(red.comm_stream)
+
+
+GradReducer.replay_finish = _replay_finish
 
 
 def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES) -> GradReducer:

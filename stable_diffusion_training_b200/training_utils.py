@@ -484,21 +484,68 @@ class CompiledTrainStep:
                         "encoder_hidden_states": torch.empty(key[1], dtype=batch["encoder_hidden_states"].dtype,
                                                              device=dev)}
             self._fill(e, batch, rng)
-            torch.cuda.synchronize(dev)
-            g = torch.cuda.CUDAGraph()
-            n0 = _lib.lib().sdb_launch_count()
-            host_step = state._host_step
-            with torch.cuda.graph(g):
-                _, metrics = train_step(state, e["buf"], None, self.sched)
-            state._host_step = host_step  # capture enqueued nothing: the replay below is the real step
-            e["launches"] = _lib.lib().sdb_launch_count() - n0
-            e["graph"], e["metrics"] = g, metrics
-            self.launches_per_replay = e["launches"]
+            self._capture(e)
         else:
             self._fill(e, batch, rng)
-        e["graph"].replay()
+        self._replay(e)
         state._host_step += 1
         return state, e["metrics"]
+
+    def _capture(self, e) -> None:
+        """Capture the step as a chain of CUDA-graph segments sharing one memory pool. Without data parallelism that
+        is one segment. With it, the NCCL collectives stay OUT of the graphs: the reducer closes a segment whenever
+        enough gradient buckets are complete, and at replay time those buckets are all-reduced eagerly on the
+        communication stream right after the segment is enqueued, overlapping the following segments."""
+        import gc
+        state = self.state
+        dev = state.arena.device
+        dp = state.dp
+        gc.collect()
+        torch.cuda.synchronize(dev)
+        pool = torch.cuda.graph_pool_handle()
+        stream = torch.cuda.Stream(device=dev)
+        stream.wait_stream(torch.cuda.current_stream(dev))
+        segs = []   # (graph, bucket ids reduced after it, is_last_backward_segment)
+        cur = {"g": None}
+        n0 = _lib.lib().sdb_launch_count()
+        host_step = state._host_step
+
+        def begin():
+            cur["g"] = torch.cuda.CUDAGraph()
+            cur["g"].capture_begin(pool=pool)
+
+        def cut(final: bool):
+            cur["g"].capture_end()
+            segs.append((cur["g"], list(dp._deferred), final))
+            dp._deferred.clear()
+            begin()
+
+        with torch.cuda.stream(stream):
+            if dp is not None:
+                dp.capture = cut
+            try:
+                begin()
+                _, metrics = train_step(state, e["buf"], None, self.sched)
+                cur["g"].capture_end()
+                segs.append((cur["g"], [], False))
+            finally:
+                if dp is not None:
+                    dp.capture = None
+        torch.cuda.current_stream(dev).wait_stream(stream)
+        state._host_step = host_step  # capture enqueued nothing: the replay that follows is the real step
+        e["launches"] = _lib.lib().sdb_launch_count() - n0
+        e["graph"], e["segs"], e["metrics"] = segs[0][0], segs, metrics
+        self.launches_per_replay = e["launches"]
+
+    def _replay(self, e) -> None:
+        dp = self.state.dp
+        for g, buckets, final in e["segs"]:
+            g.replay()
+            if dp is not None:
+                if final:
+                    dp.replay_finish(buckets, e["metrics"]["loss"])
+                else:
+                    dp.replay_segment_buckets(buckets)
 
 
 def compile_train_step(state: TrainState, frozen_noise_scheduler_state: Optional[FrozenModel] = None, **flags
