@@ -19,6 +19,7 @@
 #include "sdb_common.cuh"
 #include "ptx_sm100.cuh"
 #include "../../include/sdb200.h"
+#include <cstdlib>
 #include <mutex>
 
 namespace {
@@ -40,7 +41,7 @@ struct alignas(64) TcParams {
   int M, N, K, BN;
   int tiles_m, tiles_n, total_tiles, kblocks;
   int splits, pb_per_split, total_pb;
-  int stages;
+  int stages, dbg;
   uint32_t b_stage_bytes, stage_bytes;
   void* d;
   long long ldd, dsW, dsH, dsN;
@@ -144,7 +145,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
           ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sb = sa + kAStageBytes;
-          if (MODE == SDB_GEMM_FWD) {
+          if (p.dbg & 1) {  // experiment: no TMA traffic (SDB_GEMM_DBG=1)
+            ptx::mbar_expect_tx(&full_bar[stage], 0u);
+          } else if (MODE == SDB_GEMM_FWD) {
             const int tap = it / p.kblocks;
             const int kb = it - tap * p.kblocks;
             const uint32_t bbytes = p.b_mn ? (uint32_t)ti.nboxes * kBoxBytes : p.b_stage_bytes;
@@ -207,7 +210,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
           for (int ks = 0; ks < kBlockK / 16; ++ks) {
             const uint64_t da = ptx::umma_desc_sw128(sa + ks * a_kadv, a_lbo, 1024u);
             const uint64_t db = ptx::umma_desc_sw128(sb + ks * b_kadv, b_lbo, 1024u);
-            ptx::umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+            if (!(p.dbg & 4)) ptx::umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
           }
           ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
           if (++stage == p.stages) {
@@ -237,7 +240,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const int hi = r2 % p.bh;
         const int ni = r2 / p.bh;
         const int w = ti.w0 + wi, h = ti.h0 + hi, n = ti.n0 + ni;
-        const bool valid = (w < p.W) && (h < p.H) && (n < p.NI);
+        const bool valid = (w < p.W) && (h < p.H) && (n < p.NI) && !(p.dbg & 2);
         const long long grow = ((long long)n * p.H + h) * p.W + w;
         __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.d) + (long long)n * p.dsN + (long long)h * p.dsH +
                              (long long)w * p.dsW + ti.n_off;
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         }
       } else {
         const int m = ti.m_off + row;
-        const bool valid = m < p.M;
+        const bool valid = (m < p.M) && !(p.dbg & 2);
         float* out = reinterpret_cast<float*>(p.d) + ((long long)p.tap_brow[ti.tap] + m) * p.ldd + ti.n_off;
         for (int c0 = 0; c0 < ti.nw; c0 += 32) {
           uint32_t v[32];
@@ -436,7 +439,6 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     p.total_tiles = p.tiles_m * p.tiles_n;
     p.splits = 1;
     if (p.b_mn) {
-      SDB_CHECK_ARG(d->block_n % 64 == 0 || d->block_n >= d->N, "sdb_gemm_tc: MN-major B needs block_n %% 64 == 0");
       rc = encode_view(&p.mapB, d->b, 64, 64, 1, 1, "B (weights [K,N])");
       p.b_stage_bytes = (uint32_t)(((p.BN + 63) / 64) * kBoxBytes);
     } else {
@@ -448,7 +450,6 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     SDB_CHECK_ARG(d->M > 0, "sdb_gemm_tc: WGRAD needs M (rows of dW per tap)");
     SDB_CHECK_ARG(d->N % 4 == 0 && d->ldd % 4 == 0 && (((uintptr_t)d->d) & 15) == 0,
                   "sdb_gemm_tc: WGRAD needs N %% 4 == 0, ldd %% 4 == 0 and a 16-byte aligned output");
-    SDB_CHECK_ARG(d->block_n % 64 == 0 || d->block_n >= d->N, "sdb_gemm_tc: WGRAD needs block_n %% 64 == 0");
     p.b_mn = 1;
     p.M = d->M;
     p.tiles_m = sdb::ceil_div(p.M, 128);
@@ -469,6 +470,8 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_gemm_tc: stage too large");
   p.stages = stages;
+  static const int dbg_env = getenv("SDB_GEMM_DBG") ? atoi(getenv("SDB_GEMM_DBG")) : 0;  // timing experiments only
+  p.dbg = dbg_env;
   const size_t smem_bytes = (size_t)stages * p.stage_bytes + 1024 /*align slack*/ + 256 /*barriers*/;
 
   static std::once_flag attr_once;

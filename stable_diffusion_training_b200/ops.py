@@ -6,6 +6,8 @@ Weights: Flax layouts — Dense kernel (in, out), Conv kernel HWIO — row-major
 """
 from __future__ import annotations
 
+import os
+
 import ctypes as C
 
 import torch
@@ -47,17 +49,39 @@ def _pixel_box(W: int, H: int, N: int, pixels: int):
     return bw, bh, bn
 
 
+_BN_CACHE: dict = {}
+
+
 def _pick_block_n(N: int, need64: bool, m_tiles: int) -> int:
-    if N <= 256:
-        return N if (not need64 or N % 64 == 0) else min(256, (N + 63) // 64 * 64) if N > 64 else N
-    best, best_cost = 256, None
-    for bn in (256, 192, 128):
-        tiles = (N + bn - 1) // bn
-        total = tiles * m_tiles
-        waves = (total + NUM_SMS - 1) // NUM_SMS
-        cost = waves * bn  # time ~ waves x tile width
+    """Tile width for the persistent GEMM: simulate the kernel's static round-robin schedule (tile t -> CTA t % 148,
+    n-tile = t % tiles_n) for every legal width (multiples of 16 up to 256; MN-major B is staged in 64-column boxes,
+    so its smem footprint rounds up to 64) and take the width whose busiest CTA has the least work. Work of a tile =
+    its width, stretched below 128 columns where the UMMA operand fetch (4 KB of A + 32*BN B of B per BN/2 cycles)
+    exceeds 128 B/clk of shared-memory bandwidth, plus a fixed per-tile cost (pipeline refill) in column equivalents."""
+    del need64  # any multiple of 16 is legal for both operand majors now
+    key = (N, m_tiles)
+    if key in _BN_CACHE:
+        return _BN_CACHE[key]
+    forced = int(os.environ.get("SDB_BN", "0"))
+    if forced:
+        return min(forced, (N + 15) // 16 * 16)
+    best, best_cost = None, None
+    for bn in range(256, 63, -16):
+        tiles_n = -(-N // bn)
+        if bn * (tiles_n - 1) >= N:
+            continue
+        last = N - bn * (tiles_n - 1)
+        total = tiles_n * m_tiles
+        load = [0] * min(total, NUM_SMS)
+        for t in range(total):
+            w = bn if (t % tiles_n) < tiles_n - 1 else (last + 15) // 16 * 16
+            load[t % NUM_SMS] += w * max(1.0, (8192.0 / w + 64.0) / 128.0) + 24
+        cost = max(load)
         if best_cost is None or cost < best_cost:
             best, best_cost = bn, cost
+    if N < 64 or best is None:
+        best = (N + 15) // 16 * 16
+    _BN_CACHE[key] = best
     return best
 
 
@@ -124,9 +148,9 @@ def gemm_wgrad(a_views, taps, b_view: View4, out: torch.Tensor, pix, M: int, N: 
     d.outW, d.outH, d.outN = W, H, NI
     d.bw, d.bh, d.bn = _pixel_box(W, H, NI, 64)
     d.M, d.N = M, N
-    d.block_n = N if N <= 256 and (N % 64 == 0 or N <= 64) else (256 if N > 256 else (N + 63) // 64 * 64)
-    if d.block_n > 256:
-        d.block_n = 256
+    # balanced widths: N = 320 -> 2 x 160 rather than 256 + 64 (MN-major boxes round the smem footprint up to 64)
+    tiles_n = -(-N // 256)
+    d.block_n = min(256, (-(-N // tiles_n) + 15) // 16 * 16)
     tiles = len(taps) * -(-M // 128) * -(-N // d.block_n)
     total_pb = -(-W // d.bw) * -(-H // d.bh) * -(-NI // d.bn)
     splits = max(1, min(total_pb, (2 * NUM_SMS) // max(1, tiles)))

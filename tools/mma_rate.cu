@@ -1,0 +1,106 @@
+// Microbenchmark: cycles per tcgen05.mma (M=128, K=16, bf16) as a function of N, for A from shared memory (SS) and
+// A from tensor memory (TS). Settles how tile widths should be chosen in gemm_tc.cu / attention.cu.
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o mma_rate tools/mma_rate.cu -lcuda && ./mma_rate
+#include <cstdint>
+#include <cstdio>
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include "../stable_diffusion_training_b200/csrc/ptx_sm100.cuh"
+
+__device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
+// mode: 0 SS (B K-major), 1 SS (B MN-major), 2 TS (B K-major), 3 TS (B MN-major), 4 SS alternating accumulators
+__global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int n, int iters, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = ptx::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sA = smem;              // 128 x 64 bf16 (16 KB)
+  uint8_t* sB = smem + 16384;      // 256 x 64 bf16 (32 KB) K-major, or 4 boxes of 64x64 MN-major
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 16384 + 32768);
+  uint32_t* tptr = reinterpret_cast<uint32_t*>(bar + 1);
+  for (int i = threadIdx.x; i < (16384 + 32768) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u + i;
+  if (threadIdx.x == 0) {
+    ptx::mbar_init(bar, 1);
+    ptx::fence_barrier_init();
+  }
+  if (threadIdx.x < 32) {
+    ptx::tmem_alloc(tptr, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tptr;
+  if (threadIdx.x == 0) {
+    const bool b_mn = (mode & 1) && mode < 4;
+    const bool ts = (mode == 2 || mode == 3);
+    const uint32_t idesc = ptx::umma_idesc_bf16(n, 0, b_mn ? 1 : 0);
+    const uint64_t dA = ptx::umma_desc_sw128(ptx::smem_u32(sA), 0u, 1024u);
+    const uint64_t dB = ptx::umma_desc_sw128(ptx::smem_u32(sB), b_mn ? 8192u : 0u, 1024u);
+    const uint32_t tA = tmem + 256u;  // A operand region for TS (garbage values: timing only)
+    // warm-up
+    for (int k = 0; k < 4; ++k) ptx::umma_bf16(tmem, dA + 2u * k, dB + (b_mn ? 128u * k : 2u * k), idesc, 1u);
+    ptx::umma_commit(bar);
+    ptx::mbar_wait(bar, 0);
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const uint64_t db = dB + (b_mn ? 128u * k : 2u * k);
+        const uint32_t d = (mode == 4) ? tmem + (uint32_t)((it * 4 + k) & 1) * 256u : tmem;
+        if (ts) umma_bf16_ts(d, tA + 8u * k, db, idesc, 1u);
+        else ptx::umma_bf16(d, dA + 2u * k, db, idesc, 1u);
+      }
+    }
+    const long long t_issue = clock64();
+    ptx::umma_commit(bar);
+    ptx::mbar_wait(bar, 1);
+    const long long t1 = clock64();
+    if (blockIdx.x == 0) {
+      out[0] = t1 - t0;
+      out[1] = t_issue - t0;
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 512);
+  }
+}
+
+int main() {
+  long long* out;
+  cudaMalloc(&out, 16);
+  const int smem = 16384 + 32768 + 1024 + 64;
+  cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int iters = 2000;
+  const char* names[5] = {"SS  B K-major ", "SS  B MN-major", "TS  B K-major ", "TS  B MN-major", "SS  alt-accum "};
+  const int ns[] = {16, 32, 48, 64, 96, 128, 160, 192, 256};
+  for (int grid : {1, 148}) {
+    printf("grid %d (cycles per MMA M=128 K=16; total incl. drain / issue-only)\n", grid);
+    for (int mode = 0; mode < 5; ++mode) {
+      for (int n : ns) {
+        if (mode == 4 && n > 256) continue;
+        rate_kernel<<<grid, 128, smem>>>(mode, n, iters, out);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) {
+          printf("%s N=%d: %s\n", names[mode], n, cudaGetErrorString(e));
+          return 1;
+        }
+        long long h[2];
+        cudaMemcpy(h, out, 16, cudaMemcpyDeviceToHost);
+        printf("%s N=%3d  %7.1f  issue %6.1f\n", names[mode], n, (double)h[0] / (iters * 4.0), (double)h[1] / (iters * 4.0));
+      }
+    }
+  }
+  return 0;
+}

@@ -40,5 +40,13 @@ elif what == "lion":
         _lib.check(_lib.lib().sdb_lion8_update(g.data_ptr(), p.data_ptr(), p.data_ptr(), sh.data_ptr(), codes.data_ptr(),
                                                inv.data_ptr(), n, 16, 0.9, 0.99, 1e-6 / 7, 0.07, 1, 0, 1.0, 0,
                                                _lib.stream_ptr()), "lion8")
+elif what == "gn":
+    for (B, HW, C) in [(8, 4096, 320), (8, 1024, 640)]:
+        x, dy = rnd(B, HW, C), rnd(B, HW, C)
+        g, b_ = torch.ones(C, device=dev), torch.zeros(C, device=dev)
+        dg, db = torch.empty(C, device=dev), torch.empty(C, device=dev)
+        for _ in range(2):
+            y, st = ops.groupnorm_fwd(x, g, b_, silu=True)
+            ops.groupnorm_bwd(x, dy, st, g, b_, dg, db, silu=True)
 torch.cuda.synchronize()
 print("ok")
