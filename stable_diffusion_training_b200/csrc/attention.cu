@@ -67,11 +67,16 @@ __device__ __forceinline__ void mma_ksteps(uint32_t tmem_d, uint64_t dA, uint32_
 }
 
 // =============================================== forward ===============================================
-// 320 threads: warps 0-7 = softmax (two warps per TMEM lane quarter: warp w and w+4 own the same 32 query rows and
-// split the 128 keys of a block in halves), warp 8 = tcgen05.mma issuer + TMEM owner, warp 9 = TMA producer.
-// S is double-buffered in TMEM and P in shared memory, so QK^T of block j+1 and PV of block j-1 run on the tensor pipe
-// while the softmax warps (the MUFU-bound resource: 128x128 exp2 per block) work on block j.
-constexpr int kFwdThreads = 320;
+// 384 threads: warps 0-7 = softmax (two warps per TMEM lane quarter: warp w and w+4 own the same 32 query rows and
+// split the 128 keys of a block in halves), warp 8 = QK^T issuer + TMEM owner, warp 9 = TMA producer, warps 10-11 = PV
+// issuers. S is double-buffered in TMEM and P in shared memory, so QK^T of block j+1 and PV of block j-1 run on the
+// tensor pipe while the softmax warps (the MUFU-bound resource: 128x128 exp2 per block) work on block j.
+//
+// Why several issuing warps (tools/mma_rate.cu, measured on B200): ONE thread cannot issue tcgen05.mma faster than one
+// per ~63 ns whatever the shape, so the 3 + 8 narrow MMAs of a key block (N = 128 for QK^T, N = dpad <= 64 for PV)
+// cost ~0.7 us from a single issuer — more than the softmax of the block. Independent issuers overlap: QK^T gets its
+// own warp and PV is split by key halves (k-steps 0-3 / 4-7) into two accumulators that the epilogue adds.
+constexpr int kFwdThreads = 384;
 constexpr int kMaxBiasBlocks = 16;  // per-key bias (cross-attention quirk / masks given by the caller): Skv <= 2048
 
 struct FwdParams {
@@ -80,7 +85,7 @@ struct FwdParams {
   long long ldo;
   float* lse2;
   const float* kbias2;
-  int B, H, Sq, Skv, d, dpad, atoms, kstages, vstages, nkb;
+  int B, H, Sq, Skv, d, dpad, atoms, kstages, vstages, nkb, npv;
   float scale2;
 };
 
@@ -104,8 +109,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
   uint64_t* v_empty = bars + 7;
   uint64_t* bar_S = bars + 9;
   uint64_t* bar_P = bars + 11;
-  uint64_t* bar_PV = bars + 13;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* bar_PV = bars + 13;  // [2]: PV(j) commits to bar_PV[j & 1]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 15);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
@@ -119,11 +124,12 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       ptx::mbar_init(&k_full[s], 1);
       ptx::mbar_init(&k_empty[s], 1);
       ptx::mbar_init(&v_full[s], 1);
-      ptx::mbar_init(&v_empty[s], 1);
+      ptx::mbar_init(&v_empty[s], (uint32_t)p.npv);
       ptx::mbar_init(&bar_S[s], 1);
       ptx::mbar_init(&bar_P[s], 256);
     }
-    ptx::mbar_init(bar_PV, 1);
+    ptx::mbar_init(&bar_PV[0], (uint32_t)p.npv);
+    ptx::mbar_init(&bar_PV[1], (uint32_t)p.npv);
     ptx::fence_barrier_init();
   }
   if (warp == 8) {
@@ -135,7 +141,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   const uint32_t tS = tmem_base;         // 2 x 128 columns
-  const uint32_t tO = tmem_base + 256u;  // dpad columns
+  const uint32_t tO = tmem_base + 256u;  // npv x dpad columns (one accumulator per PV issuer)
 
   if (warp == 9) {
     // ===================== TMA producer =====================
@@ -158,19 +164,19 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       }
     }
   } else if (warp == 8) {
-    // ===================== MMA issuer =====================
+    // ===================== QK^T issuer =====================
     if (lane == 0) {
       const uint32_t idescS = ptx::umma_idesc_bf16(128, 0, 0);
-      const uint32_t idescO = ptx::umma_idesc_bf16(p.dpad, 0, 1);
       const uint64_t dQ = ptx::umma_desc_sw128(ptx::smem_u32(sQ), 0u, 1024u);
       const uint64_t dK0 = ptx::umma_desc_sw128(ptx::smem_u32(sK), 0u, 1024u);
-      const uint64_t dV0 = ptx::umma_desc_sw128(ptx::smem_u32(sV), kAtom128, 1024u);  // MN-major: LBO = atom stride
-      const uint64_t dP0 = ptx::umma_desc_sw128(ptx::smem_u32(sP), 0u, 1024u);
       const uint32_t tile16 = tile_bytes >> 4, atom16 = kAtom128 >> 4;
       const int ksteps = p.dpad / 16;
-      int ks = 0, vs = 0;
-      uint32_t kph = 0, vph = 0;
-      auto issue_S = [&](int j) {
+      int ks = 0;
+      uint32_t kph = 0;
+      ptx::mbar_wait(barQ, 0);
+      for (int j = 0; j < p.nkb; ++j) {
+        // S buffer j&1 was last read by softmax(j-2): its arrival on bar_P comes after its TMEM loads
+        if (j >= 2) ptx::mbar_wait_sleep(&bar_P[j & 1], (uint32_t)(((j - 2) >> 1) & 1));
         ptx::mbar_wait_sleep(&k_full[ks], kph);
         ptx::tc_fence_after();
         mma_ksteps<false>(tS + (uint32_t)(j & 1) * 128u, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS, ksteps,
@@ -178,19 +184,30 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
         ptx::umma_commit(&k_empty[ks]);
         ptx::umma_commit(&bar_S[j & 1]);
         if (++ks == p.kstages) { ks = 0; kph ^= 1u; }
-      };
-      ptx::mbar_wait(barQ, 0);
-      issue_S(0);
+      }
+    }
+  } else if (warp >= 10) {
+    // ===================== PV issuers: issuer hv owns k-steps [hv*8/npv, (hv+1)*8/npv) and accumulator hv ============
+    const int hv = warp - 10;
+    if (lane == 0 && hv < p.npv) {
+      const uint32_t idescO = ptx::umma_idesc_bf16(p.dpad, 0, 1);
+      const uint64_t dV0 = ptx::umma_desc_sw128(ptx::smem_u32(sV), kAtom128, 1024u);  // MN-major: LBO = atom stride
+      const uint64_t dP0 = ptx::umma_desc_sw128(ptx::smem_u32(sP), 0u, 1024u);
+      const uint32_t tile16 = tile_bytes >> 4, atom16 = kAtom128 >> 4;
+      const int nsteps = 8 / p.npv;
+      const uint32_t tOh = tO + (uint32_t)(hv * p.dpad);
+      const uint32_t a_off = (p.npv == 2) ? (uint32_t)hv * atom16 : 0u;   // P atom = key half
+      const uint32_t b_off = (p.npv == 2) ? (uint32_t)hv * 4u * 128u : 0u;  // 16 key rows = 2048 B of an MN-major V atom
+      int vs = 0;
+      uint32_t vph = 0;
       for (int j = 0; j < p.nkb; ++j) {
-        // S buffer (j+1)&1 was last read by softmax(j-1), whose completion (bar_P) was observed in iteration j-1
-        if (j + 1 < p.nkb) issue_S(j + 1);
         ptx::mbar_wait_sleep(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
         ptx::mbar_wait_sleep(&v_full[vs], vph);
         ptx::tc_fence_after();
-        mma_ksteps<true>(tO, dP0 + (uint32_t)(j & 1) * 2u * atom16, atom16, dV0 + (uint32_t)vs * tile16, 0u, idescO, 8,
-                         j > 0 ? 1u : 0u);
+        mma_ksteps<true>(tOh, dP0 + (uint32_t)(j & 1) * 2u * atom16 + a_off, atom16, dV0 + (uint32_t)vs * tile16 + b_off, 0u,
+                         idescO, nsteps, j > 0 ? 1u : 0u);
         ptx::umma_commit(&v_empty[vs]);
-        ptx::umma_commit(bar_PV);
+        ptx::umma_commit(&bar_PV[j & 1]);
         if (++vs == p.vstages) { vs = 0; vph ^= 1u; }
       }
     }
@@ -242,14 +259,17 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       if (j == 0) {
         m_used = mx;
       } else {
-        ptx::mbar_wait_sleep(bar_PV, (uint32_t)((j - 1) & 1), 20);  // O holds blocks 0..j-1; P buffer j&1 is free again
-        ptx::tc_fence_after();
+        // P buffer j&1 was last read by PV(j-2). PV(j-1) may still be running: it only has to be waited for in the
+        // rare case that O must be rescaled (the lazy threshold), so the exp pass below overlaps it.
+        if (j >= 2) ptx::mbar_wait_sleep(&bar_PV[j & 1], (uint32_t)(((j - 2) >> 1) & 1), 20);
         const bool need = mx > m_used + 8.0f;
         if (__any_sync(0xffffffffu, need)) {
+          ptx::mbar_wait_sleep(&bar_PV[(j - 1) & 1], (uint32_t)(((j - 1) >> 1) & 1), 20);  // O holds blocks 0..j-1
+          ptx::tc_fence_after();
           const float alpha = need ? ptx::ex2_approx(m_used - mx) : 1.0f;
           if (need) m_used = mx;
           l *= alpha;
-          for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {  // the two warps of a row interleave 16-column chunks
+          for (int c0 = half * 16; c0 < p.npv * p.dpad; c0 += 32) {  // the two warps of a row interleave 16-column chunks
             uint32_t v[16];
             ptx::tmem_ld_32x16(tO + lane_base + c0, v);
             ptx::tmem_ld_wait();
@@ -290,7 +310,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
     sL[half * 128 + row] = l;
     ptx::named_bar_sync(1, 256);
     l += sL[(half ^ 1) * 128 + row];
-    ptx::mbar_wait(bar_PV, (uint32_t)((p.nkb - 1) & 1));
+    if (p.nkb >= 2) ptx::mbar_wait(&bar_PV[(p.nkb - 2) & 1], (uint32_t)(((p.nkb - 2) >> 1) & 1));
+    ptx::mbar_wait(&bar_PV[(p.nkb - 1) & 1], (uint32_t)(((p.nkb - 1) >> 1) & 1));
     ptx::tc_fence_after();
     const int q = q0 + row;
     const bool valid = q < p.Sq;
@@ -299,6 +320,13 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
     for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {
       uint32_t v[16];
       ptx::tmem_ld_32x16(tO + lane_base + c0, v);
+      if (p.npv == 2) {
+        uint32_t v2[16];
+        ptx::tmem_ld_32x16(tO + lane_base + (uint32_t)p.dpad + c0, v2);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(u2f(v[i]) + u2f(v2[i]));
+      }
       ptx::tmem_ld_wait();
       if (valid) {
 #pragma unroll
@@ -326,12 +354,14 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
 }
 
 // =============================================== backward ===============================================
-// 320 threads: warps 0-7 = compute (warp w and w+4 own the same 32 rows and split the columns of a block in halves; no
-// row reductions are needed in backward because lse and D are inputs), warp 8 = tcgen05.mma issuer + TMEM owner,
-// warp 9 = TMA producer. With nbuf = 2 (head dim <= 128) S / dP are double-buffered in TMEM and P^T / dS^T in shared
+// 416 threads: warps 0-7 = compute (warp w and w+4 own the same 32 rows and split the columns of a block in halves; no
+// row reductions are needed in backward because lse and D are inputs), warp 9 = TMA producer, and FOUR tcgen05.mma
+// issuers — warp 8 scores (+ TMEM owner), warp 10 dP, warp 11 first accumulator (dK / dQ), warp 12 second accumulator
+// (dV, mode 0) — because one thread issues at most one MMA per ~63 ns (see the forward kernel's note) and a block
+// needs 14 of them. With nbuf = 2 (head dim <= 128) S / dP are double-buffered in TMEM and P^T / dS^T in shared
 // memory, so the tensor pipe computes block i+1's scores and block i-1's accumulations while the compute warps run
 // the exp2 / dS arithmetic of block i.
-constexpr int kBwdThreads = 320;
+constexpr int kBwdThreads = 416;
 constexpr int kBwdMaxStages = 4;
 
 struct BwdParams {
@@ -383,14 +413,15 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     ptx::tma_prefetch_desc(&p.mapC1);
     ptx::tma_prefetch_desc(&p.mapC2);
     ptx::mbar_init(barR, 1);
+    constexpr uint32_t kAccIssuers = (MODE == 0) ? 2u : 1u;
     for (int s = 0; s < kBwdMaxStages; ++s) {
       ptx::mbar_init(&c_full[s], 1);
-      ptx::mbar_init(&c_empty[s], 1);
+      ptx::mbar_init(&c_empty[s], kAccIssuers);
     }
     for (int s = 0; s < 2; ++s) {
-      ptx::mbar_init(&bar_SdP[s], 1);
+      ptx::mbar_init(&bar_SdP[s], 2);
       ptx::mbar_init(&bar_PdS[s], 256);
-      ptx::mbar_init(&bar_acc[s], 1);
+      ptx::mbar_init(&bar_acc[s], kAccIssuers);
     }
     ptx::fence_barrier_init();
   }
@@ -420,50 +451,52 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         tma_tile(sC2 + (size_t)s * ctile, &p.mapC2, &c_full[s], p.atoms, catom, i * p.bc, h, b);
       }
     }
-  } else if (warp == 8) {
+  } else if (warp == 8 || warp == 10) {
+    // ===================== score issuers: warp 8  S = R1 C1^T,  warp 10  dP = R2 C2^T =====================
     if (lane == 0) {
+      const bool second = warp == 10;
       const uint32_t idescS = ptx::umma_idesc_bf16(p.bc, 0, 0);
-      const uint32_t idescA = ptx::umma_idesc_bf16(p.dpad, 0, 1);
-      const uint64_t dR1 = ptx::umma_desc_sw128(ptx::smem_u32(sR1), 0u, 1024u);
-      const uint64_t dR2 = ptx::umma_desc_sw128(ptx::smem_u32(sR2), 0u, 1024u);
-      const uint64_t dC1k = ptx::umma_desc_sw128(ptx::smem_u32(sC1), 0u, 1024u);      // column tiles as K-major B (scores)
-      const uint64_t dC2k = ptx::umma_desc_sw128(ptx::smem_u32(sC2), 0u, 1024u);
-      const uint64_t dC1m = ptx::umma_desc_sw128(ptx::smem_u32(sC1), catom, 1024u);   // ... and as MN-major B (accumulate)
-      const uint64_t dC2m = ptx::umma_desc_sw128(ptx::smem_u32(sC2), catom, 1024u);
-      const uint64_t dDS0 = ptx::umma_desc_sw128(ptx::smem_u32(sDS), 0u, 1024u);
-      const uint64_t dPT0 = ptx::umma_desc_sw128(ptx::smem_u32(sPT), 0u, 1024u);
-      const uint32_t atom16 = kAtom128 >> 4, catom16 = catom >> 4, ctile16 = ctile >> 4, ptile16 = ptile >> 4;
+      const uint64_t dR = ptx::umma_desc_sw128(ptx::smem_u32(second ? sR2 : sR1), 0u, 1024u);
+      const uint64_t dCk = ptx::umma_desc_sw128(ptx::smem_u32(second ? sC2 : sC1), 0u, 1024u);  // column tile as K-major B
+      const uint32_t atom16 = kAtom128 >> 4, catom16 = catom >> 4, ctile16 = ctile >> 4;
       const int ksteps = p.dpad / 16;
-      const int k2 = p.bc / 16;
-      int ss = 0, as = 0;       // stage of the next S/dP issue, of the next accumulate
+      int ss = 0;
       uint32_t sph = 0;
-      auto issue_SdP = [&](int i) {
+      ptx::mbar_wait(barR, 0);
+      for (int i = 0; i < p.ncb; ++i) {
+        const int buf = i & (NBUF - 1);
+        // S/dP buffer `buf` was last read by compute(i - NBUF), which arrives on bar_PdS after its TMEM loads
+        if (i >= NBUF) ptx::mbar_wait_sleep(&bar_PdS[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
         ptx::mbar_wait_sleep(&c_full[ss], sph);
         ptx::tc_fence_after();
-        const int buf = i & (NBUF - 1);
-        const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc;
-        mma_ksteps<false>(tSi, dR1, atom16, dC1k + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
-        mma_ksteps<false>(tSi + (uint32_t)p.bc, dR2, atom16, dC2k + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
+        const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + (second ? (uint32_t)p.bc : 0u);
+        mma_ksteps<false>(tSi, dR, atom16, dCk + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
         ptx::umma_commit(&bar_SdP[buf]);
         if (++ss == p.stages) { ss = 0; sph ^= 1u; }
-      };
-      ptx::mbar_wait(barR, 0);
-      issue_SdP(0);
+      }
+    }
+  } else if (warp == 11 || warp == 12) {
+    // ===================== accumulate issuers: warp 11  A1 += dS C1,  warp 12 (mode 0)  A2 += P^T C2 =====================
+    if (lane == 0 && (warp == 11 || MODE == 0)) {
+      const bool second = warp == 12;
+      const uint32_t idescA = ptx::umma_idesc_bf16(p.dpad, 0, 1);
+      const uint64_t dCm = ptx::umma_desc_sw128(ptx::smem_u32(second ? sC2 : sC1), catom, 1024u);  // MN-major B
+      const uint64_t dA0 = ptx::umma_desc_sw128(ptx::smem_u32(second ? sPT : sDS), 0u, 1024u);
+      const uint32_t atom16 = kAtom128 >> 4, ctile16 = ctile >> 4, ptile16 = ptile >> 4;
+      const int k2 = p.bc / 16;
+      const uint32_t tA = second ? tA2 : tA1;
+      int as = 0;
+      uint32_t aph = 0;
       for (int i = 0; i < p.ncb; ++i) {
-        // double-buffered: S/dP buffer (i+1)&1 was last read by compute(i-1), observed through bar_PdS in iteration i-1
-        if (NBUF == 2 && i + 1 < p.ncb) issue_SdP(i + 1);
         const int buf = i & (NBUF - 1);
         ptx::mbar_wait_sleep(&bar_PdS[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
+        ptx::mbar_wait_sleep(&c_full[as], aph);  // already complete (the scores of block i used it); orders the async proxy
         ptx::tc_fence_after();
-        mma_ksteps<true>(tA1, dDS0 + (uint32_t)buf * ptile16, atom16, dC1m + (uint32_t)as * ctile16, 0u, idescA, k2,
+        mma_ksteps<true>(tA, dA0 + (uint32_t)buf * ptile16, atom16, dCm + (uint32_t)as * ctile16, 0u, idescA, k2,
                          i > 0 ? 1u : 0u);
-        if (MODE == 0)
-          mma_ksteps<true>(tA2, dPT0 + (uint32_t)buf * ptile16, atom16, dC2m + (uint32_t)as * ctile16, 0u, idescA, k2,
-                           i > 0 ? 1u : 0u);
         ptx::umma_commit(&c_empty[as]);
         ptx::umma_commit(&bar_acc[buf]);
-        if (++as == p.stages) as = 0;
-        if (NBUF == 1 && i + 1 < p.ncb) issue_SdP(i + 1);
+        if (++as == p.stages) { as = 0; aph ^= 1u; }
       }
     }
   } else {
@@ -709,6 +742,7 @@ extern "C" int sdb_attn_fwd(const void* q, long long ldq, const void* k, long lo
   p.dpad = (d + 15) & ~15;
   p.atoms = (d + 63) / 64;
   p.nkb = (Skv + 127) / 128;
+  p.npv = (256 + 2 * p.dpad <= 512) ? 2 : 1;  // two PV accumulators when they fit beside the double-buffered S
   p.scale2 = scale * 1.4426950408889634f;
   if (kbias2 != nullptr && p.nkb > kMaxBiasBlocks)
     return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_fwd: a per-key bias supports Skv <= %d (got %d)",

@@ -16,7 +16,8 @@ __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, u
       : "memory");
 }
 
-// mode: 0 SS (B K-major), 1 SS (B MN-major), 2 TS (B K-major), 3 TS (B MN-major), 4 SS alternating accumulators
+// mode: 0 SS (B K-major), 1 SS (B MN-major), 2 TS (B K-major), 3 TS (B MN-major), 4 SS alternating accumulators,
+//       5 SS with TWO issuing warps (separate accumulators), 6 SS M=64, 7 TS with two issuing warps
 __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int n, int iters, long long* out) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
@@ -24,10 +25,11 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int n, int iters
   uint8_t* sA = smem;              // 128 x 64 bf16 (16 KB)
   uint8_t* sB = smem + 16384;      // 256 x 64 bf16 (32 KB) K-major, or 4 boxes of 64x64 MN-major
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 16384 + 32768);
-  uint32_t* tptr = reinterpret_cast<uint32_t*>(bar + 1);
+  uint32_t* tptr = reinterpret_cast<uint32_t*>(bar + 2);
   for (int i = threadIdx.x; i < (16384 + 32768) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0x3c003c00u + i;
   if (threadIdx.x == 0) {
     ptx::mbar_init(bar, 1);
+    ptx::mbar_init(bar + 1, 1);
     ptx::fence_barrier_init();
   }
   if (threadIdx.x < 32) {
@@ -39,32 +41,35 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int mode, int n, int iters
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem = *tptr;
-  if (threadIdx.x == 0) {
+  if (threadIdx.x == 0 || (threadIdx.x == 32 && (mode == 5 || mode == 7))) {
+    const int w = threadIdx.x >> 5;
+    uint64_t* mybar = bar + w;
     const bool b_mn = (mode & 1) && mode < 4;
-    const bool ts = (mode == 2 || mode == 3);
-    const uint32_t idesc = ptx::umma_idesc_bf16(n, 0, b_mn ? 1 : 0);
+    const bool ts = (mode == 2 || mode == 3 || mode == 7);
+    const uint32_t idesc = ptx::umma_idesc_bf16(n, 0, b_mn ? 1 : 0, mode == 6 ? 64 : 128);
+    const uint32_t tD = tmem + (uint32_t)w * 128u;  // second issuer: its own accumulator (N <= 128 there)
     const uint64_t dA = ptx::umma_desc_sw128(ptx::smem_u32(sA), 0u, 1024u);
     const uint64_t dB = ptx::umma_desc_sw128(ptx::smem_u32(sB), b_mn ? 8192u : 0u, 1024u);
-    const uint32_t tA = tmem + 256u;  // A operand region for TS (garbage values: timing only)
+    const uint32_t tA = tmem + 256u + (uint32_t)w * 64u;  // A operand region for TS (garbage values: timing only)
     // warm-up
-    for (int k = 0; k < 4; ++k) ptx::umma_bf16(tmem, dA + 2u * k, dB + (b_mn ? 128u * k : 2u * k), idesc, 1u);
-    ptx::umma_commit(bar);
-    ptx::mbar_wait(bar, 0);
+    for (int k = 0; k < 4; ++k) ptx::umma_bf16(tD, dA + 2u * k, dB + (b_mn ? 128u * k : 2u * k), idesc, 1u);
+    ptx::umma_commit(mybar);
+    ptx::mbar_wait(mybar, 0);
     const long long t0 = clock64();
     for (int it = 0; it < iters; ++it) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
         const uint64_t db = dB + (b_mn ? 128u * k : 2u * k);
-        const uint32_t d = (mode == 4) ? tmem + (uint32_t)((it * 4 + k) & 1) * 256u : tmem;
+        const uint32_t d = (mode == 4) ? tmem + (uint32_t)((it * 4 + k) & 1) * 256u : tD;
         if (ts) umma_bf16_ts(d, tA + 8u * k, db, idesc, 1u);
         else ptx::umma_bf16(d, dA + 2u * k, db, idesc, 1u);
       }
     }
     const long long t_issue = clock64();
-    ptx::umma_commit(bar);
-    ptx::mbar_wait(bar, 1);
+    ptx::umma_commit(mybar);
+    ptx::mbar_wait(mybar, 1);
     const long long t1 = clock64();
-    if (blockIdx.x == 0) {
+    if (blockIdx.x == 0 && w == 0) {
       out[0] = t1 - t0;
       out[1] = t_issue - t0;
     }
@@ -83,13 +88,13 @@ int main() {
   const int smem = 16384 + 32768 + 1024 + 64;
   cudaFuncSetAttribute(rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const int iters = 2000;
-  const char* names[5] = {"SS  B K-major ", "SS  B MN-major", "TS  B K-major ", "TS  B MN-major", "SS  alt-accum "};
+  const char* names[8] = {"SS  B K-major ", "SS  B MN-major", "TS  B K-major ", "TS  B MN-major", "SS  alt-accum ", "SS  2 issuers ", "SS  M=64      ", "TS  2 issuers "};
   const int ns[] = {16, 32, 48, 64, 96, 128, 160, 192, 256};
-  for (int grid : {1, 148}) {
+  for (int grid : {148}) {
     printf("grid %d (cycles per MMA M=128 K=16; total incl. drain / issue-only)\n", grid);
-    for (int mode = 0; mode < 5; ++mode) {
+    for (int mode : {0, 2, 5, 6, 7}) {
       for (int n : ns) {
-        if (mode == 4 && n > 256) continue;
+        if ((mode == 5 || mode == 7) && n > 128) continue;
         rate_kernel<<<grid, 128, smem>>>(mode, n, iters, out);
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) {
