@@ -122,11 +122,11 @@ typedef struct {
   int tap_dw[SDB_MAX_TAPS];
   int tap_brow[SDB_MAX_TAPS];
   int outW, outH, outN; /* pixel space */
-  int bw, bh, bn;       /* pixel box: 128 pixels (FWD) / 64 pixels (WGRAD) */
+  int bw, bh, bn;       /* pixel box: 128 * m_halves pixels (FWD) / 64 pixels (WGRAD) */
   int M;                /* WGRAD: rows of dW per tap (Cin). FWD: ignored (pixels) */
   int N;                /* output columns */
   int K;                /* FWD: reduction length per tap (channels of A) */
-  int block_n;          /* N tile width, multiple of 16, <= 256 (multiple of 64 when B is MN-major) */
+  int block_n;          /* N tile width, multiple of 16, <= 256 */
   int splits;           /* WGRAD only */
   void* d;
   long long ldd;
@@ -138,6 +138,7 @@ typedef struct {
   long long ldt;
   const void* residual;
   long long ldr;
+  int m_halves;         /* sdb_gemm_tc: M tile = 128 * m_halves rows (1 or 2; 0 = 1). Two halves share every B stage */
 } sdb_gemm_desc;
 
 int sdb_gemm_tc(const sdb_gemm_desc* desc, cudaStream_t stream);

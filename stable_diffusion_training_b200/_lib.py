@@ -32,7 +32,7 @@ class GemmDesc(C.Structure):
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("block_n", C.c_int), ("splits", C.c_int),
         ("d", C.c_void_p), ("ldd", C.c_longlong), ("d_strideW", C.c_longlong), ("d_strideH", C.c_longlong),
         ("d_strideN", C.c_longlong), ("bias", C.c_void_p), ("temb", C.c_void_p), ("ldt", C.c_longlong),
-        ("residual", C.c_void_p), ("ldr", C.c_longlong),
+        ("residual", C.c_void_p), ("ldr", C.c_longlong), ("m_halves", C.c_int),
     ]
 
 
@@ -107,6 +107,13 @@ def lib() -> C.CDLL:
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
+        # SDB_SKIP=sym1,sym2 (timing experiments only, tools/ablate.sh): the named entry points return 0 without
+        # launching, so the marginal cost of an operator class inside a CUDA-graph replay can be measured. Results
+        # are then meaningless; nothing in the product or the tests sets it.
+        skip = [x for x in os.environ.get("SDB_SKIP", "").split(",") if x]
+        for name in skip:
+            if name in SIGNATURES:
+                setattr(l, name, (lambda *a, **k: 0))
         _lib = l
     return _lib
 

@@ -22,9 +22,17 @@
 #include <cstdlib>
 #include <mutex>
 
+// The SDB_GEMM_DBG timing experiments (skip TMA / stores / MMA; profiles/r1f_gemm_experiments.md) are compiled in only
+// with -DSDB_GEMM_EXPERIMENTS: the flag tests sit in the single-thread producer / issuer loops.
+#ifdef SDB_GEMM_EXPERIMENTS
+#define SDB_DBG(p, bit) ((p).dbg & (bit))
+#else
+#define SDB_DBG(p, bit) 0
+#endif
+
 namespace {
 
-constexpr int kThreads = 192;
+constexpr int kThreads = 224;                // warp 0 TMA, warp 1 MMA issuer (half 0), warps 2-5 epilogue, warp 6 MMA issuer (half 1)
 constexpr int kBlockK = 64;                 // bf16 elements per K block (one 128-byte swizzle row)
 constexpr uint32_t kAStageBytes = 128 * 128;  // 16 KB: 128 rows x 128 B, or two 64-row MN-major boxes
 constexpr uint32_t kBoxBytes = 64 * 128;      // one 64-row box
@@ -41,7 +49,8 @@ struct alignas(64) TcParams {
   int M, N, K, BN;
   int tiles_m, tiles_n, total_tiles, kblocks;
   int splits, pb_per_split, total_pb;
-  int stages, dbg;
+  int stages, dbg, mt;
+  uint32_t a_stage_bytes;
   uint32_t b_stage_bytes, stage_bytes;
   void* d;
   long long ldd, dsW, dsH, dsN;
@@ -83,7 +92,7 @@ __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
     r /= p.tiles_n;
     int m_tile = r % p.tiles_m;
     ti.tap = r / p.tiles_m;
-    ti.m_off = m_tile * 128;
+    ti.m_off = m_tile * 128 * p.mt;
     ti.n_off = n_tile * p.BN;
     ti.kb_begin = split * p.pb_per_split;
     int kb_end = min(p.total_pb, ti.kb_begin + p.pb_per_split);
@@ -96,7 +105,10 @@ __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
   return ti;
 }
 
-template <int MODE>
+// MT = number of 128-row halves of the M tile (1: 128 x BN with two accumulators double-buffered across tiles;
+// 2: 256 x BN, one accumulator and one issuing warp per half — the B stage is fetched once for 256 rows, which is what
+// matters when the SM's ingest of TMA bytes, not the tensor pipe, paces the main loop).
+template <int MODE, int MT>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ TcParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
@@ -117,7 +129,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     ptx::tma_prefetch_desc(&p.mapB);
     for (int s = 0; s < p.stages; ++s) {
       ptx::mbar_init(&full_bar[s], 1);
-      ptx::mbar_init(&empty_bar[s], 1);
+      ptx::mbar_init(&empty_bar[s], MT);
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(&tmem_full[a], 1);
@@ -144,14 +156,14 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         for (int it = 0; it < ti.num_k; ++it) {
           ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
-          uint8_t* sb = sa + kAStageBytes;
-          if (p.dbg & 1) {  // experiment: no TMA traffic (SDB_GEMM_DBG=1)
+          uint8_t* sb = sa + p.a_stage_bytes;
+          if (SDB_DBG(p, 1)) {  // experiment: no TMA traffic (SDB_GEMM_DBG=1)
             ptx::mbar_expect_tx(&full_bar[stage], 0u);
           } else if (MODE == SDB_GEMM_FWD) {
             const int tap = it / p.kblocks;
             const int kb = it - tap * p.kblocks;
             const uint32_t bbytes = p.b_mn ? (uint32_t)ti.nboxes * kBoxBytes : p.b_stage_bytes;
-            ptx::mbar_expect_tx(&full_bar[stage], kAStageBytes + bbytes);
+            ptx::mbar_expect_tx(&full_bar[stage], p.a_stage_bytes + bbytes);
             ptx::tma_load_4d(sa, &p.mapA[p.tap_src[tap]], &full_bar[stage], kb * kBlockK, ti.w0 + p.tap_dw[tap],
                              ti.h0 + p.tap_dh[tap], ti.n0);
             if (p.b_mn) {
@@ -168,9 +180,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             const int ih = r % p.th;
             const int in = r / p.th;
             const int pw0 = iw * p.bw, ph0 = ih * p.bh, pn0 = in * p.bn;
-            ptx::mbar_expect_tx(&full_bar[stage], 2 * kBoxBytes + (uint32_t)ti.nboxes * kBoxBytes);
+            ptx::mbar_expect_tx(&full_bar[stage], p.a_stage_bytes + (uint32_t)ti.nboxes * kBoxBytes);
             const CUtensorMap* ma = &p.mapA[p.tap_src[ti.tap]];
-            for (int i = 0; i < 2; ++i)
+            for (int i = 0; i < 2 * MT; ++i)
               ptx::tma_load_4d(sa + i * kBoxBytes, ma, &full_bar[stage], ti.m_off + 64 * i, pw0 + p.tap_dw[ti.tap],
                                ph0 + p.tap_dh[ti.tap], pn0);
             for (int j = 0; j < ti.nboxes; ++j)
@@ -183,9 +195,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
+  } else if (warp == 1 || warp == 6) {
+    // ===================== MMA issuers: warp 1 -> rows 0..127 of the tile, warp 6 -> rows 128..255 (MT == 2) ==========
+    const int half = (warp == 6) ? 1 : 0;
+    if (lane == 0 && half < MT) {
       int stage = 0;
       uint32_t phase = 0;
       int tile_count = 0;
@@ -195,22 +208,25 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       const uint32_t b_lbo = b_mn ? kBoxBytes : 0u, b_kadv = b_mn ? 2048u : 32u;
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tile_count) {
         const Tile ti = decode_tile(p, t);
-        const int acc = tile_count & 1;
-        const uint32_t acc_phase = (uint32_t)(tile_count >> 1) & 1u;
+        // MT == 1: accumulators alternate per tile; MT == 2: accumulator = half, reused every tile
+        const int acc = (MT == 1) ? (tile_count & 1) : half;
+        const uint32_t acc_phase = (MT == 1) ? ((uint32_t)(tile_count >> 1) & 1u) : ((uint32_t)tile_count & 1u);
         ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1u);
         ptx::tc_fence_after();
         const uint32_t tmem_d = tmem_base + (uint32_t)acc * kAccCols;
         const uint32_t idesc = ptx::umma_idesc_bf16(ti.umma_n, a_mn, b_mn);
+        // a WGRAD half whose dW rows all lie past M has nothing to compute (it still takes part in the barriers)
+        const bool live = (MODE != SDB_GEMM_WGRAD) || (ti.m_off + half * 128 < p.M);
         for (int it = 0; it < ti.num_k; ++it) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
-          const uint32_t sa = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes);
-          const uint32_t sb = sa + kAStageBytes;
+          const uint32_t sa = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes) + (uint32_t)half * kAStageBytes;
+          const uint32_t sb = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes) + p.a_stage_bytes;
 #pragma unroll
           for (int ks = 0; ks < kBlockK / 16; ++ks) {
             const uint64_t da = ptx::umma_desc_sw128(sa + ks * a_kadv, a_lbo, 1024u);
             const uint64_t db = ptx::umma_desc_sw128(sb + ks * b_kadv, b_lbo, 1024u);
-            if (!(p.dbg & 4)) ptx::umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+            if (live && !SDB_DBG(p, 4)) ptx::umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
           }
           ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
           if (++stage == p.stages) {
@@ -224,12 +240,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
-    const int row = q * 32 + lane;
     int tile_count = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tile_count) {
       const Tile ti = decode_tile(p, t);
-      const int acc = tile_count & 1;
-      const uint32_t acc_phase = (uint32_t)(tile_count >> 1) & 1u;
+     for (int half = 0; half < MT; ++half) {
+      const int row = half * 128 + q * 32 + lane;
+      const int acc = (MT == 1) ? (tile_count & 1) : half;
+      const uint32_t acc_phase = (MT == 1) ? ((uint32_t)(tile_count >> 1) & 1u) : ((uint32_t)tile_count & 1u);
       ptx::mbar_wait(&tmem_full[acc], acc_phase);
       ptx::tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kAccCols;
@@ -240,7 +257,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const int hi = r2 % p.bh;
         const int ni = r2 / p.bh;
         const int w = ti.w0 + wi, h = ti.h0 + hi, n = ti.n0 + ni;
-        const bool valid = (w < p.W) && (h < p.H) && (n < p.NI) && !(p.dbg & 2);
+        const bool valid = (w < p.W) && (h < p.H) && (n < p.NI) && !SDB_DBG(p, 2);
         const long long grow = ((long long)n * p.H + h) * p.W + w;
         __nv_bfloat16* out = reinterpret_cast<__nv_bfloat16*>(p.d) + (long long)n * p.dsN + (long long)h * p.dsH +
                              (long long)w * p.dsW + ti.n_off;
@@ -290,7 +307,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         }
       } else {
         const int m = ti.m_off + row;
-        const bool valid = (m < p.M) && !(p.dbg & 2);
+        const bool valid = (m < p.M) && !SDB_DBG(p, 2);
         float* out = reinterpret_cast<float*>(p.d) + ((long long)p.tap_brow[ti.tap] + m) * p.ldd + ti.n_off;
         for (int c0 = 0; c0 < ti.nw; c0 += 32) {
           uint32_t v[32];
@@ -317,6 +334,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       }
       ptx::tc_fence_before();
       ptx::mbar_arrive(&tmem_empty[acc]);
+     }
     }
   }
 
@@ -380,9 +398,12 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
   SDB_CHECK_ARG(d->outW > 0 && d->outH > 0 && d->outN > 0, "sdb_gemm_tc: bad pixel space");
   const int box_pixels = d->bw * d->bh * d->bn;
   const bool wgrad = d->mode == SDB_GEMM_WGRAD;
-  SDB_CHECK_ARG(d->bw > 0 && d->bh > 0 && d->bn > 0 && box_pixels == (wgrad ? 64 : 128) && d->bw <= 256 &&
+  const int mt = d->m_halves == 2 ? 2 : 1;
+  SDB_CHECK_ARG(d->m_halves >= 0 && d->m_halves <= 2, "sdb_gemm_tc: m_halves must be 0, 1 or 2");
+  SDB_CHECK_ARG(d->bw > 0 && d->bh > 0 && d->bn > 0 && box_pixels == (wgrad ? 64 : 128 * mt) && d->bw <= 256 &&
                     d->bh <= 256 && d->bn <= 256,
-                "sdb_gemm_tc: pixel box %dx%dx%d must hold exactly %d pixels", d->bw, d->bh, d->bn, wgrad ? 64 : 128);
+                "sdb_gemm_tc: pixel box %dx%dx%d must hold exactly %d pixels", d->bw, d->bh, d->bn,
+                wgrad ? 64 : 128 * mt);
   SDB_CHECK_ARG(d->N > 0 && d->block_n >= 16 && d->block_n <= 256 && d->block_n % 16 == 0,
                 "sdb_gemm_tc: block_n %d must be a multiple of 16 in [16,256]", d->block_n);
   SDB_CHECK_ARG(d->d != nullptr, "sdb_gemm_tc: null output");
@@ -393,6 +414,8 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
   TcParams p;
   memset(&p, 0, sizeof(p));
   p.mode = d->mode;
+  p.mt = mt;
+  p.a_stage_bytes = (uint32_t)mt * kAStageBytes;
   p.ntaps = d->ntaps;
   for (int t = 0; t < d->ntaps; ++t) {
     p.tap_src[t] = d->tap_src[t];
@@ -452,7 +475,7 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
                   "sdb_gemm_tc: WGRAD needs N %% 4 == 0, ldd %% 4 == 0 and a 16-byte aligned output");
     p.b_mn = 1;
     p.M = d->M;
-    p.tiles_m = sdb::ceil_div(p.M, 128);
+    p.tiles_m = sdb::ceil_div(p.M, 128 * mt);
     p.total_pb = p.tw * p.th * p.tn;
     int splits = d->splits < 1 ? 1 : d->splits;
     if (splits > p.total_pb) splits = p.total_pb;
@@ -464,7 +487,7 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     p.b_stage_bytes = (uint32_t)(((p.BN + 63) / 64) * kBoxBytes);
   }
   p.b_stage_bytes = (p.b_stage_bytes + 1023u) & ~1023u;
-  p.stage_bytes = kAStageBytes + p.b_stage_bytes;
+  p.stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
   const uint32_t budget = 200 * 1024;
   int stages = (int)(budget / p.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
@@ -477,16 +500,26 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
   static std::once_flag attr_once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(attr_once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_FWD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    const int bytes = 227 * 1024;
+    attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_FWD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
     if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_WGRAD>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+      attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_FWD, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_WGRAD, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(gemm_tc_kernel<SDB_GEMM_WGRAD, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   });
   if (attr_err != cudaSuccess)
     return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
 
   const int grid = p.total_tiles < sdb::kNumSMs ? p.total_tiles : sdb::kNumSMs;
-  if (wgrad) gemm_tc_kernel<SDB_GEMM_WGRAD><<<grid, kThreads, smem_bytes, stream>>>(p);
-  else gemm_tc_kernel<SDB_GEMM_FWD><<<grid, kThreads, smem_bytes, stream>>>(p);
+  if (wgrad) {
+    if (mt == 2) gemm_tc_kernel<SDB_GEMM_WGRAD, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
+    else gemm_tc_kernel<SDB_GEMM_WGRAD, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
+  } else {
+    if (mt == 2) gemm_tc_kernel<SDB_GEMM_FWD, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
+    else gemm_tc_kernel<SDB_GEMM_FWD, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
+  }
   SDB_CUDA_LAUNCH_CHECK("sdb_gemm_tc");
   return SDB_OK;
 }

@@ -9,6 +9,7 @@
 // of channel vectors (so gamma/beta and the per-channel accumulators live in registers) and strides over pixel rows.
 #include "sdb_common.cuh"
 #include "../../include/sdb200.h"
+#include <cstdlib>
 
 namespace {
 
@@ -276,6 +277,301 @@ __global__ void gn_param_grad_kernel(const float2* __restrict__ chan_tot, float*
   dgamma[c] = t1;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Fused GroupNorm: ONE launch per direction. All CTAs of a sample are co-resident (grid <= occupancy x SMs, checked on
+// the host), so the statistics are exchanged through global memory behind a per-sample arrival counter instead of
+// ending the kernel: pass 1 (partial sums) -> counter -> every CTA folds the chunks' group partials in a fixed order
+// (deterministic) -> pass 2 (normalise) re-reads the rows it has just read (L1/L2 hits). Replaces the partial /
+// finalize / param-grad / apply chain above (3-4 launches whose dependent start-up latency dominated on the L2-sized
+// feature maps of this UNet); that chain remains the fallback when the grid cannot be co-resident.
+//   sync[b]      arrivals of sample b          sync[B]  arrivals of the whole grid (backward: parameter gradients)
+// The counters are zeroed by a memset node in front of the launch.
+__device__ __forceinline__ void gn_arrive_and_wait(unsigned int* counter, unsigned int expected) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    atomicAdd(counter, 1u);
+    while (*reinterpret_cast<volatile unsigned int*>(counter) < expected) __nanosleep(40);
+    __threadfence();
+  }
+  __syncthreads();
+}
+
+template <int KC, bool BWD, bool SILU>
+__global__ void __launch_bounds__(256, 2)
+gn_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy, float2* stats,
+                const float* __restrict__ gamma, const float* __restrict__ beta, const __nv_bfloat16* __restrict__ add,
+                __nv_bfloat16* __restrict__ out, float2* part_g, float2* part_c, float2* chan_tot,
+                float* __restrict__ dgamma, float* __restrict__ dbeta, unsigned int* sync, GnShape s, float eps) {
+  extern __shared__ float smem[];
+  float* s_a = smem;                       // [RL][C]
+  float* s_b = smem + (size_t)s.RL * s.C;  // [RL][C]
+  __shared__ float2 s_red[8][kGroups];
+  __shared__ float2 s_grp[kGroups];   // fwd: (mean, rstd) ; bwd: (mean_g(gamma dz), mean_g(gamma dz xhat))
+  __shared__ int s_last;
+  const int b = blockIdx.y, chunk = blockIdx.x;
+  const int nthr = blockDim.x;
+  const int tc = threadIdx.x % s.TC, rl = threadIdx.x / s.TC;
+  const int r0 = chunk * s.rows_per_chunk;
+  const int r1 = min(s.HW, r0 + s.rows_per_chunk);
+  const size_t base = (size_t)b * s.HW * s.C;
+
+  // ---------------- pass 1: per-channel partial sums of this chunk ----------------
+  {
+    float a0[KC][8], a1[KC][8], sc[KC][8], sh[KC][8], rs_[KC][8], xb[KC][8];
+#pragma unroll
+    for (int k = 0; k < KC; ++k)
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        a0[k][i] = 0.f; a1[k][i] = 0.f;
+        if (BWD) {
+          const int c = (tc + k * s.TC) * 8 + i;
+          const float2 st = stats[b * kGroups + c / s.cpg];
+          const float gm = gamma[c];
+          rs_[k][i] = st.y; xb[k][i] = -st.x * st.y;              // xhat = x*rs + xb
+          sc[k][i] = st.y * gm; sh[k][i] = fmaf(-st.x * st.y, gm, beta[c]);  // z = x*sc + sh
+        }
+      }
+    if (rl < s.RL) {
+      for (int r = r0 + rl; r < r1; r += kGnUnroll * s.RL) {
+        uint4 xr[kGnUnroll][KC], dr[kGnUnroll][KC];
+#pragma unroll
+        for (int u = 0; u < kGnUnroll; ++u) {
+          const int rr = r + u * s.RL;
+#pragma unroll
+          for (int k = 0; k < KC; ++k) {
+            const size_t off = base + (size_t)rr * s.C + (size_t)(tc + k * s.TC) * 8;
+            xr[u][k] = (rr < r1) ? sdb::ld_u4(x + off) : make_uint4(0u, 0u, 0u, 0u);
+            if (BWD) dr[u][k] = (rr < r1) ? sdb::ld_u4(dy + off) : make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kGnUnroll; ++u) {
+#pragma unroll
+          for (int k = 0; k < KC; ++k) {
+            float xv[8];
+            unpack8(xr[u][k], xv);
+            if (!BWD) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) { a0[k][i] += xv[i]; a1[k][i] = fmaf(xv[i], xv[i], a1[k][i]); }
+            } else {
+              float dv[8];
+              unpack8(dr[u][k], dv);  // rows past the chunk carry dy = 0: they add nothing
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float xh = fmaf(xv[i], rs_[k][i], xb[k][i]);
+                float dz = dv[i];
+                if (SILU) {
+                  const float z = fmaf(xv[i], sc[k][i], sh[k][i]);
+                  const float sg = sigmoid_f(z);
+                  dz *= sg * (1.0f + z * (1.0f - sg));
+                }
+                a0[k][i] += dz; a1[k][i] = fmaf(dz, xh, a1[k][i]);
+              }
+            }
+          }
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < KC; ++k)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int c = (tc + k * s.TC) * 8 + i;
+          s_a[rl * s.C + c] = a0[k][i];
+          s_b[rl * s.C + c] = a1[k][i];
+        }
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < s.C; c += nthr) {  // fold the row lanes into row 0 (a thread only touches column c)
+    float t0 = 0.f, t1 = 0.f;
+    for (int j = 0; j < s.RL; ++j) { t0 += s_a[j * s.C + c]; t1 += s_b[j * s.C + c]; }
+    if (BWD) {
+      part_c[((size_t)b * s.chunks + chunk) * s.C + c] = make_float2(t0, t1);
+      const float gm = gamma[c];
+      t0 *= gm; t1 *= gm;
+    }
+    s_a[c] = t0; s_b[c] = t1;
+  }
+  __syncthreads();
+  if (threadIdx.x < kGroups) {
+    float t0 = 0.f, t1 = 0.f;
+    for (int ci = 0; ci < s.cpg; ++ci) { t0 += s_a[threadIdx.x * s.cpg + ci]; t1 += s_b[threadIdx.x * s.cpg + ci]; }
+    part_g[((size_t)b * s.chunks + chunk) * kGroups + threadIdx.x] = make_float2(t0, t1);
+  }
+
+  // ---------------- exchange: wait for the other chunks of this sample ----------------
+  gn_arrive_and_wait(&sync[b], (unsigned int)s.chunks);
+  {
+    // full warps only (the block has 129..256 threads): warp `slice` folds chunks slice, slice + nslices, ...
+    const int g = threadIdx.x & 31, slice = threadIdx.x >> 5, nslices = nthr >> 5;
+    float t0 = 0.f, t1 = 0.f;
+    if (slice < nslices) {
+      for (int j = slice; j < s.chunks; j += nslices) {
+        const float2 q = __ldcg(&part_g[((size_t)b * s.chunks + j) * kGroups + g]);
+        t0 += q.x; t1 += q.y;
+      }
+      s_red[slice][g] = make_float2(t0, t1);
+    }
+    __syncthreads();
+    if (threadIdx.x < kGroups) {
+      t0 = 0.f; t1 = 0.f;
+      for (int j = 0; j < nslices; ++j) { t0 += s_red[j][g].x; t1 += s_red[j][g].y; }
+      const float inv_n = 1.0f / ((float)s.HW * (float)s.cpg);
+      if (!BWD) {
+        const float mean = t0 * inv_n;
+        const float var = fmaxf(0.0f, t1 * inv_n - mean * mean);
+        const float2 st = make_float2(mean, rsqrtf(var + eps));
+        s_grp[g] = st;
+        if (chunk == 0) stats[b * kGroups + g] = st;
+      } else {
+        s_grp[g] = make_float2(t0 * inv_n, t1 * inv_n);
+      }
+    }
+    if (BWD) {
+      // channel slice of this CTA: totals over the sample's chunks; the last CTA of the grid folds the samples
+      const int cps = (s.C + s.chunks - 1) / s.chunks;
+      for (int t = threadIdx.x; t < cps; t += nthr) {
+        const int c = chunk * cps + t;
+        if (c < s.C) {
+          float u0 = 0.f, u1 = 0.f;
+          for (int j = 0; j < s.chunks; ++j) {
+            const float2 q = __ldcg(&part_c[((size_t)b * s.chunks + j) * s.C + c]);
+            u0 += q.x; u1 += q.y;
+          }
+          chan_tot[(size_t)b * s.C + c] = make_float2(u0, u1);
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned int old = atomicAdd(&sync[s.B], 1u);
+        s_last = (old == (unsigned int)(s.B * s.chunks) - 1u) ? 1 : 0;
+        __threadfence();
+      }
+    }
+    __syncthreads();
+    if (BWD && s_last) {
+      for (int c = threadIdx.x; c < s.C; c += nthr) {
+        float u0 = 0.f, u1 = 0.f;
+        for (int bb = 0; bb < s.B; ++bb) {
+          const float2 q = __ldcg(&chan_tot[(size_t)bb * s.C + c]);
+          u0 += q.x; u1 += q.y;
+        }
+        dbeta[c] = u0;
+        dgamma[c] = u1;
+      }
+    }
+  }
+
+  // ---------------- pass 2: normalise / input gradient ----------------
+  if (rl >= s.RL) return;
+  float sc[KC][8], sh[KC][8], rs_[KC][8], xb[KC][8], rA[KC][8], rB[KC][8];
+#pragma unroll
+  for (int k = 0; k < KC; ++k)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = (tc + k * s.TC) * 8 + i;
+      const int g = c / s.cpg;
+      const float2 st = BWD ? stats[b * kGroups + g] : s_grp[g];
+      const float gm = gamma[c];
+      sc[k][i] = st.y * gm; sh[k][i] = fmaf(-st.x * st.y, gm, beta[c]);
+      if (BWD) {
+        const float2 gg = s_grp[g];
+        rs_[k][i] = st.y; xb[k][i] = -st.x * st.y;
+        rA[k][i] = st.y * gg.x; rB[k][i] = st.y * gg.y;
+      }
+    }
+  for (int r = r0 + rl; r < r1; r += kGnUnroll * s.RL) {
+    uint4 xr[kGnUnroll][KC], dr[kGnUnroll][KC], ar[kGnUnroll][KC];
+#pragma unroll
+    for (int u = 0; u < kGnUnroll; ++u) {
+      const int rr = r + u * s.RL;
+#pragma unroll
+      for (int k = 0; k < KC; ++k) {
+        const size_t off = base + (size_t)rr * s.C + (size_t)(tc + k * s.TC) * 8;
+        const uint4 z4 = make_uint4(0u, 0u, 0u, 0u);
+        xr[u][k] = (rr < r1) ? sdb::ld_u4(x + off) : z4;
+        if (BWD) {
+          dr[u][k] = (rr < r1) ? sdb::ld_u4(dy + off) : z4;
+          ar[u][k] = (rr < r1 && add != nullptr) ? sdb::ld_u4(add + off) : z4;
+        }
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kGnUnroll; ++u) {
+      const int rr = r + u * s.RL;
+      if (rr >= r1) break;
+#pragma unroll
+      for (int k = 0; k < KC; ++k) {
+        const size_t off = base + (size_t)rr * s.C + (size_t)(tc + k * s.TC) * 8;
+        float xv[8], o[8];
+        unpack8(xr[u][k], xv);
+        if (!BWD) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float z = fmaf(xv[i], sc[k][i], sh[k][i]);
+            o[i] = SILU ? z * sigmoid_f(z) : z;
+          }
+        } else {
+          float dv[8], av[8];
+          unpack8(dr[u][k], dv);
+          unpack8(ar[u][k], av);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = fmaf(xv[i], rs_[k][i], xb[k][i]);
+            float dz = dv[i];
+            if (SILU) {
+              const float z = fmaf(xv[i], sc[k][i], sh[k][i]);
+              const float sg = sigmoid_f(z);
+              dz *= sg * (1.0f + z * (1.0f - sg));
+            }
+            // dx = rstd * (gamma*dz - A_g - xhat*B_g) (+ add)
+            o[i] = fmaf(sc[k][i], dz, av[i] - fmaf(xh, rB[k][i], rA[k][i]));
+          }
+        }
+        sdb::st_u4(out + off, pack8(o));
+      }
+    }
+  }
+}
+
+constexpr int kGnFusedMaxOcc = 4;
+
+// workspace of the fused path: sync [B+1] u32 (padded to 256 B) | part_g [B][chunks][32] | part_c [B][chunks][C] | chan_tot [B][C]
+size_t gn_fused_ws_bytes(const GnShape& s) {
+  return 256 + (((size_t)s.B + 1) * 4 + 255) / 256 * 256 +
+         sizeof(float2) * ((size_t)s.B * s.chunks * kGroups + (size_t)s.B * s.chunks * s.C + (size_t)s.B * s.C);
+}
+
+// Co-resident grid for the fused kernel: chunks per sample = min(rows / RL, capacity / B). Returns false when the
+// samples alone exceed the capacity (fall back to the multi-launch path).
+// SDB_GN_LEGACY=1 keeps the multi-launch path (A/B timing and a second implementation for the parity tests)
+bool gn_force_legacy() {
+  static const bool v = getenv("SDB_GN_LEGACY") != nullptr && atoi(getenv("SDB_GN_LEGACY")) != 0;
+  return v;
+}
+
+template <typename K>
+bool gn_fused_plan(K kernel, GnShape* s) {
+  const int threads = s->TC * s->RL;
+  const size_t sm = (size_t)s->RL * s->C * 2 * sizeof(float);
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, threads, sm) != cudaSuccess || occ < 1) {
+    cudaGetLastError();
+    return false;
+  }
+  if (occ > kGnFusedMaxOcc) occ = kGnFusedMaxOcc;
+  const int capacity = occ * sdb::kNumSMs;
+  if (s->B > capacity) return false;
+  int chunks = capacity / s->B;
+  const int max_chunks = (s->HW + s->RL - 1) / s->RL;
+  if (chunks > max_chunks) chunks = max_chunks;
+  s->rows_per_chunk = (s->HW + chunks - 1) / chunks;
+  s->chunks = (s->HW + s->rows_per_chunk - 1) / s->rows_per_chunk;
+  return true;
+}
+
 size_t gn_ws_bytes(const GnShape& s) {
   // part [B][chunks][C] float2 | chan_tot [B][C] float2 | grp [B][32] float2
   return sizeof(float2) * ((size_t)s.B * s.chunks * s.C + (size_t)s.B * s.C + (size_t)s.B * kGroups);
@@ -495,7 +791,15 @@ int ew_grid(long long work, int per_sm = 8) {
 extern "C" size_t sdb_groupnorm_workspace_bytes(int B, int HW, int C) {
   GnShape s;
   if (!gn_shape(B, HW, C, &s)) return 0;
-  return gn_ws_bytes(s);
+  const size_t legacy = gn_ws_bytes(s);
+  GnShape f = s;  // upper bound of the fused path's chunk count
+  int chunks = (kGnFusedMaxOcc * sdb::kNumSMs) / (B > 0 ? B : 1);
+  const int max_chunks = (HW + s.RL - 1) / s.RL;
+  if (chunks > max_chunks) chunks = max_chunks;
+  if (chunks < 1) chunks = 1;
+  f.chunks = chunks;
+  const size_t fused = gn_fused_ws_bytes(f);
+  return legacy > fused ? legacy : fused;
 }
 
 extern "C" int sdb_groupnorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* stats, int B,
@@ -509,9 +813,32 @@ extern "C" int sdb_groupnorm_fwd(const void* x, const float* gamma, const float*
   const __nv_bfloat16* xp = reinterpret_cast<const __nv_bfloat16*>(x);
   __nv_bfloat16* yp = reinterpret_cast<__nv_bfloat16*>(y);
   float2* st = reinterpret_cast<float2*>(stats);
-  const dim3 grid(s.chunks, B);
   const int threads = s.TC * s.RL;
   const size_t sm = (size_t)s.RL * s.C * 2 * sizeof(float);
+  if (!gn_force_legacy()) {
+    GnShape f = s;
+    bool ok;
+#define GN_PLAN(KC_, SILU_) ok = gn_fused_plan(gn_fused_kernel<KC_, false, SILU_>, &f)
+    if (s.KC == 1) { if (silu) GN_PLAN(1, true); else GN_PLAN(1, false); }
+    else { if (silu) GN_PLAN(2, true); else GN_PLAN(2, false); }
+#undef GN_PLAN
+    if (ok && gn_fused_ws_bytes(f) <= ws_bytes) {
+      unsigned int* sync = reinterpret_cast<unsigned int*>(workspace);
+      const size_t sync_bytes = (((size_t)B + 1) * 4 + 255) / 256 * 256;
+      float2* part_g = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(workspace) + sync_bytes);
+      cudaMemsetAsync(sync, 0, sync_bytes, stream);
+      const dim3 fgrid(f.chunks, B);
+#define GN_FUSED(KC_, SILU_)                                                                                        \
+  gn_fused_kernel<KC_, false, SILU_><<<fgrid, threads, sm, stream>>>(xp, nullptr, st, gamma, beta, nullptr, yp, part_g, \
+                                                                    nullptr, nullptr, nullptr, nullptr, sync, f, eps)
+      if (s.KC == 1) { if (silu) GN_FUSED(1, true); else GN_FUSED(1, false); }
+      else { if (silu) GN_FUSED(2, true); else GN_FUSED(2, false); }
+#undef GN_FUSED
+      SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_fwd(fused)");
+      return SDB_OK;
+    }
+  }
+  const dim3 grid(s.chunks, B);
   if (s.KC == 1) gn_partial_kernel<1, false, false><<<grid, threads, sm, stream>>>(xp, nullptr, nullptr, nullptr, nullptr, part, s);
   else gn_partial_kernel<2, false, false><<<grid, threads, sm, stream>>>(xp, nullptr, nullptr, nullptr, nullptr, part, s);
   SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_fwd(partial)");
@@ -541,9 +868,34 @@ extern "C" int sdb_groupnorm_bwd(const void* x, const void* dy, const float* sta
   const __nv_bfloat16* addp = reinterpret_cast<const __nv_bfloat16*>(dx_add);
   __nv_bfloat16* dxp = reinterpret_cast<__nv_bfloat16*>(dx);
   const float2* st = reinterpret_cast<const float2*>(stats);
-  const dim3 grid(s.chunks, B);
   const int threads = s.TC * s.RL;
   const size_t sm = (size_t)s.RL * s.C * 2 * sizeof(float);
+  if (!gn_force_legacy()) {
+    GnShape f = s;
+    bool ok;
+#define GN_PLAN(KC_, SILU_) ok = gn_fused_plan(gn_fused_kernel<KC_, true, SILU_>, &f)
+    if (s.KC == 1) { if (silu) GN_PLAN(1, true); else GN_PLAN(1, false); }
+    else { if (silu) GN_PLAN(2, true); else GN_PLAN(2, false); }
+#undef GN_PLAN
+    if (ok && gn_fused_ws_bytes(f) <= ws_bytes) {
+      unsigned int* sync = reinterpret_cast<unsigned int*>(workspace);
+      const size_t sync_bytes = (((size_t)B + 1) * 4 + 255) / 256 * 256;
+      float2* part_g = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(workspace) + sync_bytes);
+      float2* part_c = part_g + (size_t)f.B * f.chunks * kGroups;
+      float2* ctot = part_c + (size_t)f.B * f.chunks * f.C;
+      cudaMemsetAsync(sync, 0, sync_bytes, stream);
+      const dim3 fgrid(f.chunks, B);
+#define GN_FUSED(KC_, SILU_)                                                                                          \
+  gn_fused_kernel<KC_, true, SILU_><<<fgrid, threads, sm, stream>>>(xp, dyp, const_cast<float2*>(st), gamma, beta, addp, \
+                                                                   dxp, part_g, part_c, ctot, dgamma, dbeta, sync, f, 0.f)
+      if (s.KC == 1) { if (silu) GN_FUSED(1, true); else GN_FUSED(1, false); }
+      else { if (silu) GN_FUSED(2, true); else GN_FUSED(2, false); }
+#undef GN_FUSED
+      SDB_CUDA_LAUNCH_CHECK("sdb_groupnorm_bwd(fused)");
+      return SDB_OK;
+    }
+  }
+  const dim3 grid(s.chunks, B);
 #define GN_PART(KC_, SILU_) \
   gn_partial_kernel<KC_, true, SILU_><<<grid, threads, sm, stream>>>(xp, dyp, st, gamma, beta, part, s)
   if (s.KC == 1) { if (silu) GN_PART(1, true); else GN_PART(1, false); }

@@ -49,43 +49,76 @@ def _pixel_box(W: int, H: int, N: int, pixels: int):
     return bw, bh, bn
 
 
-_BN_CACHE: dict = {}
+_TILE_CACHE: dict = {}
 
 
-def _pick_block_n(N: int, need64: bool, m_tiles: int) -> int:
-    """Tile width for the persistent GEMM: simulate the kernel's static round-robin schedule (tile t -> CTA t % 148,
-    n-tile = t % tiles_n) for every legal width (multiples of 16 up to 256; MN-major B is staged in 64-column boxes,
-    so its smem footprint rounds up to 64) and take the width whose busiest CTA has the least work. Work of a tile =
-    its width, stretched below 128 columns where the UMMA operand fetch (4 KB of A + 32*BN B of B per BN/2 cycles)
-    exceeds 128 B/clk of shared-memory bandwidth, plus a fixed per-tile cost (pipeline refill) in column equivalents."""
-    del need64  # any multiple of 16 is legal for both operand majors now
-    key = (N, m_tiles)
-    if key in _BN_CACHE:
-        return _BN_CACHE[key]
-    forced = int(os.environ.get("SDB_BN", "0"))
-    if forced:
-        return min(forced, (N + 15) // 16 * 16)
+def _kblock_clks(mt: int, bn: int, b_mn: bool) -> float:
+    """Cycles one 64-deep K block of a (128*mt x bn) tile occupies an SM — measured model (tools/mma_rate.cu and the
+    SDB_GEMM_DBG experiments): the main loop runs at the slower of
+      * operand delivery: the smem ring holds `stages` K blocks and a refill takes ~3000 clk under load (the L2
+        request queues are full: ~13 TB/s chip-wide), so one K block per 3000 / stages clk whatever its size —
+        which is why fewer, larger tiles (less re-fetching of A and B) win until the ring gets too shallow;
+      * tcgen05.mma with both operands in shared memory: max(95, bn/2 + 40.5) clk per K=16 step from one issuing
+        thread; two issuing threads (mt == 2, one per 128-row half) overlap operand fetches: ~40 + 0.355*bn each."""
+    bcols = -(-bn // 64) * 64 if b_mn else bn
+    stage_bytes = (128 * mt + bcols) * 128
+    stages = max(1, min(8, (200 * 1024) // stage_bytes))
+    delivery = 3000.0 / stages
+    mma = 4 * max(95.0, bn / 2 + 40.5) if mt == 1 else 8 * max(62.0, 40.0 + 0.355 * bn)
+    return max(delivery, mma)
+
+
+def _pick_tile(N: int, pix, b_mn: bool, nkb: int):
+    """(m_halves, block_n) for the persistent GEMM: simulate the kernel's static round-robin schedule (tile t -> CTA
+    t % 148, n-tile = t % tiles_n) for every legal shape and take the one whose busiest CTA finishes first."""
+    key = (N, pix, b_mn, nkb)
+    if key in _TILE_CACHE:
+        return _TILE_CACHE[key]
+    W, H, NI = pix
+    forced_bn = int(os.environ.get("SDB_BN", "0"))
+    forced_mt = int(os.environ.get("SDB_MT", "0"))
     best, best_cost = None, None
-    for bn in range(256, 63, -16):
-        tiles_n = -(-N // bn)
-        if bn * (tiles_n - 1) >= N:
+    for mt in (1, 2):
+        if forced_mt and mt != forced_mt:
             continue
-        last = N - bn * (tiles_n - 1)
-        total = tiles_n * m_tiles
-        load = [0] * min(total, NUM_SMS)
-        for t in range(total):
-            w = bn if (t % tiles_n) < tiles_n - 1 else (last + 15) // 16 * 16
-            load[t % NUM_SMS] += w * max(1.0, (8192.0 / w + 64.0) / 128.0) + 24
-        cost = max(load)
-        if best_cost is None or cost < best_cost:
-            best, best_cost = bn, cost
-    if N < 64 or best is None:
-        best = (N + 15) // 16 * 16
-    _BN_CACHE[key] = best
+        try:
+            bw, bh, bn_ = _pixel_box(W, H, NI, 128 * mt)
+        except AssertionError:
+            continue
+        m_tiles = -(-W // bw) * -(-H // bh) * -(-NI // bn_)
+        if mt == 2 and W * H * NI < 256:
+            continue
+        for bn in range(256, 63, -16):
+            if forced_bn and bn != min(forced_bn, (N + 15) // 16 * 16):
+                continue
+            tiles_n = -(-N // bn)
+            if bn * (tiles_n - 1) >= N:
+                continue
+            last = (N - bn * (tiles_n - 1) + 15) // 16 * 16
+            total = tiles_n * m_tiles
+            # per-tile fixed cost: pipeline fill; with two halves the accumulators are not double-buffered, so the
+            # epilogue of a tile is exposed as well
+            fixed = 1500.0 if mt == 1 else 4000.0 + 16.0 * bn
+            c_full = nkb * _kblock_clks(mt, bn, b_mn) + fixed
+            c_last = nkb * _kblock_clks(mt, last, b_mn) + fixed
+            load = [0.0] * min(total, NUM_SMS)
+            for t in range(total):
+                load[t % NUM_SMS] += c_full if (t % tiles_n) < tiles_n - 1 else c_last
+            cost = max(load)
+            if best_cost is None or cost < best_cost:
+                best, best_cost = (mt, bn), cost
+    if best is None:
+        best = (1, (N + 15) // 16 * 16)
+    _TILE_CACHE[key] = best
     return best
 
 
+_SKIP_GEMM = set(x for x in os.environ.get("SDB_SKIP", "").split(",") if x.startswith("gemm_"))
+
+
 def _launch(desc: GemmDesc, impl: str) -> None:
+    if _SKIP_GEMM and ("gemm_fwd" if desc.mode == SDB_GEMM_FWD else "gemm_wgrad") in _SKIP_GEMM:
+        return  # timing experiments only (see _lib.lib)
     l = _lib.lib()
     fn = l.sdb_gemm_tc if impl == "tc" else l.sdb_gemm_simt
     _lib.check(fn(C.byref(desc), _lib.stream_ptr()), "sdb_gemm_" + impl)
@@ -113,10 +146,10 @@ def gemm_fwd(a_views, taps, b: torch.Tensor, b_mn: bool, out: torch.Tensor, pix,
     d.b_mn_major = 1 if b_mn else 0
     _set_taps(d, taps)
     d.outW, d.outH, d.outN = W, H, NI
-    d.bw, d.bh, d.bn = _pixel_box(W, H, NI, 128)
     d.N, d.K = N, K
-    m_tiles = -(-W // d.bw) * -(-H // d.bh) * -(-NI // d.bn)
-    d.block_n = _pick_block_n(N, b_mn, m_tiles)
+    mt, d.block_n = _pick_tile(N, (W, H, NI), bool(b_mn), len(taps) * -(-K // 64))
+    d.m_halves = mt
+    d.bw, d.bh, d.bn = _pixel_box(W, H, NI, 128 * mt)
     d.splits = 1
     out2 = out.view(-1, out.shape[-1])
     d.d = out2.data_ptr() + d_offset * out2.element_size()
@@ -151,7 +184,10 @@ def gemm_wgrad(a_views, taps, b_view: View4, out: torch.Tensor, pix, M: int, N: 
     # balanced widths: N = 320 -> 2 x 160 rather than 256 + 64 (MN-major boxes round the smem footprint up to 64)
     tiles_n = -(-N // 256)
     d.block_n = min(256, (-(-N // tiles_n) + 15) // 16 * 16)
-    tiles = len(taps) * -(-M // 128) * -(-N // d.block_n)
+    # two 128-row halves share each dY stage: measured to pay for the 3x3 convolutions of the large feature maps
+    # (many pixel blocks per tile), not for linears or the 16x16 / 8x8 levels
+    d.m_halves = 2 if (M > 128 and len(taps) > 1 and W * H * NI >= 8192 and os.environ.get("SDB_MT", "0") != "1") else 1
+    tiles = len(taps) * -(-M // (128 * d.m_halves)) * -(-N // d.block_n)
     total_pb = -(-W // d.bw) * -(-H // d.bh) * -(-NI // d.bn)
     splits = max(1, min(total_pb, (2 * NUM_SMS) // max(1, tiles)))
     d.splits = splits
