@@ -368,11 +368,27 @@ def conv3x3_s2_dgrad(dy, w, *, out=None, impl="tc"):
 # ---------------------------------------------------------------------------------------------------------------
 # normalisation / activation / attention / data movement
 _WS = {}
+_WS_TAG = "main"
+
+
+class side_workspace:
+    """Ops enqueued inside this context use a second scratch buffer: they run on another stream than the main chain
+    (unet.Graph forks the parameter-gradient GEMMs / reductions), so they must not share its stream-ordered scratch."""
+
+    def __enter__(self):
+        global _WS_TAG
+        self._old, _WS_TAG = _WS_TAG, "side"
+
+    def __exit__(self, *exc):
+        global _WS_TAG
+        _WS_TAG = self._old
+        return False
 
 
 def workspace(device, nbytes: int = 64 << 20) -> torch.Tensor:
-    """One stream-ordered scratch buffer per device (partials of reductions; every op finishes with it in-stream)."""
-    key = (device.type, device.index)
+    """One stream-ordered scratch buffer per device and stream role (partials of reductions; every op finishes with it
+    in-stream)."""
+    key = (device.type, device.index, _WS_TAG)
     ws = _WS.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 64 << 20), dtype=torch.uint8, device=device)

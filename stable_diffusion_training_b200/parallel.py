@@ -76,6 +76,7 @@ class GradReducer:
         self.capture = None          # callable(force: bool) -> None that cuts the graph segment
         self.capture_cut_every = 8
         self._deferred: List[int] = []
+        self.before_issue = None     # callable() run before a bucket is handed to the collective / the capturer
 
     # ---- one step ----
     def begin(self, _graph=None) -> None:
@@ -102,6 +103,8 @@ class GradReducer:
     def _all_reduce_bucket(self, b: int) -> None:
         s, e, _ = self.buckets[b]
         self.issued_order.append(b)
+        if self.before_issue is not None:
+            self.before_issue()  # e.g. unet.Graph.join: parameter gradients are produced on a second stream
         if self.capture is not None:
             self._deferred.append(b)
             if len(self._deferred) >= self.capture_cut_every:
@@ -123,6 +126,8 @@ class GradReducer:
     def finish(self, loss: torch.Tensor) -> torch.Tensor:
         """Flush the remaining buckets, average the loss over ranks, join the communication stream."""
         self._issue_ready(force=True)
+        if self.before_issue is not None:
+            self.before_issue()
         if self.capture is not None:
             self.capture(True)  # the replayer reduces the remaining buckets and the loss, then joins the streams
             return loss

@@ -371,6 +371,7 @@ def train_step(state: TrainState, batch: dict, rng, frozen_noise_scheduler_state
     loss, dpred = mse_loss_and_grad(pred.v, target, weight, 1.0 / (state.dp.world_size if state.dp else 1))
     if state.dp is not None:
         state.dp.begin(net.graph)
+        state.dp.before_issue = net.graph.join
     net.backward(pred, dpred, on_grad)
     if state.dp is not None:
         loss = state.dp.finish(loss)

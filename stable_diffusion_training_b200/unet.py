@@ -11,6 +11,7 @@ backward closure on a tape; `backward()` replays the tape in reverse. torch is u
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -203,6 +204,38 @@ class Graph:
         self.tape = []
         self.quirk = reference_attention_quirk
         self._kb_cache = {}
+        # Parameter gradients (wgrad GEMMs, bias column sums) feed nothing but the optimizer, so backward enqueues them
+        # on a second stream: their CTAs fill the SMs the main chain leaves idle (partial last waves of the persistent
+        # GEMMs, launch gaps). SDB_SIDE_STREAM=0 keeps everything on one stream.
+        self.side: Optional[torch.cuda.Stream] = None
+        self._side_enabled = os.environ.get("SDB_SIDE_STREAM", "1") != "0"
+        self._forked = False
+        self._keep: list = []
+
+    # -------- second stream for parameter gradients --------
+    def _fork(self, fn, *keep) -> None:
+        """Run `fn` (launches that only READ activations / output gradients and write parameter gradients) on the
+        side stream, after everything the main stream has enqueued so far. `keep` are tensors the main chain drops
+        before the side stream is done with them: they stay referenced until the join so the allocator cannot hand
+        their memory to a later main-stream tensor."""
+        if not self._side_enabled or not torch.cuda.is_available():
+            fn()
+            return
+        main = torch.cuda.current_stream()
+        if self.side is None or self.side.device != main.device:
+            self.side = torch.cuda.Stream(device=main.device)
+        self.side.wait_stream(main)
+        with torch.cuda.stream(self.side), ops.side_workspace():
+            fn()
+        self._keep.extend(keep)
+        self._forked = True
+
+    def join(self) -> None:
+        """Main stream waits for the side stream (before gradients are consumed: bucket all-reduce, optimizer, any
+        in-place accumulation into a tensor the side stream may still read)."""
+        if self._forked:
+            torch.cuda.current_stream().wait_stream(self.side)
+            self._forked = False
 
     # -------- gradient plumbing --------
     @staticmethod
@@ -214,6 +247,11 @@ class Graph:
         else:
             ops.add_(t.g, g)
 
+    def _acc_safe(self, t: T, g: torch.Tensor) -> None:
+        if t.rg and t.g is not None:
+            self.join()  # in-place add into a tensor that may alias an output gradient the side stream still reads
+        self._acc(t, g)
+
     def backward(self, on_grads=None) -> None:
         """Replay the tape in reverse. `on_grads(names)` is called right after the closure that finishes the gradients
         of those parameter leaves has been enqueued (every leaf is used once per forward, so 'finished' is exact):
@@ -222,6 +260,8 @@ class Graph:
             fn()
             if on_grads is not None and names:
                 on_grads(names)
+        self.join()
+        self._keep = []
         self.tape = []
 
     def _kbias(self, sq: int, skv: int, device):
@@ -243,14 +283,17 @@ class Graph:
 
         def bwd():
             dy = y.g
-            if bias:
-                ops.colsum(dy, self.G[name + "/bias"])
             gw = self.G[name + "/kernel"]
-            ops.linear_wgrad(x.v, dy, out=gw.view(-1, gw.shape[-1]))
+
+            def param_grads():
+                if bias:
+                    ops.colsum(dy, self.G[name + "/bias"])
+                ops.linear_wgrad(x.v, dy, out=gw.view(-1, gw.shape[-1]))
+            self._fork(param_grads, dy)
             if x.rg:
                 x.g = ops.linear_dgrad(dy, w2, residual=x.g)
             if res is not None:
-                self._acc(res, dy)
+                self._acc_safe(res, dy)
             y.g = None
         self.tape.append((bwd, [name + "/kernel"] + ([name + "/bias"] if bias else [])))
         return y
@@ -280,29 +323,35 @@ class Graph:
         def bwd():
             dy = y.g
             dy4 = dy.view(geom[0], geom[1], geom[2], cout)
-            if temb is not None:
+            if temb is not None:  # the per-image column sums feed the time-embedding gradient: main stream
                 dt = torch.empty((B, cout), device=dy.device, dtype=BF16)
                 ops.colsum(dy, self.G[name + "/bias"], nseg=B, out_seg=dt)
-                self._acc(temb, dt)
-            else:
-                ops.colsum(dy, self.G[name + "/bias"])
+                self._acc_safe(temb, dt)
+
+            def param_grads():
+                if temb is None:
+                    ops.colsum(dy, self.G[name + "/bias"])
+                if c4:
+                    ops.conv3x3_c4_wgrad(x4, dy4, out=self.G[name + "/kernel"])
+                elif stride == 1:
+                    ops.conv3x3_wgrad(x4, dy4, out=self.G[name + "/kernel"], impl=impl)
+                else:
+                    ops.conv3x3_s2_wgrad(x4, dy4, out=self.G[name + "/kernel"], impl=impl)
+            self._fork(param_grads, dy)
             if c4:
-                ops.conv3x3_c4_wgrad(x4, dy4, out=self.G[name + "/kernel"])
                 if x.rg:
-                    self._acc(x, ops.conv3x3_c4out_dgrad(dy4, w).view(-1, cin))
+                    self._acc_safe(x, ops.conv3x3_c4out_dgrad(dy4, w).view(-1, cin))
             elif stride == 1:
-                ops.conv3x3_wgrad(x4, dy4, out=self.G[name + "/kernel"], impl=impl)
                 if x.rg:
                     if x.g is None or small:
-                        self._acc(x, ops.conv3x3_dgrad(dy4, w, impl=impl).view(-1, cin))
+                        self._acc_safe(x, ops.conv3x3_dgrad(dy4, w, impl=impl).view(-1, cin))
                     else:  # accumulate into the existing gradient inside the GEMM epilogue
                         x.g = _dgrad_acc(dy4, w, x.g.view(B, H, W, cin)).view(-1, cin)
             else:
-                ops.conv3x3_s2_wgrad(x4, dy4, out=self.G[name + "/kernel"], impl=impl)
                 if x.rg:
-                    self._acc(x, ops.conv3x3_s2_dgrad(dy4, w, impl=impl).view(-1, cin))
+                    self._acc_safe(x, ops.conv3x3_s2_dgrad(dy4, w, impl=impl).view(-1, cin))
             if res is not None:
-                self._acc(res, dy)
+                self._acc_safe(res, dy)
             y.g = None
         self.tape.append((bwd, [name + "/kernel", name + "/bias"]))
         return y
@@ -338,7 +387,7 @@ class Graph:
         y = T(ops.geglu_fwd(u.v), u.geom)
 
         def bwd():
-            self._acc(u, ops.geglu_bwd(u.v, y.g))
+            self._acc_safe(u, ops.geglu_bwd(u.v, y.g))
             y.g = None
         self.tape.append((bwd, None))
         return y
@@ -347,7 +396,7 @@ class Graph:
         y = T(ops.silu_fwd(x.v), x.geom)
 
         def bwd():
-            self._acc(x, ops.silu_bwd(x.v, y.g))
+            self._acc_safe(x, ops.silu_bwd(x.v, y.g))
             y.g = None
         self.tape.append((bwd, None))
         return y
@@ -362,9 +411,9 @@ class Graph:
 
         def bwd():
             dq, dk, dv = ops.attention_bwd(q3, k3, v3, o3, o.g.view(B, Sq, C), lse2, heads, kbias2=kb)
-            self._acc(q, dq.view(-1, C))
-            self._acc(k, dk.view(-1, C))
-            self._acc(v, dv.view(-1, C))
+            self._acc_safe(q, dq.view(-1, C))
+            self._acc_safe(k, dk.view(-1, C))
+            self._acc_safe(v, dv.view(-1, C))
             o.g = None
         self.tape.append((bwd, None))
         return o
@@ -389,6 +438,7 @@ class Graph:
                     t.g = torch.empty_like(t.v)
                     ops.copy2d(sl, t.g)
                 else:
+                    self.join()
                     ops.copy2d(sl, t.g, accumulate=True)
             y.g = None
         self.tape.append((bwd, None))
@@ -400,7 +450,7 @@ class Graph:
         y = T(ops.upsample2x_fwd(x.v.view(B, H, W, C)).view(-1, C), (B, 2 * H, 2 * W))
 
         def bwd():
-            self._acc(x, ops.upsample2x_bwd(y.g.view(B, 2 * H, 2 * W, C)).view(-1, C))
+            self._acc_safe(x, ops.upsample2x_bwd(y.g.view(B, 2 * H, 2 * W, C)).view(-1, C))
             y.g = None
         self.tape.append((bwd, None))
         return y
