@@ -90,6 +90,7 @@ struct FwdParams {
 };
 
 __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_constant__ FwdParams p) {
+  sdb::pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -140,6 +141,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  sdb::pdl_wait();  // prologue above overlaps the previous kernel's tail
   const uint32_t tS = tmem_base;         // 2 x 128 columns
   const uint32_t tO = tmem_base + 256u;  // npv x dpad columns (one accumulator per PV issuer)
 
@@ -380,6 +382,7 @@ struct BwdParams {
 
 template <int MODE, int NBUF>
 __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_constant__ BwdParams p) {
+  sdb::pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -433,6 +436,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  sdb::pdl_wait();  // prologue above overlaps the previous kernel's tail
   // [S0 | dP0 | (S1 | dP1) | A1 | A2]
   const uint32_t tS = tmem_base;
   const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc * (uint32_t)NBUF;
@@ -654,6 +658,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
 __global__ void __launch_bounds__(256)
 attn_dvec_kernel(const __nv_bfloat16* __restrict__ o, long long ldo, const __nv_bfloat16* __restrict__ dO,
                  long long lddo, float* __restrict__ dvec, int B, int H, int Sq, int d) {
+  sdb::pdl_trigger();
   const long long total = (long long)B * Sq * H;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -764,7 +769,10 @@ extern "C" int sdb_attn_fwd(const void* q, long long ldq, const void* k, long lo
   if (attr_err != cudaSuccess)
     return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
   dim3 grid((Sq + 127) / 128, H, B);
-  attn_fwd_kernel<<<grid, kFwdThreads, smem_bytes, stream>>>(p);
+  if (sdb::launch_pdl(attn_fwd_kernel, grid, dim3(kFwdThreads), smem_bytes, stream, p) != cudaSuccess) {
+    const cudaError_t e = cudaGetLastError();
+    return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_fwd: launch failed: %s", cudaGetErrorString(e));
+  }
   SDB_CUDA_LAUNCH_CHECK("sdb_attn_fwd");
   return SDB_OK;
 }
@@ -855,10 +863,16 @@ extern "C" int sdb_attn_bwd(const void* q, long long ldq, const void* k, long lo
     p.stages = stages;
     const size_t smem_bytes = fixed + (size_t)p.stages * 2 * ctile;
     dim3 grid((p.Srow + 127) / 128, H, B);
-    if (mode == 0 && p.nbuf == 2) attn_bwd_kernel<0, 2><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
-    else if (mode == 0) attn_bwd_kernel<0, 1><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
-    else if (p.nbuf == 2) attn_bwd_kernel<1, 2><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
-    else attn_bwd_kernel<1, 1><<<grid, kBwdThreads, smem_bytes, stream>>>(p);
+    const dim3 b3(kBwdThreads);
+    cudaError_t lerr;
+    if (mode == 0 && p.nbuf == 2) lerr = sdb::launch_pdl(attn_bwd_kernel<0, 2>, grid, b3, smem_bytes, stream, p);
+    else if (mode == 0) lerr = sdb::launch_pdl(attn_bwd_kernel<0, 1>, grid, b3, smem_bytes, stream, p);
+    else if (p.nbuf == 2) lerr = sdb::launch_pdl(attn_bwd_kernel<1, 2>, grid, b3, smem_bytes, stream, p);
+    else lerr = sdb::launch_pdl(attn_bwd_kernel<1, 1>, grid, b3, smem_bytes, stream, p);
+    if (lerr != cudaSuccess) {
+      cudaGetLastError();
+      return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_bwd: launch failed: %s", cudaGetErrorString(lerr));
+    }
     SDB_CUDA_LAUNCH_CHECK("sdb_attn_bwd");
   }
   return SDB_OK;

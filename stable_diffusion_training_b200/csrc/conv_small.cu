@@ -26,6 +26,7 @@ __device__ __forceinline__ void unpack4(const uint2& v, float* f) {
 __global__ void __launch_bounds__(256)
 c4_to_wide_kernel(const __nv_bfloat16* __restrict__ a4, const __nv_bfloat16* __restrict__ w, const float* __restrict__ bias,
                   __nv_bfloat16* __restrict__ out, int B, int H, int W, int C, int w_tap, int w_k, int w_n, int flip) {
+  sdb::pdl_trigger();
   extern __shared__ float s_w[];  // [9][4][C]
   for (int i = threadIdx.x; i < 36 * C; i += blockDim.x) {
     const int n = i % C, k = (i / C) & 3, tap = i / (4 * C);
@@ -76,6 +77,7 @@ c4_to_wide_kernel(const __nv_bfloat16* __restrict__ a4, const __nv_bfloat16* __r
 __global__ void __launch_bounds__(256)
 wide_to_c4_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ w, const float* __restrict__ bias,
                   __nv_bfloat16* __restrict__ out, int B, int H, int W, int C) {
+  sdb::pdl_trigger();
   // smem weights as [tap][i = channel % 8][v = channel / 8][4]: the lanes of a warp (consecutive v) read consecutive
   // float4 -> conflict-free LDS.128
   extern __shared__ float s_w[];
@@ -127,6 +129,7 @@ template <bool C4_IS_INPUT>
 __global__ void __launch_bounds__(1024)
 wgrad_c4_kernel(const __nv_bfloat16* __restrict__ wide, const __nv_bfloat16* __restrict__ c4, float* __restrict__ dw, int B,
                 int H, int W, int C, long long pix_per_cta) {
+  sdb::pdl_trigger();
   const int nv = C / 8;
   const int tap = threadIdx.x / nv, v = threadIdx.x % nv;
   if (tap >= 9) return;

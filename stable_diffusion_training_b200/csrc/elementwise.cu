@@ -29,6 +29,7 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
 }
 
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  sdb::pdl_trigger();
   const long long n4 = n / 4;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < n4; v += stride) {
@@ -45,6 +46,7 @@ __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat1
 // src NCHW fp32 [B,C,HW] -> dst NHWC bf16 [B,HW,C] (C tiny: 4)
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B, int C,
                                     int HW) {
+  sdb::pdl_trigger();
   const long long total = (long long)B * C * HW;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -58,6 +60,7 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16
 
 // y[b, 2h+i, 2w+j, :] = x[b, h, w, :]
 __global__ void upsample2x_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int B, int H, int W, int CV) {
+  sdb::pdl_trigger();
   const long long total = (long long)B * 2 * H * 2 * W * CV;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -72,6 +75,7 @@ __global__ void upsample2x_fwd_kernel(const uint4* __restrict__ x, uint4* __rest
 // dx[b,h,w,:] = sum_{i,j} dy[b,2h+i,2w+j,:]
 __global__ void upsample2x_bwd_kernel(const uint4* __restrict__ dy, uint4* __restrict__ dx, int B, int H, int W,
                                       int CV) {
+  sdb::pdl_trigger();
   const long long total = (long long)B * H * W * CV;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -98,6 +102,7 @@ __global__ void upsample2x_bwd_kernel(const uint4* __restrict__ dy, uint4* __res
 template <bool ACC>
 __global__ void copy2d_kernel(const __nv_bfloat16* __restrict__ src, long long lds, __nv_bfloat16* __restrict__ dst,
                               long long ldd, long long rows, int cv) {
+  sdb::pdl_trigger();
   const long long total = rows * cv;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -119,6 +124,7 @@ __global__ void copy2d_kernel(const __nv_bfloat16* __restrict__ src, long long l
 
 __global__ void add_bf16_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out,
                                 long long nv) {
+  sdb::pdl_trigger();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += (long long)gridDim.x * blockDim.x) {
     float fa[8], fb[8];
     unpack8(a[i], fa);
@@ -137,6 +143,7 @@ constexpr int kColsumMinRows = 32;
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows_per_seg, int bps, int rpb,
                       int cols, float* __restrict__ part) {
+  sdb::pdl_trigger();
   // thread (ty, tx): tx over 8-wide column vectors (32 per chunk), ty over 8 row lanes
   __shared__ float s[8][256 + 8];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -187,6 +194,7 @@ colsum_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long lo
 __global__ void __launch_bounds__(256)
 colsum_final_kernel(const float* __restrict__ part, int nseg, int bps, int cols, float* __restrict__ out_total,
                     __nv_bfloat16* __restrict__ out_seg) {
+  sdb::pdl_trigger();
   __shared__ float s[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int c = blockIdx.x * 32 + tx;
@@ -211,6 +219,7 @@ colsum_final_kernel(const float* __restrict__ part, int nseg, int bps, int cols,
 // any (small) column count, no alignment requirement: one block per column
 __global__ void __launch_bounds__(256)
 colsum_narrow_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long long rows, float* __restrict__ out) {
+  sdb::pdl_trigger();
   const int c = blockIdx.x;
   float acc = 0.f;
   for (long long r = threadIdx.x; r < rows; r += 256) acc += __bfloat162float(x[r * ld + c]);
@@ -226,6 +235,7 @@ colsum_narrow_kernel(const __nv_bfloat16* __restrict__ x, long long ld, long lon
 }
 
 __global__ void silu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
+  sdb::pdl_trigger();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float v = __bfloat162float(x[i]);
     y[i] = __float2bfloat16_rn(v / (1.0f + __expf(-v)));
@@ -234,6 +244,7 @@ __global__ void silu_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat
 // dx = dy * silu'(x) (+ add)
 __global__ void silu_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                                 __nv_bfloat16* __restrict__ dx, long long n) {
+  sdb::pdl_trigger();
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float v = __bfloat162float(x[i]);
     const float sg = 1.0f / (1.0f + __expf(-v));
@@ -244,6 +255,7 @@ __global__ void silu_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_
 // emb[b, :] = flip ? [cos(t f), sin(t f)] : [sin, cos], f_i = exp(-ln(10000) * i / (half - freq_shift))
 __global__ void timestep_embedding_kernel(const int* __restrict__ t, __nv_bfloat16* __restrict__ out, int B, int dim,
                                           int flip_sin_to_cos, float freq_shift) {
+  sdb::pdl_trigger();
   const int half = dim / 2;
   const int idx = blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= B * half) return;

@@ -32,6 +32,7 @@ __device__ __forceinline__ const __nv_bfloat16* view_ptr(const sdb_view4& v, int
 
 // one thread per output element (pixel, n)
 __global__ void __launch_bounds__(256) simt_fwd_kernel(const SimtParams p) {
+  sdb::pdl_trigger();
   const long long total = (long long)p.W * p.H * p.NI * p.N;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
        idx += (long long)gridDim.x * blockDim.x) {
@@ -65,6 +66,7 @@ __global__ void __launch_bounds__(256) simt_fwd_kernel(const SimtParams p) {
 
 // grid.x over (tap, m, n) elements, grid.y over pixel chunks; atomicAdd into the (zeroed) fp32 output
 __global__ void __launch_bounds__(256) simt_wgrad_kernel(const SimtParams p) {
+  sdb::pdl_trigger();
   const long long total = (long long)p.ntaps * p.M * p.N;
   const long long npix = (long long)p.W * p.H * p.NI;
   const long long per_chunk = (npix + p.pixel_chunks - 1) / p.pixel_chunks;

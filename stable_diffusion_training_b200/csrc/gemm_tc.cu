@@ -110,6 +110,7 @@ __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
 // matters when the SM's ingest of TMA bytes, not the tensor pipe, paces the main loop).
 template <int MODE, int MT>
 __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_constant__ TcParams p) {
+  sdb::pdl_trigger();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = ptx::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -145,6 +146,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
+  sdb::pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -513,12 +515,18 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err));
 
   const int grid = p.total_tiles < sdb::kNumSMs ? p.total_tiles : sdb::kNumSMs;
+  cudaError_t lerr;
+  const dim3 g3(grid), b3(kThreads);
   if (wgrad) {
-    if (mt == 2) gemm_tc_kernel<SDB_GEMM_WGRAD, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
-    else gemm_tc_kernel<SDB_GEMM_WGRAD, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
+    if (mt == 2) lerr = sdb::launch_pdl(gemm_tc_kernel<SDB_GEMM_WGRAD, 2>, g3, b3, smem_bytes, stream, p);
+    else lerr = sdb::launch_pdl(gemm_tc_kernel<SDB_GEMM_WGRAD, 1>, g3, b3, smem_bytes, stream, p);
   } else {
-    if (mt == 2) gemm_tc_kernel<SDB_GEMM_FWD, 2><<<grid, kThreads, smem_bytes, stream>>>(p);
-    else gemm_tc_kernel<SDB_GEMM_FWD, 1><<<grid, kThreads, smem_bytes, stream>>>(p);
+    if (mt == 2) lerr = sdb::launch_pdl(gemm_tc_kernel<SDB_GEMM_FWD, 2>, g3, b3, smem_bytes, stream, p);
+    else lerr = sdb::launch_pdl(gemm_tc_kernel<SDB_GEMM_FWD, 1>, g3, b3, smem_bytes, stream, p);
+  }
+  if (lerr != cudaSuccess) {
+    cudaGetLastError();
+    return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: launch failed: %s", cudaGetErrorString(lerr));
   }
   SDB_CUDA_LAUNCH_CHECK("sdb_gemm_tc");
   return SDB_OK;

@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(256)
 gn_partial_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
                   const float2* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
                   float2* __restrict__ part, GnShape s) {
+  sdb::pdl_trigger();
   extern __shared__ float smem[];
   float* s_a = smem;                       // [RL][C]
   float* s_b = smem + (size_t)s.RL * s.C;  // [RL][C]
@@ -150,6 +151,7 @@ template <bool BWD>
 __global__ void __launch_bounds__(256)
 gn_finalize_kernel(const float2* __restrict__ part, const float* __restrict__ gamma, float2* __restrict__ out_grp,
                    float2* __restrict__ chan_tot, GnShape s, float eps) {
+  sdb::pdl_trigger();
   __shared__ float2 s_w[8];
   const int g = blockIdx.x, b = blockIdx.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -196,6 +198,7 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
                 const float2* __restrict__ stats, const float2* __restrict__ grp, const float* __restrict__ gamma,
                 const float* __restrict__ beta, const __nv_bfloat16* __restrict__ add, __nv_bfloat16* __restrict__ out,
                 GnShape s) {
+  sdb::pdl_trigger();
   const int b = blockIdx.y, chunk = blockIdx.x;
   const int tc = threadIdx.x % s.TC, rl = threadIdx.x / s.TC;
   if (rl >= s.RL) return;
@@ -269,6 +272,7 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
 // dgamma[c] = sum_b chan_tot[b][c].y ; dbeta[c] = sum_b chan_tot[b][c].x
 __global__ void gn_param_grad_kernel(const float2* __restrict__ chan_tot, float* __restrict__ dgamma,
                                      float* __restrict__ dbeta, int B, int C) {
+  sdb::pdl_trigger();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
   float t0 = 0.f, t1 = 0.f;
@@ -303,6 +307,7 @@ gn_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
                 const float* __restrict__ gamma, const float* __restrict__ beta, const __nv_bfloat16* __restrict__ add,
                 __nv_bfloat16* __restrict__ out, float2* part_g, float2* part_c, float2* chan_tot,
                 float* __restrict__ dgamma, float* __restrict__ dbeta, unsigned int* sync, GnShape s, float eps) {
+  sdb::pdl_trigger();
   extern __shared__ float smem[];
   float* s_a = smem;                       // [RL][C]
   float* s_b = smem + (size_t)s.RL * s.C;  // [RL][C]
@@ -586,6 +591,7 @@ template <int NV>  // vectors per lane
 __global__ void __launch_bounds__(256)
 ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
               __nv_bfloat16* __restrict__ y, float2* __restrict__ stats, int rows, int C, float eps) {
+  sdb::pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nv = C / 8;
   for (int row = blockIdx.x * kLnRowsPerBlock + warp; row < rows; row += gridDim.x * kLnRowsPerBlock) {
@@ -629,6 +635,7 @@ __global__ void __launch_bounds__(256)
 ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ dy,
               const float2* __restrict__ stats, const float* __restrict__ gamma, const __nv_bfloat16* __restrict__ add,
               __nv_bfloat16* __restrict__ dx, float* __restrict__ part, int rows, int C) {
+  sdb::pdl_trigger();
   extern __shared__ float smem[];  // [8 warps][2][C]
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nv = C / 8;
@@ -699,6 +706,7 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
 __global__ void __launch_bounds__(256)
 colsum_finalize_kernel(const float* __restrict__ part, int nblocks, int width, float* __restrict__ out0,
                        float* __restrict__ out1, int C) {
+  sdb::pdl_trigger();
   // 32 columns per block, 8 row slices per column
   __shared__ float s[8][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -739,6 +747,7 @@ __device__ __forceinline__ void gelu_tanh_both(float z, float* val, float* grad)
 
 __global__ void __launch_bounds__(256)
 geglu_fwd_kernel(const __nv_bfloat16* __restrict__ u, __nv_bfloat16* __restrict__ out, long long rows, int H) {
+  sdb::pdl_trigger();
   const int hv = H / 8;
   const long long total = rows * hv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -757,6 +766,7 @@ geglu_fwd_kernel(const __nv_bfloat16* __restrict__ u, __nv_bfloat16* __restrict_
 __global__ void __launch_bounds__(256)
 geglu_bwd_kernel(const __nv_bfloat16* __restrict__ u, const __nv_bfloat16* __restrict__ dout,
                  __nv_bfloat16* __restrict__ du, long long rows, int H) {
+  sdb::pdl_trigger();
   const int hv = H / 8;
   const long long total = rows * hv;
   for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;

@@ -17,6 +17,7 @@ __global__ void __launch_bounds__(256)
 noise_mix_kernel(const float* __restrict__ x0, const float* __restrict__ noise, const int* __restrict__ timesteps,
                  const float* __restrict__ alphas_cumprod, float* __restrict__ out, int per_sample_vec4,
                  long long total_vec4) {
+  sdb::pdl_trigger();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < total_vec4; v += stride) {
     const int b = (int)(v / per_sample_vec4);
@@ -50,6 +51,7 @@ struct DdpmCoef {
 __global__ void __launch_bounds__(256)
 ddpm_step_kernel(const float* __restrict__ model_out, const float* __restrict__ sample,
                  const float* __restrict__ noise, float* __restrict__ prev, long long n, DdpmCoef c) {
+  sdb::pdl_trigger();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     const float mo = model_out[i], x = sample[i];
@@ -74,6 +76,7 @@ __global__ void __launch_bounds__(256)
 mse_kernel(const __nv_bfloat16* __restrict__ pred, const float* __restrict__ target,
            const float* __restrict__ sample_weight, __nv_bfloat16* __restrict__ dpred, double* __restrict__ partials,
            int B, int C, int HW, float grad_scale) {
+  sdb::pdl_trigger();
   const long long total = (long long)B * C * HW;
   const long long stride = (long long)gridDim.x * blockDim.x;
   double acc = 0.0;
@@ -101,6 +104,7 @@ mse_kernel(const __nv_bfloat16* __restrict__ pred, const float* __restrict__ tar
   }
 }
 __global__ void mse_finalize_kernel(const double* __restrict__ partials, int n, double inv_count, float* loss) {
+  sdb::pdl_trigger();
   __shared__ double s[256];
   double t = 0.0;
   for (int i = threadIdx.x; i < n; i += 256) t += partials[i];

@@ -91,4 +91,30 @@ __device__ __forceinline__ float silu_grad_f(float x) {
 
 inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
+// ---- programmatic dependent launch (PDL) ----
+// Every kernel of the library executes pdl_trigger() first: once all CTAs of a grid have started, the NEXT kernel in
+// the stream may begin launching — but only if it was launched with launch_pdl(), and such kernels run their prologue
+// (barrier init, TMEM allocation, descriptor prefetch) and then block in pdl_wait() until the previous grid has
+// completed and flushed. Kernels launched with <<<>>> keep the ordinary full dependency. Inside a CUDA graph the pair
+// becomes a programmatic edge: the ~2-4 us of launch latency + prologue per tensor-core kernel overlap the tail of
+// its predecessor.
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 }  // namespace sdb
