@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SDB200_ABI_VERSION 1
+#define SDB200_ABI_VERSION 2
 
 #ifndef __CUDA_RUNTIME_H__
 typedef struct CUstream_st* cudaStream_t;

@@ -126,3 +126,61 @@ def test_conv3x3_simt_small_channels(cuda, Cin, Cout):
     _close(dx, xt.grad.permute(0, 2, 3, 1), atol=5e-2)
     ref_dw = wt.grad.permute(2, 3, 1, 0)
     assert (dw - ref_dw).abs().max().item() <= 2e-3 * max(1.0, ref_dw.abs().max().item())
+
+
+@pytest.fixture
+def force_tile(monkeypatch):
+    """Force the tile picker (SDB_MT: 128-row halves per tile, SDB_BN: tile width) and drop its cache around a test."""
+    def _set(mt=None, bn=None):
+        for k, v in (("SDB_MT", mt), ("SDB_BN", bn)):
+            if v is None:
+                monkeypatch.delenv(k, raising=False)
+            else:
+                monkeypatch.setenv(k, str(v))
+        ops._TILE_CACHE.clear()
+    yield _set
+    ops._TILE_CACHE.clear()
+
+
+@pytest.mark.parametrize("mt", [1, 2])
+@pytest.mark.parametrize("bn", [None, 80, 160, 256])
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(2, 32, 32, 128, 320), (8, 32, 32, 320, 160), (1, 16, 16, 64, 96),
+                                            (3, 12, 20, 64, 64)])
+def test_conv3x3_tile_shapes(cuda, force_tile, mt, bn, B, H, W, Cin, Cout):
+    """256-row tiles (two issuing warps sharing each B stage) and every tile width give the same result as 128-row
+    tiles: forward (MN-major weights), dgrad (K-major weights, fused gradient accumulation) and wgrad."""
+    force_tile(mt, bn)
+    x = _rand((B, H, W, Cin), cuda, seed=1)
+    w = _rand((3, 3, Cin, Cout), cuda, 1.0 / (9 * Cin) ** 0.5, seed=2)
+    bias = torch.randn(Cout, device=cuda)
+    res = _rand((B, H, W, Cout), cuda, seed=5)
+    y = ops.conv3x3(x, w, bias=bias, residual=res)
+    xt = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wt = w.float().permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    ref = torch.nn.functional.conv2d(xt, wt, bias, padding=1)
+    torch.cuda.synchronize()
+    _close(y, ref.permute(0, 2, 3, 1) + res.float())
+    dy = _rand((B, H, W, Cout), cuda, seed=3)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = ops.conv3x3_dgrad(dy, w)
+    dw = ops.conv3x3_wgrad(x, dy)
+    torch.cuda.synchronize()
+    _close(dx, xt.grad.permute(0, 2, 3, 1), atol=4e-2)
+    ref_dw = wt.grad.permute(2, 3, 1, 0)
+    err = (dw - ref_dw).abs().max().item()
+    assert err <= 2e-3 * max(1.0, ref_dw.abs().max().item()), err
+
+
+@pytest.mark.parametrize("mt", [1, 2])
+@pytest.mark.parametrize("M,K,N", [(512, 320, 320), (8192, 640, 1280), (616, 768, 320), (300, 64, 200)])
+def test_linear_tile_shapes(cuda, force_tile, mt, M, K, N):
+    force_tile(mt, None)
+    x = _rand((M, K), cuda, seed=1)
+    w = _rand((K, N), cuda, 1.0 / K ** 0.5, seed=2)
+    bias = torch.randn(N, device=cuda)
+    y = ops.linear(x, w, bias=bias)
+    dy = _rand((M, N), cuda, seed=3)
+    dx = ops.linear_dgrad(dy, w)
+    torch.cuda.synchronize()
+    _close(y, x.float() @ w.float() + bias)
+    _close(dx, dy.float() @ w.float().t(), atol=4e-2)
