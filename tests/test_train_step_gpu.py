@@ -166,3 +166,37 @@ def test_compiled_train_step_matches_eager(cuda):
     assert np.mean(pe != pg) < 1e-2
     np.testing.assert_allclose(pg, pe, rtol=0, atol=4 * 4 * (1e-6 / 7) * 1.1)
     assert np.mean(ce != cg) < 1e-2
+
+
+def test_sd2_style_train_step_matches_oracle(cuda):
+    """SD-2.x wiring (BASELINE.json configs[3]) at a size the CPU oracle finishes in seconds: per-level head counts with
+    head dim 64, Dense proj_in / proj_out (use_linear_projection), two layers per block, v-prediction, ctx dim != C."""
+    kw = dict(block_out_channels=(64, 128), down_block_types=("CrossAttnDownBlock2D", "DownBlock2D"),
+              up_block_types=("UpBlock2D", "CrossAttnUpBlock2D"), layers_per_block=2, attention_head_dim=(1, 2),
+              cross_attention_dim=48, use_linear_projection=True)
+    cfg, ocfg = PU.UNetConfig(**kw), OU.UNetConfig(**kw)
+    ptype = "v_prediction"
+    params_np = PU.init_params_numpy(cfg, 0)
+    tree = LQ.unflatten_dict(params_np)
+    state = TU.TrainState.create(apply_fn=TU.UNetModel(cfg).apply, params=tree, tx=TU.create_lion_optimizer(tree),
+                                 device=cuda)
+    sched = TU.default_scheduler(cuda, "scaled_linear", ptype)
+    b = _batch(2, 16, 16, 77, cfg.cross_attention_dim, seed=3)
+    batch = {k: torch.from_numpy(v).to(cuda) for k, v in b.items()}
+    state, metrics = TU.train_step(state, batch, rng=0, frozen_noise_scheduler_state=sched)
+    torch.cuda.synchronize()
+    names = sorted(params_np)
+    g_gpu = {n: state.arena.g[n].detach().cpu().numpy() for n in names}
+    ac = OS.common_state("scaled_linear", 0.00085, 0.012)["alphas_cumprod"]
+    op = {n: torch.from_numpy(v) for n, v in params_np.items()}
+    args = (torch.from_numpy(b["latents"]), torch.from_numpy(b["noise"]), torch.from_numpy(b["timesteps"]).long(),
+            torch.from_numpy(b["encoder_hidden_states"]), ac)
+    loss64, g64, _ = OU.loss_and_grads(ocfg, op, *args, prediction_type=ptype, mode="fp64")
+    loss16, g16, _ = OU.loss_and_grads(ocfg, op, *args, prediction_type=ptype, mode="bf16")
+    v64 = np.concatenate([g64[n].numpy().ravel() for n in names])
+    v16 = np.concatenate([g16[n].numpy().ravel() for n in names])
+    vgpu = np.concatenate([g_gpu[n].ravel() for n in names])
+    yard, err = _rel(v16, v64), _rel(vgpu, v64)
+    print(f"loss gpu {float(metrics['loss']):.6f} fp64 {float(loss64):.6f}; grad rel err {err:.4e} yardstick {yard:.4e}")
+    assert abs(float(metrics["loss"]) - float(loss64)) <= max(3 * abs(float(loss16) - float(loss64)), 2e-3 * abs(float(loss64)))
+    assert err <= 3 * yard, (err, yard)

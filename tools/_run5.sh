@@ -1,4 +1,2 @@
-for c in 4 12; do
-NCCL_MAX_CTAS=$c timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --steps 10 --warmup 3 --no-cpu --no-kernels > gpurun_out/r1l_bench_n8_cta$c.json 2> gpurun_out/r1l_bench_n8_cta$c.err
-done
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus 8 --steps 10 --warmup 3 --no-cpu --no-kernels > gpurun_out/r1p_bench_n8.json 2> gpurun_out/r1p_bench_n8.err
 true
