@@ -25,7 +25,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-DEFAULT_BUCKET_BYTES = 64 << 20
+DEFAULT_BUCKET_BYTES = int(os.environ.get("SDB_DP_BUCKET_MB", "64")) << 20
 
 
 def build_buckets(ranges: Dict[str, Tuple[int, int]], bucket_elems: int) -> List[Tuple[int, int, List[str]]]:
@@ -74,7 +74,7 @@ class GradReducer:
         # close the current graph segment, and at replay time the recorded buckets are all-reduced eagerly on the
         # communication stream right after that segment has been enqueued (replay_segment_buckets / replay_finish).
         self.capture = None          # callable(force: bool) -> None that cuts the graph segment
-        self.capture_cut_every = 8
+        self.capture_cut_every = int(os.environ.get("SDB_DP_CUT", "8"))
         self._deferred: List[int] = []
         self.before_issue = None     # callable() run before a bucket is handed to the collective / the capturer
 
