@@ -356,14 +356,17 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
 }
 
 // =============================================== backward ===============================================
-// 416 threads: warps 0-7 = compute (warp w and w+4 own the same 32 rows and split the columns of a block in halves; no
-// row reductions are needed in backward because lse and D are inputs), warp 9 = TMA producer, and FOUR tcgen05.mma
-// issuers — warp 8 scores (+ TMEM owner), warp 10 dP, warp 11 first accumulator (dK / dQ), warp 12 second accumulator
-// (dV, mode 0) — because one thread issues at most one MMA per ~63 ns (see the forward kernel's note) and a block
-// needs 14 of them. With nbuf = 2 (head dim <= 128) S / dP are double-buffered in TMEM and P^T / dS^T in shared
+// 672 threads: warps 0-15 = compute (warps w, w+4, w+8, w+12 own the same 32 rows and split the 64 columns of a block in
+// quarters; no row reductions are needed in backward because lse and D are inputs), warp 17 = TMA producer, and FOUR
+// tcgen05.mma issuers — warp 16 scores (+ TMEM owner), warp 18 dP, warp 19 first accumulator (dK / dQ), warp 20 second
+// accumulator (dV, mode 0) — because one thread issues at most one MMA per ~63 ns (see the forward kernel's note) and
+// a block needs 14 of them. Sixteen compute warps (four per scheduler) rather than eight: the kernel is bound by the
+// compute warps' exp2 / conversion / staging instruction stream, whose TMEM-load and MUFU latencies two warps per
+// scheduler could not hide (46 % issue utilisation, profiles/r1n_ncu_full.md). With nbuf = 2 (head dim <= 128) S / dP are double-buffered in TMEM and P^T / dS^T in shared
 // memory, so the tensor pipe computes block i+1's scores and block i-1's accumulations while the compute warps run
 // the exp2 / dS arithmetic of block i.
-constexpr int kBwdThreads = 416;
+constexpr int kBwdThreads = 672;
+constexpr int kBwdComputeThreads = 512;
 constexpr int kBwdMaxStages = 4;
 
 struct BwdParams {
@@ -405,12 +408,13 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   uint64_t* bar_SdP = c_empty + kBwdMaxStages;     // [2]
   uint64_t* bar_PdS = bar_SdP + 2;                 // [2]
   uint64_t* bar_acc = bar_PdS + 2;                 // [2]
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_acc + 2);
+  uint64_t* bar_done = bar_acc + 2;                // every accumulation of the CTA has completed
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_done + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int r0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
 
-  if (warp == 9 && lane == 0) {
+  if (warp == 17 && lane == 0) {
     ptx::tma_prefetch_desc(&p.mapR1);
     ptx::tma_prefetch_desc(&p.mapR2);
     ptx::tma_prefetch_desc(&p.mapC1);
@@ -423,12 +427,13 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&bar_SdP[s], 2);
-      ptx::mbar_init(&bar_PdS[s], 256);
+      ptx::mbar_init(&bar_PdS[s], NBUF == 2 ? 256 : kBwdComputeThreads);
       ptx::mbar_init(&bar_acc[s], kAccIssuers);
     }
+    ptx::mbar_init(bar_done, kAccIssuers);
     ptx::fence_barrier_init();
   }
-  if (warp == 8) {
+  if (warp == 16) {
     ptx::tmem_alloc(tmem_ptr_smem, 512);
     ptx::tmem_relinquish();
   }
@@ -442,7 +447,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc * (uint32_t)NBUF;
   const uint32_t tA2 = tA1 + (uint32_t)p.dpad;
 
-  if (warp == 9) {
+  if (warp == 17) {
     if (lane == 0) {
       ptx::mbar_expect_tx(barR, 2 * rtile);
       tma_tile(sR1, &p.mapR1, barR, p.atoms, kAtom128, r0, h, b);
@@ -455,10 +460,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         tma_tile(sC2 + (size_t)s * ctile, &p.mapC2, &c_full[s], p.atoms, catom, i * p.bc, h, b);
       }
     }
-  } else if (warp == 8 || warp == 10) {
-    // ===================== score issuers: warp 8  S = R1 C1^T,  warp 10  dP = R2 C2^T =====================
+  } else if (warp == 16 || warp == 18) {
+    // ===================== score issuers: warp 16  S = R1 C1^T,  warp 18  dP = R2 C2^T =====================
     if (lane == 0) {
-      const bool second = warp == 10;
+      const bool second = warp == 18;
       const uint32_t idescS = ptx::umma_idesc_bf16(p.bc, 0, 0);
       const uint64_t dR = ptx::umma_desc_sw128(ptx::smem_u32(second ? sR2 : sR1), 0u, 1024u);
       const uint64_t dCk = ptx::umma_desc_sw128(ptx::smem_u32(second ? sC2 : sC1), 0u, 1024u);  // column tile as K-major B
@@ -479,10 +484,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         if (++ss == p.stages) { ss = 0; sph ^= 1u; }
       }
     }
-  } else if (warp == 11 || warp == 12) {
-    // ===================== accumulate issuers: warp 11  A1 += dS C1,  warp 12 (mode 0)  A2 += P^T C2 =====================
-    if (lane == 0 && (warp == 11 || MODE == 0)) {
-      const bool second = warp == 12;
+  } else if (warp == 19 || warp == 20) {
+    // ===================== accumulate issuers: warp 19  A1 += dS C1,  warp 20 (mode 0)  A2 += P^T C2 =====================
+    if (lane == 0 && (warp == 19 || MODE == 0)) {
+      const bool second = warp == 20;
       const uint32_t idescA = ptx::umma_idesc_bf16(p.dpad, 0, 1);
       const uint64_t dCm = ptx::umma_desc_sw128(ptx::smem_u32(second ? sC2 : sC1), catom, 1024u);  // MN-major B
       const uint64_t dA0 = ptx::umma_desc_sw128(ptx::smem_u32(second ? sPT : sDS), 0u, 1024u);
@@ -502,10 +507,20 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         ptx::umma_commit(&bar_acc[buf]);
         if (++as == p.stages) { as = 0; aph ^= 1u; }
       }
+      ptx::umma_commit(bar_done);
     }
   } else {
-    // ===================== compute threads: thread = (row, column half) =====================
-    const int q4 = warp & 3, half = warp >> 2;
+    // ===================== compute threads =====================
+    // Two independent groups of 8 warps: group g works on the column blocks i = g, g + 2, ... (TMEM / smem buffer g),
+    // thread = (row, column half) inside a group. The groups run out of phase, so on every scheduler one pair of warps
+    // computes while the other waits for its block's MMAs (with all 16 warps on the same block everybody waited at
+    // the same time).
+    const int q4 = warp & 3, part = warp >> 2;       // part: column quarter for the final drain
+    const int grp = (NBUF == 2) ? (warp >> 3) : 0;   // single-buffered (head dim > 128): one group of 16 warps
+    const int nsub = (NBUF == 2) ? 2 : 4;            // column slices per block inside a group
+    const int sub = (NBUF == 2) ? ((warp >> 2) & 1) : part;
+    const int gthreads = (NBUF == 2) ? 256 : 512;
+    const int gtid = (NBUF == 2) ? ((int)threadIdx.x & 255) : (int)threadIdx.x;
     const int row = q4 * 32 + lane;
     const uint32_t lane_base = ((uint32_t)(q4 * 32)) << 16;
     const int r = r0 + row;
@@ -517,12 +532,12 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       rowA = (r < p.Sq) ? -p.lse2[bh * p.Sq + r] : -INFINITY;
       rowD = (r < p.Sq) ? p.dvec[bh * p.Sq + r] : 0.f;
     }
-    // per-column metadata of block i, fetched one block ahead into registers by the first bc threads.
+    // per-column metadata of block i, fetched one block ahead into registers by the first bc threads of the group.
     // MODE 1 needs it only when a key bias is given or the block is cut by Skv (plain blocks skip the LDS entirely).
     float nA = 0.f, nB = 0.f;
     auto fetch_cols = [&](int i) {
-      if ((int)threadIdx.x < p.bc && i < p.ncb) {
-        const int c = i * p.bc + (int)threadIdx.x;
+      if (gtid < p.bc && i < p.ncb) {
+        const int c = i * p.bc + gtid;
         if (MODE == 0) {
           nA = (c < p.Sq) ? -p.lse2[bh * p.Sq + c] : -INFINITY;
           nB = (c < p.Sq) ? p.dvec[bh * p.Sq + c] : 0.f;
@@ -531,20 +546,23 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         }
       }
     };
-    fetch_cols(0);
-    const int hc = p.bc / 2;        // columns per thread per block
-    const int ncc = hc / 32;        // 32-column chunks per thread
-    for (int i = 0; i < p.ncb; ++i) {
-      float* cA = sColA + (i & 1) * 128;
-      float* cB = sColB + (i & 1) * 128;
+    const int istep = (NBUF == 2) ? 2 : 1;
+    fetch_cols(grp);
+    const int wcols = p.bc / nsub;        // 32 (two slices) or 16 (four slices) columns per thread and block
+    for (int i = grp; i < p.ncb; i += istep) {
+      const int buf = i & (NBUF - 1);     // == grp when double-buffered
+      float* cA = sColA + buf * 128;
+      float* cB = sColB + buf * 128;
       const bool col_meta = (MODE == 0) || (p.kbias2 != nullptr) || ((i + 1) * p.bc > p.Skv);
-      if ((int)threadIdx.x < p.bc) {
-        cA[threadIdx.x] = nA;
-        if (MODE == 0) cB[threadIdx.x] = nB;
+      // the group's previous block (i - istep) used the same cA/cB: every thread of the group has finished reading
+      // them before it arrived on bar_PdS, and this barrier orders those reads before the overwrite below
+      ptx::named_bar_sync(1 + grp, gthreads);
+      if (gtid < p.bc) {
+        cA[gtid] = nA;
+        if (MODE == 0) cB[gtid] = nB;
       }
-      ptx::named_bar_sync(1, 256);
-      fetch_cols(i + 1);
-      const int buf = i & (NBUF - 1);
+      ptx::named_bar_sync(1 + grp, gthreads);
+      fetch_cols(i + istep);
       ptx::mbar_wait_sleep(&bar_SdP[buf], (uint32_t)((i >> (NBUF - 1)) & 1), 20);
       ptx::tc_fence_after();
       if (i >= NBUF) ptx::mbar_wait_sleep(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1), 20);  // P^T/dS^T[buf] free
@@ -553,18 +571,18 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       uint8_t* tileP = sPT + (size_t)buf * ptile;
       uint8_t* tileD = sDS + (size_t)buf * ptile;
 #pragma unroll 1
-      for (int cc = 0; cc < ncc; ++cc) {
-        const int col0 = half * hc + cc * 32;
-        uint32_t sv[32], dv[32];
-        ptx::tmem_ld_32x32(tSi + col0, sv);
-        ptx::tmem_ld_32x32(tdPi + col0, dv);
+      for (int cc = 0; cc < wcols; cc += 16) {
+        const int col0 = sub * wcols + cc;
+        uint32_t sv[16], dv[16];
+        ptx::tmem_ld_32x16(tSi + col0, sv);
+        ptx::tmem_ld_32x16(tdPi + col0, dv);
         ptx::tmem_ld_wait();
-        float pv[32], ds[32];  // dS without the softmax scale: it is applied once when the accumulator is drained
+        float pv[16], ds[16];  // dS without the softmax scale: it is applied once when the accumulator is drained
         if (col_meta) {
           const float4* cA4 = reinterpret_cast<const float4*>(cA + col0);
           const float4* cB4 = reinterpret_cast<const float4*>(cB + col0);
 #pragma unroll
-          for (int k4 = 0; k4 < 8; ++k4) {
+          for (int k4 = 0; k4 < 4; ++k4) {
             const float4 a4 = cA4[k4];
             const float av[4] = {a4.x, a4.y, a4.z, a4.w};
             float bv[4] = {rowD, rowD, rowD, rowD};
@@ -582,29 +600,27 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
           }
         } else {
 #pragma unroll
-          for (int k = 0; k < 32; ++k) {
+          for (int k = 0; k < 16; ++k) {
             const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, rowA));
             pv[k] = pk;
             ds[k] = pk * (u2f(dv[k]) - rowD);
           }
         }
-        uint8_t* atomP = tileP + (col0 >> 6) * kAtom128;
-        uint8_t* atomD = tileD + (col0 >> 6) * kAtom128;
-        const int chunk0 = (col0 & 63) >> 3;
+        const int chunk0 = col0 >> 3;  // bc = 64: one swizzle atom per tile
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 0; c < 2; ++c) {
           uint4 o;
           o.x = sdb::pack_bf16x2(ds[c * 8 + 0], ds[c * 8 + 1]);
           o.y = sdb::pack_bf16x2(ds[c * 8 + 2], ds[c * 8 + 3]);
           o.z = sdb::pack_bf16x2(ds[c * 8 + 4], ds[c * 8 + 5]);
           o.w = sdb::pack_bf16x2(ds[c * 8 + 6], ds[c * 8 + 7]);
-          st_swz(atomD, row, chunk0 + c, o);
+          st_swz(tileD, row, chunk0 + c, o);
           if (MODE == 0) {
             o.x = sdb::pack_bf16x2(pv[c * 8 + 0], pv[c * 8 + 1]);
             o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
             o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
             o.w = sdb::pack_bf16x2(pv[c * 8 + 6], pv[c * 8 + 7]);
-            st_swz(atomP, row, chunk0 + c, o);
+            st_swz(tileP, row, chunk0 + c, o);
           }
         }
       }
@@ -612,12 +628,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       ptx::tc_fence_before();
       ptx::mbar_arrive(&bar_PdS[buf]);
     }
-    // ---- drain the accumulators (commits complete in order: the last one covers all) ----
-    {
-      const int last = p.ncb - 1;
-      ptx::mbar_wait(&bar_acc[last & (NBUF - 1)], (uint32_t)((last >> (NBUF - 1)) & 1));
-      ptx::tc_fence_after();
-    }
+    // ---- drain the accumulators: bar_done completes when every issuer's last accumulation has (a thread must not
+    // wait on bar_acc of the OTHER group's buffer: it has not followed that barrier's phases) ----
+    ptx::mbar_wait(bar_done, 0);
+    ptx::tc_fence_after();
     const bool valid = r < p.Srow;
     for (int which = 0; which < (MODE == 0 ? 2 : 1); ++which) {
       const uint32_t tA = which == 0 ? tA1 : tA2;
@@ -625,7 +639,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       __nv_bfloat16* base = which == 0 ? p.out1 : p.out2;
       const long long ld = which == 0 ? p.ld1 : p.ld2;
       __nv_bfloat16* orow = base + ((long long)b * p.Srow + r) * ld + (long long)h * p.d;
-      for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {
+      for (int c0 = part * 16; c0 < p.dpad; c0 += 64) {
         uint32_t v[16];
         ptx::tmem_ld_32x16(tA + lane_base + c0, v);
         ptx::tmem_ld_wait();
@@ -648,7 +662,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
 
   ptx::tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == 16) {
     ptx::tc_fence_after();
     ptx::tmem_dealloc(tmem_base, 512);
   }
