@@ -490,7 +490,7 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
   }
   p.b_stage_bytes = (p.b_stage_bytes + 1023u) & ~1023u;
   p.stage_bytes = p.a_stage_bytes + p.b_stage_bytes;
-  const uint32_t budget = 200 * 1024;
+  const uint32_t budget = 225 * 1024;  // 227 KB per CTA minus the alignment slack and the barriers
   int stages = (int)(budget / p.stage_bytes);
   if (stages > kMaxStages) stages = kMaxStages;
   if (stages < 2) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_gemm_tc: stage too large");

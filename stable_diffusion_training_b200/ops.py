@@ -62,7 +62,7 @@ def _kblock_clks(mt: int, bn: int, b_mn: bool) -> float:
         thread; two issuing threads (mt == 2, one per 128-row half) overlap operand fetches: ~40 + 0.355*bn each."""
     bcols = -(-bn // 64) * 64 if b_mn else bn
     stage_bytes = (128 * mt + bcols) * 128
-    stages = max(1, min(8, (200 * 1024) // stage_bytes))
+    stages = max(1, min(8, (225 * 1024) // stage_bytes))
     delivery = 3000.0 / stages
     mma = 4 * max(95.0, bn / 2 + 40.5) if mt == 1 else 8 * max(62.0, 40.0 + 0.355 * bn)
     return max(delivery, mma)
