@@ -9,7 +9,9 @@
 // of channel vectors (so gamma/beta and the per-channel accumulators live in registers) and strides over pixel rows.
 #include "sdb_common.cuh"
 #include "../../include/sdb200.h"
+#include <atomic>
 #include <cstdlib>
+#include <mutex>
 
 namespace {
 
@@ -288,18 +290,28 @@ __global__ void gn_param_grad_kernel(const float2* __restrict__ chan_tot, float*
 // (deterministic) -> pass 2 (normalise) re-reads the rows it has just read (L1/L2 hits). Replaces the partial /
 // finalize / param-grad / apply chain above (3-4 launches whose dependent start-up latency dominated on the L2-sized
 // feature maps of this UNet); that chain remains the fallback when the grid cannot be co-resident.
-//   sync[b]      arrivals of sample b          sync[B]  arrivals of the whole grid (backward: parameter gradients)
-// The counters are zeroed by a memset node in front of the launch.
-__device__ __forceinline__ void gn_arrive_and_wait(unsigned int* counter, unsigned int expected) {
+//   sync[b] arrivals of sample b, sync[B+b] CTAs past the wait, sync[2B] arrivals of the whole grid (backward: parameter
+//   gradients). The counters live in a static device array, zero at rest: the last CTA through resets them.
+__device__ __forceinline__ void gn_arrive_and_wait(unsigned int* counter, unsigned int* passed, unsigned int expected) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     atomicAdd(counter, 1u);
     while (*reinterpret_cast<volatile unsigned int*>(counter) < expected) __nanosleep(40);
     __threadfence();
+    // the last CTA to get past the wait leaves both counters zeroed for the next launch that uses this slot
+    if (atomicAdd(passed, 1u) == expected - 1u) {
+      *counter = 0u;
+      *passed = 0u;
+    }
   }
   __syncthreads();
 }
+
+// Arrival counters of the fused kernel: zero at rest (self-resetting), one slot per launch in flight.
+constexpr int kGnSyncSlots = 256;
+constexpr int kGnSyncInts = 160;   // per slot: [0..B) arrivals, [B..2B) passed, [2B] grid arrivals -> B <= 79
+__device__ unsigned int g_gn_sync[kGnSyncSlots * kGnSyncInts];
 
 template <int KC, bool BWD, bool SILU>
 __global__ void __launch_bounds__(256, 2)
@@ -325,18 +337,27 @@ gn_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   {
     float a0[KC][8], a1[KC][8], sc[KC][8], sh[KC][8], rs_[KC][8], xb[KC][8];
 #pragma unroll
-    for (int k = 0; k < KC; ++k)
+    for (int k = 0; k < KC; ++k) {
+      const int cbase = (tc + k * s.TC) * 8;
+      int g = cbase / s.cpg, gend = (g + 1) * s.cpg;  // one division per vector: the group index only steps forward
+      float gmv[8], btv[8];
+      if (BWD) {
+        const float4 g0 = sdb::ld_f4(gamma + cbase), g1 = sdb::ld_f4(gamma + cbase + 4);
+        const float4 b0 = sdb::ld_f4(beta + cbase), b1 = sdb::ld_f4(beta + cbase + 4);
+        gmv[0] = g0.x; gmv[1] = g0.y; gmv[2] = g0.z; gmv[3] = g0.w; gmv[4] = g1.x; gmv[5] = g1.y; gmv[6] = g1.z; gmv[7] = g1.w;
+        btv[0] = b0.x; btv[1] = b0.y; btv[2] = b0.z; btv[3] = b0.w; btv[4] = b1.x; btv[5] = b1.y; btv[6] = b1.z; btv[7] = b1.w;
+      }
+      float2 st = BWD ? stats[b * kGroups + g] : make_float2(0.f, 0.f);
 #pragma unroll
       for (int i = 0; i < 8; ++i) {
         a0[k][i] = 0.f; a1[k][i] = 0.f;
         if (BWD) {
-          const int c = (tc + k * s.TC) * 8 + i;
-          const float2 st = stats[b * kGroups + c / s.cpg];
-          const float gm = gamma[c];
+          while (cbase + i >= gend) { ++g; gend += s.cpg; st = stats[b * kGroups + g]; }
           rs_[k][i] = st.y; xb[k][i] = -st.x * st.y;              // xhat = x*rs + xb
-          sc[k][i] = st.y * gm; sh[k][i] = fmaf(-st.x * st.y, gm, beta[c]);  // z = x*sc + sh
+          sc[k][i] = st.y * gmv[i]; sh[k][i] = fmaf(-st.x * st.y, gmv[i], btv[i]);  // z = x*sc + sh
         }
       }
+    }
     if (rl < s.RL) {
       for (int r = r0 + rl; r < r1; r += kGnUnroll * s.RL) {
         uint4 xr[kGnUnroll][KC], dr[kGnUnroll][KC];
@@ -406,7 +427,7 @@ gn_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   }
 
   // ---------------- exchange: wait for the other chunks of this sample ----------------
-  gn_arrive_and_wait(&sync[b], (unsigned int)s.chunks);
+  gn_arrive_and_wait(&sync[b], &sync[s.B + b], (unsigned int)s.chunks);
   {
     // full warps only (the block has 129..256 threads): warp `slice` folds chunks slice, slice + nslices, ...
     const int g = threadIdx.x & 31, slice = threadIdx.x >> 5, nslices = nthr >> 5;
@@ -450,8 +471,9 @@ gn_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
       __syncthreads();
       if (threadIdx.x == 0) {
         __threadfence();
-        const unsigned int old = atomicAdd(&sync[s.B], 1u);
+        const unsigned int old = atomicAdd(&sync[2 * s.B], 1u);
         s_last = (old == (unsigned int)(s.B * s.chunks) - 1u) ? 1 : 0;
+        if (s_last) sync[2 * s.B] = 0u;  // self-reset
         __threadfence();
       }
     }
@@ -473,20 +495,29 @@ gn_fused_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __rest
   if (rl >= s.RL) return;
   float sc[KC][8], sh[KC][8], rs_[KC][8], xb[KC][8], rA[KC][8], rB[KC][8];
 #pragma unroll
-  for (int k = 0; k < KC; ++k)
+  for (int k = 0; k < KC; ++k) {
+    const int cbase = (tc + k * s.TC) * 8;
+    int g = cbase / s.cpg, gend = (g + 1) * s.cpg;
+    const float4 g0 = sdb::ld_f4(gamma + cbase), g1 = sdb::ld_f4(gamma + cbase + 4);
+    const float4 b0 = sdb::ld_f4(beta + cbase), b1 = sdb::ld_f4(beta + cbase + 4);
+    const float gmv[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const float btv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    float2 st = BWD ? stats[b * kGroups + g] : s_grp[g];
+    float2 gg = s_grp[g];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int c = (tc + k * s.TC) * 8 + i;
-      const int g = c / s.cpg;
-      const float2 st = BWD ? stats[b * kGroups + g] : s_grp[g];
-      const float gm = gamma[c];
-      sc[k][i] = st.y * gm; sh[k][i] = fmaf(-st.x * st.y, gm, beta[c]);
+      while (cbase + i >= gend) {
+        ++g; gend += s.cpg;
+        st = BWD ? stats[b * kGroups + g] : s_grp[g];
+        gg = s_grp[g];
+      }
+      sc[k][i] = st.y * gmv[i]; sh[k][i] = fmaf(-st.x * st.y, gmv[i], btv[i]);
       if (BWD) {
-        const float2 gg = s_grp[g];
         rs_[k][i] = st.y; xb[k][i] = -st.x * st.y;
         rA[k][i] = st.y * gg.x; rB[k][i] = st.y * gg.y;
       }
     }
+  }
   for (int r = r0 + rl; r < r1; r += kGnUnroll * s.RL) {
     uint4 xr[kGnUnroll][KC], dr[kGnUnroll][KC], ar[kGnUnroll][KC];
 #pragma unroll
@@ -551,6 +582,14 @@ size_t gn_fused_ws_bytes(const GnShape& s) {
 
 // Co-resident grid for the fused kernel: chunks per sample = min(rows / RL, capacity / B). Returns false when the
 // samples alone exceed the capacity (fall back to the multi-launch path).
+unsigned int* gn_sync_slot() {
+  static unsigned int* base = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] { cudaGetSymbolAddress(reinterpret_cast<void**>(&base), g_gn_sync); });
+  static std::atomic<unsigned int> next{0};
+  return base + (size_t)kGnSyncInts * (next.fetch_add(1u) % (unsigned)kGnSyncSlots);
+}
+
 // SDB_GN_LEGACY=1 keeps the multi-launch path (A/B timing and a second implementation for the parity tests)
 bool gn_force_legacy() {
   static const bool v = getenv("SDB_GN_LEGACY") != nullptr && atoi(getenv("SDB_GN_LEGACY")) != 0;
@@ -832,11 +871,10 @@ extern "C" int sdb_groupnorm_fwd(const void* x, const float* gamma, const float*
     if (s.KC == 1) { if (silu) GN_PLAN(1, true); else GN_PLAN(1, false); }
     else { if (silu) GN_PLAN(2, true); else GN_PLAN(2, false); }
 #undef GN_PLAN
-    if (ok && gn_fused_ws_bytes(f) <= ws_bytes) {
-      unsigned int* sync = reinterpret_cast<unsigned int*>(workspace);
+    if (ok && gn_fused_ws_bytes(f) <= ws_bytes && 2 * B + 1 <= kGnSyncInts) {
+      unsigned int* sync = gn_sync_slot();
       const size_t sync_bytes = (((size_t)B + 1) * 4 + 255) / 256 * 256;
       float2* part_g = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(workspace) + sync_bytes);
-      cudaMemsetAsync(sync, 0, sync_bytes, stream);
       const dim3 fgrid(f.chunks, B);
 #define GN_FUSED(KC_, SILU_)                                                                                        \
   gn_fused_kernel<KC_, false, SILU_><<<fgrid, threads, sm, stream>>>(xp, nullptr, st, gamma, beta, nullptr, yp, part_g, \
@@ -887,13 +925,12 @@ extern "C" int sdb_groupnorm_bwd(const void* x, const void* dy, const float* sta
     if (s.KC == 1) { if (silu) GN_PLAN(1, true); else GN_PLAN(1, false); }
     else { if (silu) GN_PLAN(2, true); else GN_PLAN(2, false); }
 #undef GN_PLAN
-    if (ok && gn_fused_ws_bytes(f) <= ws_bytes) {
-      unsigned int* sync = reinterpret_cast<unsigned int*>(workspace);
+    if (ok && gn_fused_ws_bytes(f) <= ws_bytes && 2 * B + 1 <= kGnSyncInts) {
+      unsigned int* sync = gn_sync_slot();
       const size_t sync_bytes = (((size_t)B + 1) * 4 + 255) / 256 * 256;
       float2* part_g = reinterpret_cast<float2*>(reinterpret_cast<uint8_t*>(workspace) + sync_bytes);
       float2* part_c = part_g + (size_t)f.B * f.chunks * kGroups;
       float2* ctot = part_c + (size_t)f.B * f.chunks * f.C;
-      cudaMemsetAsync(sync, 0, sync_bytes, stream);
       const dim3 fgrid(f.chunks, B);
 #define GN_FUSED(KC_, SILU_)                                                                                          \
   gn_fused_kernel<KC_, true, SILU_><<<fgrid, threads, sm, stream>>>(xp, dyp, const_cast<float2*>(st), gamma, beta, addp, \
