@@ -103,13 +103,21 @@ class GradReducer:
     def _all_reduce_bucket(self, b: int) -> None:
         s, e, _ = self.buckets[b]
         self.issued_order.append(b)
-        if self.before_issue is not None:
-            self.before_issue()  # e.g. unet.Graph.join: parameter gradients are produced on a second stream
         if self.capture is not None:
+            # graph capture: the bucket is reduced eagerly after the segment that completes it has been replayed, so the
+            # second (parameter-gradient) stream only has to be joined where a segment is cut, not at every bucket
             self._deferred.append(b)
-            if len(self._deferred) >= self.capture_cut_every:
+            # the buckets of a segment are reduced after the whole segment: keep the LAST segments short (2 buckets) so
+            # little communication is left exposed between the end of backward and the optimizer
+            remaining = len(self.buckets) - (b + 1)
+            every = self.capture_cut_every if remaining >= self.capture_cut_every else min(2, self.capture_cut_every)
+            if len(self._deferred) >= every:
+                if self.before_issue is not None:
+                    self.before_issue()
                 self.capture(False)
             return
+        if self.before_issue is not None:
+            self.before_issue()  # e.g. unet.Graph.join: parameter gradients are produced on a second stream
         if self.world_size == 1:
             return
         view = self.grad[s:e]
