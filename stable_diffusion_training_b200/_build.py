@@ -23,7 +23,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr",
     "-I", INCLUDE,
-]
+] + [f for f in os.environ.get("NVCC_EXTRA", "").split() if f]  # e.g. -DSDB_GEMM_EXPERIMENTS, -DSDB_ATTN_TIMELINE
 
 
 def _nvcc() -> str:

@@ -26,6 +26,21 @@
 #include <cmath>
 #include <mutex>
 
+// -DSDB_ATTN_TIMELINE: CTA (0,0,0) of the backward kernel records clock64() at its hand-off points (tools/attn_timeline.py)
+#ifdef SDB_ATTN_TIMELINE
+__device__ long long g_attn_tl[8 * 64 * 4];
+#define SDB_TL(role, i, slot)                                                                   \
+  do {                                                                                          \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) >= 8 && (i) < 72)          \
+      g_attn_tl[((role) * 64 + ((i) - 8)) * 4 + (slot)] = clock64();                            \
+  } while (0)
+extern "C" int sdb_attn_timeline(long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_attn_tl, sizeof(long long) * 8 * 64 * 4);
+}
+#else
+#define SDB_TL(role, i, slot) do {} while (0)
+#endif
+
 namespace {
 
 constexpr uint32_t kAtom128 = 128 * 128;  // bytes of a [128 rows x 64 bf16] swizzle atom column
@@ -476,11 +491,14 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         const int buf = i & (NBUF - 1);
         // S/dP buffer `buf` was last read by compute(i - NBUF), which arrives on bar_PdS after its TMEM loads
         if (i >= NBUF) ptx::mbar_wait_sleep(&bar_PdS[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
+        SDB_TL(second ? 1 : 0, i, 0);
         ptx::mbar_wait_sleep(&c_full[ss], sph);
         ptx::tc_fence_after();
+        SDB_TL(second ? 1 : 0, i, 1);
         const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + (second ? (uint32_t)p.bc : 0u);
         mma_ksteps<false>(tSi, dR, atom16, dCk + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
         ptx::umma_commit(&bar_SdP[buf]);
+        SDB_TL(second ? 1 : 0, i, 2);
         if (++ss == p.stages) { ss = 0; sph ^= 1u; }
       }
     }
@@ -498,13 +516,16 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       uint32_t aph = 0;
       for (int i = 0; i < p.ncb; ++i) {
         const int buf = i & (NBUF - 1);
+        SDB_TL(second ? 3 : 2, i, 0);
         ptx::mbar_wait_sleep(&bar_PdS[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
         ptx::mbar_wait_sleep(&c_full[as], aph);  // already complete (the scores of block i used it); orders the async proxy
         ptx::tc_fence_after();
+        SDB_TL(second ? 3 : 2, i, 1);
         mma_ksteps<true>(tA, dA0 + (uint32_t)buf * ptile16, atom16, dCm + (uint32_t)as * ctile16, 0u, idescA, k2,
                          i > 0 ? 1u : 0u);
         ptx::umma_commit(&c_empty[as]);
         ptx::umma_commit(&bar_acc[buf]);
+        SDB_TL(second ? 3 : 2, i, 2);
         if (++as == p.stages) { as = 0; aph ^= 1u; }
       }
       ptx::umma_commit(bar_done);
@@ -563,9 +584,12 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       }
       ptx::named_bar_sync(1 + grp, gthreads);
       fetch_cols(i + istep);
+      if (gtid == 0) SDB_TL(4 + grp, i, 0);
       ptx::mbar_wait_sleep(&bar_SdP[buf], (uint32_t)((i >> (NBUF - 1)) & 1), 20);
       ptx::tc_fence_after();
+      if (gtid == 0) SDB_TL(4 + grp, i, 1);
       if (i >= NBUF) ptx::mbar_wait_sleep(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1), 20);  // P^T/dS^T[buf] free
+      if (gtid == 0) SDB_TL(4 + grp, i, 2);
       const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + lane_base;
       const uint32_t tdPi = tSi + (uint32_t)p.bc;
       uint8_t* tileP = sPT + (size_t)buf * ptile;
@@ -627,6 +651,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       ptx::fence_proxy_async_smem();
       ptx::tc_fence_before();
       ptx::mbar_arrive(&bar_PdS[buf]);
+      if (gtid == 0) SDB_TL(4 + grp, i, 3);
     }
     // ---- drain the accumulators: bar_done completes when every issuer's last accumulation has (a thread must not
     // wait on bar_acc of the OTHER group's buffer: it has not followed that barrier's phases) ----
