@@ -31,7 +31,7 @@
 __device__ long long g_attn_tl[8 * 64 * 4];
 #define SDB_TL(role, i, slot)                                                                   \
   do {                                                                                          \
-    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) >= 8 && (i) < 72)          \
+    if (blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (i) >= 8 && (i) < 72 && (threadIdx.x & 31) == 0) \
       g_attn_tl[((role) * 64 + ((i) - 8)) * 4 + (slot)] = clock64();                            \
   } while (0)
 extern "C" int sdb_attn_timeline(long long* host_out) {
@@ -395,6 +395,7 @@ struct BwdParams {
   long long ld2;
   int mode;  // 0: rows = keys (out1 = dK, out2 = dV); 1: rows = queries (out1 = dQ)
   int B, H, Sq, Skv, Srow, Scol, d, dpad, atoms, bc, stages, ncb, nbuf;
+  int alias;  // 1: the bf16 P^T / dS^T operands overwrite the S / dP columns they came from (no TMEM left for a copy)
   float scale2, scale;
 };
 
@@ -407,26 +408,24 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   const uint32_t rtile = (uint32_t)p.atoms * kAtom128;          // row tile: 128 rows
   const uint32_t catom = (uint32_t)p.bc * 128u;                 // column tile atom: bc rows x 128 B
   const uint32_t ctile = (uint32_t)p.atoms * catom;
-  const uint32_t ptile = (uint32_t)(p.bc / 64) * kAtom128;      // [128 rows x bc] bf16
   uint8_t* sR1 = smem;
   uint8_t* sR2 = sR1 + rtile;
   uint8_t* sC1 = sR2 + rtile;
   uint8_t* sC2 = sC1 + (size_t)p.stages * ctile;
-  uint8_t* sPT = sC2 + (size_t)p.stages * ctile;                // [nbuf]
-  uint8_t* sDS = sPT + (size_t)NBUF * ptile;                    // [NBUF]
-  float* sColA = reinterpret_cast<float*>(sDS + (size_t)NBUF * ptile);    // [2][128]
+  float* sColA = reinterpret_cast<float*>(sC2 + (size_t)p.stages * ctile);  // [2][128]
   float* sColB = sColA + 256;                                             // [2][128]
   uint64_t* bars = reinterpret_cast<uint64_t*>(sColB + 256);
   uint64_t* barR = bars;
   uint64_t* c_full = bars + 1;                     // [kBwdMaxStages]
   uint64_t* c_empty = c_full + kBwdMaxStages;      // [kBwdMaxStages]
   uint64_t* bar_SdP = c_empty + kBwdMaxStages;     // [2]
-  uint64_t* bar_PdS = bar_SdP + 2;                 // [2]
-  uint64_t* bar_acc = bar_PdS + 2;                 // [2]
+  uint64_t* bar_Sfree = bar_SdP + 2;               // [2]  compute has the scores of the buffer in registers
+  uint64_t* bar_PdS = bar_Sfree + 2;               // [2]  bf16 P^T / dS^T of the buffer written to tensor memory
+  uint64_t* bar_acc = bar_PdS + 2;                 // [2]  accumulation that read them complete
   uint64_t* bar_done = bar_acc + 2;                // every accumulation of the CTA has completed
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_done + 1);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = ptx::warp_idx_uniform(), lane = threadIdx.x & 31;
   const int r0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
 
   if (warp == 17 && lane == 0) {
@@ -442,6 +441,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     }
     for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&bar_SdP[s], 2);
+      ptx::mbar_init(&bar_Sfree[s], NBUF == 2 ? 256 : kBwdComputeThreads);
       ptx::mbar_init(&bar_PdS[s], NBUF == 2 ? 256 : kBwdComputeThreads);
       ptx::mbar_init(&bar_acc[s], kAccIssuers);
     }
@@ -457,10 +457,23 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
   sdb::pdl_wait();  // prologue above overlaps the previous kernel's tail
-  // [S0 | dP0 | (S1 | dP1) | A1 | A2]
+  // [S0 | dP0 | (S1 | dP1) | A1 | A2 | bf16 operands: (dS^T0 | P^T0) (dS^T1 | P^T1)]. The compute warps hand P^T / dS^T to
+  // the accumulating MMAs THROUGH TENSOR MEMORY (A operand from TMEM): shared memory carries only the TMA tiles, and it
+  // was the saturated resource when the operands were staged there (profiles/r1w_attn_bwd_timeline.md). A thread owns
+  // row = lane and writes the 16 columns of a slice it has just processed as 8 packed columns; k-step k of a block
+  // starts at column (k / kps) * slice_stride + (k % kps) * 8 with kps = k-steps per thread slice. When 512 columns
+  // cannot hold a separate copy (p.alias) the operands overwrite the front of each thread slice of S / dP in place.
   const uint32_t tS = tmem_base;
   const uint32_t tA1 = tmem_base + 2u * (uint32_t)p.bc * (uint32_t)NBUF;
   const uint32_t tA2 = tA1 + (uint32_t)p.dpad;
+  const uint32_t tOp = tA1 + (MODE == 0 ? 2u : 1u) * (uint32_t)p.dpad;  // separate operand copies (not aliased)
+  const uint32_t op_stride = (MODE == 0 ? 2u : 1u) * (uint32_t)(p.bc / 2);
+  const int wcols_k = p.bc / (NBUF == 2 ? 2 : 4);                           // columns per thread slice
+  const uint32_t slice_stride = p.alias ? (uint32_t)wcols_k : (uint32_t)(wcols_k / 2);
+  auto op_base = [&](int buf, bool pt) -> uint32_t {  // pt: P^T (second accumulator), else dS^T
+    if (p.alias) return tS + (uint32_t)buf * 2u * (uint32_t)p.bc + (pt ? 0u : (uint32_t)p.bc);
+    return tOp + (uint32_t)buf * op_stride + (pt ? (uint32_t)(p.bc / 2) : 0u);
+  };
 
   if (warp == 17) {
     if (lane == 0) {
@@ -477,7 +490,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
     }
   } else if (warp == 16 || warp == 18) {
     // ===================== score issuers: warp 16  S = R1 C1^T,  warp 18  dP = R2 C2^T =====================
-    if (lane == 0) {
+    // (whole warp, warp-uniform values, MMAs under elect: see ptx::elect_one)
+    {
       const bool second = warp == 18;
       const uint32_t idescS = ptx::umma_idesc_bf16(p.bc, 0, 0);
       const uint64_t dR = ptx::umma_desc_sw128(ptx::smem_u32(second ? sR2 : sR1), 0u, 1024u);
@@ -489,28 +503,35 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       ptx::mbar_wait(barR, 0);
       for (int i = 0; i < p.ncb; ++i) {
         const int buf = i & (NBUF - 1);
-        // S/dP buffer `buf` was last read by compute(i - NBUF), which arrives on bar_PdS after its TMEM loads
-        if (i >= NBUF) ptx::mbar_wait_sleep(&bar_PdS[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
+        // S/dP buffer `buf` was last read by compute(i - NBUF), which arrives on bar_Sfree as soon as the scores are
+        // in its registers (before the exp2 / pack / store work on them)
+        if (i >= NBUF) {
+          ptx::mbar_wait_sleep(&bar_Sfree[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
+          // aliased operands live in the S / dP columns until the accumulations of that block have read them
+          if (p.alias) ptx::mbar_wait_sleep(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
+        }
         SDB_TL(second ? 1 : 0, i, 0);
         ptx::mbar_wait_sleep(&c_full[ss], sph);
         ptx::tc_fence_after();
         SDB_TL(second ? 1 : 0, i, 1);
         const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + (second ? (uint32_t)p.bc : 0u);
-        mma_ksteps<false>(tSi, dR, atom16, dCk + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
-        ptx::umma_commit(&bar_SdP[buf]);
+        if (ptx::elect_one()) {
+          mma_ksteps<false>(tSi, dR, atom16, dCk + (uint32_t)ss * ctile16, catom16, idescS, ksteps, 0u);
+          ptx::umma_commit(&bar_SdP[buf]);
+        }
+        __syncwarp();
         SDB_TL(second ? 1 : 0, i, 2);
         if (++ss == p.stages) { ss = 0; sph ^= 1u; }
       }
     }
   } else if (warp == 19 || warp == 20) {
     // ===================== accumulate issuers: warp 19  A1 += dS C1,  warp 20 (mode 0)  A2 += P^T C2 =====================
-    if (lane == 0 && (warp == 19 || MODE == 0)) {
+    if (warp == 19 || MODE == 0) {
       const bool second = warp == 20;
       const uint32_t idescA = ptx::umma_idesc_bf16(p.dpad, 0, 1);
       const uint64_t dCm = ptx::umma_desc_sw128(ptx::smem_u32(second ? sC2 : sC1), catom, 1024u);  // MN-major B
-      const uint64_t dA0 = ptx::umma_desc_sw128(ptx::smem_u32(second ? sPT : sDS), 0u, 1024u);
-      const uint32_t atom16 = kAtom128 >> 4, ctile16 = ctile >> 4, ptile16 = ptile >> 4;
-      const int k2 = p.bc / 16;
+      const uint32_t ctile16 = ctile >> 4;
+      const int k2 = p.bc / 16, kps = wcols_k / 16;
       const uint32_t tA = second ? tA2 : tA1;
       int as = 0;
       uint32_t aph = 0;
@@ -521,14 +542,22 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         ptx::mbar_wait_sleep(&c_full[as], aph);  // already complete (the scores of block i used it); orders the async proxy
         ptx::tc_fence_after();
         SDB_TL(second ? 3 : 2, i, 1);
-        mma_ksteps<true>(tA, dA0 + (uint32_t)buf * ptile16, atom16, dCm + (uint32_t)as * ctile16, 0u, idescA, k2,
-                         i > 0 ? 1u : 0u);
-        ptx::umma_commit(&c_empty[as]);
-        ptx::umma_commit(&bar_acc[buf]);
+        const uint32_t aop = op_base(buf, second);
+        const uint64_t dB = dCm + (uint32_t)as * ctile16;
+        if (ptx::elect_one()) {
+          for (int k = 0, ks = 0, sl = 0; k < k2; ++k) {
+            ptx::umma_bf16_ts(tA, aop + (uint32_t)sl * slice_stride + (uint32_t)ks * 8u, dB + 128u * (uint32_t)k, idescA,
+                              (k > 0 || i > 0) ? 1u : 0u);
+            if (++ks == kps) { ks = 0; ++sl; }
+          }
+          ptx::umma_commit(&c_empty[as]);
+          ptx::umma_commit(&bar_acc[buf]);
+          if (i == p.ncb - 1) ptx::umma_commit(bar_done);
+        }
+        __syncwarp();
         SDB_TL(second ? 3 : 2, i, 2);
         if (++as == p.stages) { as = 0; aph ^= 1u; }
       }
-      ptx::umma_commit(bar_done);
     }
   } else {
     // ===================== compute threads =====================
@@ -588,12 +617,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       ptx::mbar_wait_sleep(&bar_SdP[buf], (uint32_t)((i >> (NBUF - 1)) & 1), 20);
       ptx::tc_fence_after();
       if (gtid == 0) SDB_TL(4 + grp, i, 1);
-      if (i >= NBUF) ptx::mbar_wait_sleep(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1), 20);  // P^T/dS^T[buf] free
-      if (gtid == 0) SDB_TL(4 + grp, i, 2);
       const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + lane_base;
       const uint32_t tdPi = tSi + (uint32_t)p.bc;
-      uint8_t* tileP = sPT + (size_t)buf * ptile;
-      uint8_t* tileD = sDS + (size_t)buf * ptile;
+      const uint32_t opD = op_base(buf, false) + lane_base + (uint32_t)sub * slice_stride;
+      const uint32_t opP = op_base(buf, true) + lane_base + (uint32_t)sub * slice_stride;
 #pragma unroll 1
       for (int cc = 0; cc < wcols; cc += 16) {
         const int col0 = sub * wcols + cc;
@@ -601,6 +628,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         ptx::tmem_ld_32x16(tSi + col0, sv);
         ptx::tmem_ld_32x16(tdPi + col0, dv);
         ptx::tmem_ld_wait();
+        if (cc + 16 >= wcols) {  // last slice loaded: the tensor pipe may overwrite S / dP[buf] with block i + NBUF
+          ptx::tc_fence_before();
+          ptx::mbar_arrive(&bar_Sfree[buf]);
+        }
         float pv[16], ds[16];  // dS without the softmax scale: it is applied once when the accumulator is drained
         if (col_meta) {
           const float4* cA4 = reinterpret_cast<const float4*>(cA + col0);
@@ -630,25 +661,23 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
             ds[k] = pk * (u2f(dv[k]) - rowD);
           }
         }
-        const int chunk0 = col0 >> 3;  // bc = 64: one swizzle atom per tile
+        // the operand columns of this buffer were last read by the accumulations of block i - NBUF
+        if (cc == 0 && i >= NBUF) {
+          ptx::mbar_wait_sleep(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1), 20);
+          ptx::tc_fence_after();
+        }
+        if (gtid == 0 && cc == 0) SDB_TL(4 + grp, i, 2);
+        uint32_t o[8];
 #pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint4 o;
-          o.x = sdb::pack_bf16x2(ds[c * 8 + 0], ds[c * 8 + 1]);
-          o.y = sdb::pack_bf16x2(ds[c * 8 + 2], ds[c * 8 + 3]);
-          o.z = sdb::pack_bf16x2(ds[c * 8 + 4], ds[c * 8 + 5]);
-          o.w = sdb::pack_bf16x2(ds[c * 8 + 6], ds[c * 8 + 7]);
-          st_swz(tileD, row, chunk0 + c, o);
-          if (MODE == 0) {
-            o.x = sdb::pack_bf16x2(pv[c * 8 + 0], pv[c * 8 + 1]);
-            o.y = sdb::pack_bf16x2(pv[c * 8 + 2], pv[c * 8 + 3]);
-            o.z = sdb::pack_bf16x2(pv[c * 8 + 4], pv[c * 8 + 5]);
-            o.w = sdb::pack_bf16x2(pv[c * 8 + 6], pv[c * 8 + 7]);
-            st_swz(tileP, row, chunk0 + c, o);
-          }
+        for (int c = 0; c < 8; ++c) o[c] = sdb::pack_bf16x2(ds[2 * c], ds[2 * c + 1]);
+        ptx::tmem_st_32x8(opD + (uint32_t)(cc >> 1), o);
+        if (MODE == 0) {
+#pragma unroll
+          for (int c = 0; c < 8; ++c) o[c] = sdb::pack_bf16x2(pv[2 * c], pv[2 * c + 1]);
+          ptx::tmem_st_32x8(opP + (uint32_t)(cc >> 1), o);
         }
       }
-      ptx::fence_proxy_async_smem();
+      ptx::tmem_st_wait();
       ptx::tc_fence_before();
       ptx::mbar_arrive(&bar_PdS[buf]);
       if (gtid == 0) SDB_TL(4 + grp, i, 3);
@@ -886,17 +915,22 @@ extern "C" int sdb_attn_bwd(const void* q, long long ldq, const void* k, long lo
     }
     const size_t rtile = (size_t)p.atoms * kAtom128;
     const size_t ctile = (size_t)p.atoms * p.bc * 128;
-    const size_t ptile = (size_t)(p.bc / 64) * kAtom128;
     int stages = 1;
     size_t fixed = 0;
     for (;;) {
-      fixed = 2 * rtile + 2 * (size_t)p.nbuf * ptile + 512 * sizeof(float) + 256 /*barriers*/ + 1024 /*align*/;
+      fixed = 2 * rtile + 512 * sizeof(float) + 256 /*barriers*/ + 1024 /*align*/;
       stages = (int)((227 * 1024 - (long long)fixed) / (long long)(2 * ctile));
       if (stages > kBwdMaxStages) stages = kBwdMaxStages;
       if (stages > p.ncb) stages = p.ncb;
       // the double-buffered schedule issues S/dP of block i+1 before block i's operands are released: needs 2 stages
       if (p.nbuf == 2 && p.ncb > 1 && stages < 2) { p.nbuf = 1; continue; }
       break;
+    }
+    {  // tensor memory: S / dP buffers, accumulators, and (when they fit) separate bf16 operand columns
+      const int nacc = mode == 0 ? 2 : 1;
+      const int need = 2 * p.bc * p.nbuf + nacc * p.dpad + p.nbuf * nacc * (p.bc / 2);
+      static const int alias_env = [] { const char* e = getenv("SDB_ATTN_ALIAS"); return e ? atoi(e) : 0; }();
+      p.alias = (need > 512 || alias_env) ? 1 : 0;
     }
     if (stages < 1) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_bwd: head dim %d needs too much smem", d);
     p.stages = stages;

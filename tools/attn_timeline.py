@@ -25,7 +25,7 @@ assert rc == 0, rc
 t = buf.reshape(8, 64, 4)
 t0 = t[t > 0].min()
 names = ["S issuer   [start, operands ready, issued]", "dP issuer", "acc1 issuer [start, P/dS ready, issued]", "acc2 issuer",
-         "compute g0 [barrier, S/dP done, acc(i-2) done, arrived]", "compute g1"]
+         "compute g0 [barrier, S/dP done, first slice computed and acc(i-2) done, arrived]", "compute g1"]
 # the LAST launch was mode 1 (rows = queries): roles 3 (acc2) unused there
 for r, nm in enumerate(names):
     print(nm)
