@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
   uint64_t* bar_PV = bars + 13;  // [2]: PV(j) commits to bar_PV[j & 1]
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 15);
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = ptx::warp_idx_uniform(), lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
 
   if (warp == 9 && lane == 0) {
@@ -161,28 +161,37 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
   const uint32_t tO = tmem_base + 256u;  // npv x dpad columns (one accumulator per PV issuer)
 
   if (warp == 9) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      ptx::mbar_expect_tx(barQ, tile_bytes);
-      tma_tile(sQ, &p.mapQ, barQ, p.atoms, kAtom128, q0, h, b);
+    // ===================== TMA producer (whole warp; the TMA instructions under elect) =====================
+    {
+      if (ptx::elect_one()) {
+        ptx::mbar_expect_tx(barQ, tile_bytes);
+        tma_tile(sQ, &p.mapQ, barQ, p.atoms, kAtom128, q0, h, b);
+      }
+      __syncwarp();
       auto load_k = [&](int j) {
         const int s = j % p.kstages, n = j / p.kstages;
         ptx::mbar_wait_sleep(&k_empty[s], (uint32_t)((n & 1) ^ 1));
-        ptx::mbar_expect_tx(&k_full[s], tile_bytes);
-        tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &k_full[s], p.atoms, kAtom128, j * 128, h, b);
+        if (ptx::elect_one()) {
+          ptx::mbar_expect_tx(&k_full[s], tile_bytes);
+          tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &k_full[s], p.atoms, kAtom128, j * 128, h, b);
+        }
+        __syncwarp();
       };
       load_k(0);
       for (int j = 0; j < p.nkb; ++j) {
         if (j + 1 < p.nkb) load_k(j + 1);  // K runs one block ahead of V: S(j+1) is issued before PV(j)
         const int s = j % p.vstages, n = j / p.vstages;
         ptx::mbar_wait_sleep(&v_empty[s], (uint32_t)((n & 1) ^ 1));
-        ptx::mbar_expect_tx(&v_full[s], tile_bytes);
-        tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &v_full[s], p.atoms, kAtom128, j * 128, h, b);
+        if (ptx::elect_one()) {
+          ptx::mbar_expect_tx(&v_full[s], tile_bytes);
+          tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &v_full[s], p.atoms, kAtom128, j * 128, h, b);
+        }
+        __syncwarp();
       }
     }
   } else if (warp == 8) {
-    // ===================== QK^T issuer =====================
-    if (lane == 0) {
+    // ===================== QK^T issuer (whole warp, MMAs under elect: see ptx::elect_one) =====================
+    {
       const uint32_t idescS = ptx::umma_idesc_bf16(128, 0, 0);
       const uint64_t dQ = ptx::umma_desc_sw128(ptx::smem_u32(sQ), 0u, 1024u);
       const uint64_t dK0 = ptx::umma_desc_sw128(ptx::smem_u32(sK), 0u, 1024u);
@@ -196,17 +205,20 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
         if (j >= 2) ptx::mbar_wait_sleep(&bar_P[j & 1], (uint32_t)(((j - 2) >> 1) & 1));
         ptx::mbar_wait_sleep(&k_full[ks], kph);
         ptx::tc_fence_after();
-        mma_ksteps<false>(tS + (uint32_t)(j & 1) * 128u, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS, ksteps,
-                          0u);
-        ptx::umma_commit(&k_empty[ks]);
-        ptx::umma_commit(&bar_S[j & 1]);
+        if (ptx::elect_one()) {
+          mma_ksteps<false>(tS + (uint32_t)(j & 1) * 128u, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS,
+                            ksteps, 0u);
+          ptx::umma_commit(&k_empty[ks]);
+          ptx::umma_commit(&bar_S[j & 1]);
+        }
+        __syncwarp();
         if (++ks == p.kstages) { ks = 0; kph ^= 1u; }
       }
     }
   } else if (warp >= 10) {
     // ===================== PV issuers: issuer hv owns k-steps [hv*8/npv, (hv+1)*8/npv) and accumulator hv ============
     const int hv = warp - 10;
-    if (lane == 0 && hv < p.npv) {
+    if (hv < p.npv) {
       const uint32_t idescO = ptx::umma_idesc_bf16(p.dpad, 0, 1);
       const uint64_t dV0 = ptx::umma_desc_sw128(ptx::smem_u32(sV), kAtom128, 1024u);  // MN-major: LBO = atom stride
       const uint64_t dP0 = ptx::umma_desc_sw128(ptx::smem_u32(sP), 0u, 1024u);
@@ -221,10 +233,13 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
         ptx::mbar_wait_sleep(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
         ptx::mbar_wait_sleep(&v_full[vs], vph);
         ptx::tc_fence_after();
-        mma_ksteps<true>(tOh, dP0 + (uint32_t)(j & 1) * 2u * atom16 + a_off, atom16, dV0 + (uint32_t)vs * tile16 + b_off, 0u,
-                         idescO, nsteps, j > 0 ? 1u : 0u);
-        ptx::umma_commit(&v_empty[vs]);
-        ptx::umma_commit(&bar_PV[j & 1]);
+        if (ptx::elect_one()) {
+          mma_ksteps<true>(tOh, dP0 + (uint32_t)(j & 1) * 2u * atom16 + a_off, atom16, dV0 + (uint32_t)vs * tile16 + b_off,
+                           0u, idescO, nsteps, j > 0 ? 1u : 0u);
+          ptx::umma_commit(&v_empty[vs]);
+          ptx::umma_commit(&bar_PV[j & 1]);
+        }
+        __syncwarp();
         if (++vs == p.vstages) { vs = 0; vph ^= 1u; }
       }
     }
@@ -476,16 +491,22 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
   };
 
   if (warp == 17) {
-    if (lane == 0) {
-      ptx::mbar_expect_tx(barR, 2 * rtile);
-      tma_tile(sR1, &p.mapR1, barR, p.atoms, kAtom128, r0, h, b);
-      tma_tile(sR2, &p.mapR2, barR, p.atoms, kAtom128, r0, h, b);
+    {  // whole warp; the TMA instructions under elect
+      if (ptx::elect_one()) {
+        ptx::mbar_expect_tx(barR, 2 * rtile);
+        tma_tile(sR1, &p.mapR1, barR, p.atoms, kAtom128, r0, h, b);
+        tma_tile(sR2, &p.mapR2, barR, p.atoms, kAtom128, r0, h, b);
+      }
+      __syncwarp();
       for (int i = 0; i < p.ncb; ++i) {
         const int s = i % p.stages, n = i / p.stages;
         ptx::mbar_wait_sleep(&c_empty[s], (uint32_t)((n & 1) ^ 1));
-        ptx::mbar_expect_tx(&c_full[s], 2 * ctile);
-        tma_tile(sC1 + (size_t)s * ctile, &p.mapC1, &c_full[s], p.atoms, catom, i * p.bc, h, b);
-        tma_tile(sC2 + (size_t)s * ctile, &p.mapC2, &c_full[s], p.atoms, catom, i * p.bc, h, b);
+        if (ptx::elect_one()) {
+          ptx::mbar_expect_tx(&c_full[s], 2 * ctile);
+          tma_tile(sC1 + (size_t)s * ctile, &p.mapC1, &c_full[s], p.atoms, catom, i * p.bc, h, b);
+          tma_tile(sC2 + (size_t)s * ctile, &p.mapC2, &c_full[s], p.atoms, catom, i * p.bc, h, b);
+        }
+        __syncwarp();
       }
     }
   } else if (warp == 16 || warp == 18) {

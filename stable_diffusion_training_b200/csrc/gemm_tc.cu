@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   uint64_t* tmem_empty = bars + 2 * kMaxStages + 2;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 2 * kMaxStages + 4);
 
-  const int warp = threadIdx.x >> 5;
+  const int warp = ptx::warp_idx_uniform();  // provably warp-uniform: see ptx::elect_one
   const int lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) {
@@ -149,8 +149,8 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   sdb::pdl_wait();  // everything above overlapped the previous kernel's tail; its results are visible from here on
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
+    // ===================== TMA producer (whole warp, warp-uniform values; the TMA instructions under elect) =========
+    {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
@@ -159,7 +159,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
           ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sb = sa + p.a_stage_bytes;
-          if (SDB_DBG(p, 1)) {  // experiment: no TMA traffic (SDB_GEMM_DBG=1)
+          if (!ptx::elect_one()) {
+            // the other lanes only follow the loop
+          } else if (SDB_DBG(p, 1)) {  // experiment: no TMA traffic (SDB_GEMM_DBG=1)
             ptx::mbar_expect_tx(&full_bar[stage], 0u);
           } else if (MODE == SDB_GEMM_FWD) {
             const int tap = it / p.kblocks;
@@ -190,6 +192,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             for (int j = 0; j < ti.nboxes; ++j)
               ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j, pw0, ph0, pn0);
           }
+          __syncwarp();
           if (++stage == p.stages) {
             stage = 0;
             phase ^= 1u;
@@ -200,7 +203,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   } else if (warp == 1 || warp == 6) {
     // ===================== MMA issuers: warp 1 -> rows 0..127 of the tile, warp 6 -> rows 128..255 (MT == 2) ==========
     const int half = (warp == 6) ? 1 : 0;
-    if (lane == 0 && half < MT) {
+    if (half < MT) {  // whole warp; the MMAs and commits under elect with descriptors in uniform registers
       int stage = 0;
       uint32_t phase = 0;
       int tile_count = 0;
@@ -224,19 +227,22 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
           ptx::tc_fence_after();
           const uint32_t sa = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes) + (uint32_t)half * kAStageBytes;
           const uint32_t sb = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes) + p.a_stage_bytes;
+          if (ptx::elect_one()) {
 #pragma unroll
-          for (int ks = 0; ks < kBlockK / 16; ++ks) {
-            const uint64_t da = ptx::umma_desc_sw128(sa + ks * a_kadv, a_lbo, 1024u);
-            const uint64_t db = ptx::umma_desc_sw128(sb + ks * b_kadv, b_lbo, 1024u);
-            if (live && !SDB_DBG(p, 4)) ptx::umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+            for (int ks = 0; ks < kBlockK / 16; ++ks) {
+              const uint64_t da = ptx::umma_desc_sw128(sa + ks * a_kadv, a_lbo, 1024u);
+              const uint64_t db = ptx::umma_desc_sw128(sb + ks * b_kadv, b_lbo, 1024u);
+              if (live && !SDB_DBG(p, 4)) ptx::umma_bf16(tmem_d, da, db, idesc, (it > 0 || ks > 0) ? 1u : 0u);
+            }
+            ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+            if (it == ti.num_k - 1) ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
           }
-          ptx::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs have read it
+          __syncwarp();
           if (++stage == p.stages) {
             stage = 0;
             phase ^= 1u;
           }
         }
-        ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
       }
     }
   } else {
