@@ -92,6 +92,7 @@ __device__ __forceinline__ void mma_ksteps(uint32_t tmem_d, uint64_t dA, uint32_
 // cost ~0.7 us from a single issuer — more than the softmax of the block. Independent issuers overlap: QK^T gets its
 // own warp and PV is split by key halves (k-steps 0-3 / 4-7) into two accumulators that the epilogue adds.
 constexpr int kFwdThreads = 384;
+constexpr int kFwdMaxStages = 4;  // K and V rings: deep enough to cover the TMA latency under load
 constexpr int kMaxBiasBlocks = 16;  // per-key bias (cross-attention quirk / masks given by the caller): Skv <= 2048
 
 struct FwdParams {
@@ -119,14 +120,14 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
   float* sKb = sL + 256;                                         // [nkb*128] per-key bias (only when kbias2 != null)
   uint64_t* bars = reinterpret_cast<uint64_t*>(sKb + (p.kbias2 ? p.nkb * 128 : 0));
   uint64_t* barQ = bars;
-  uint64_t* k_full = bars + 1;
-  uint64_t* k_empty = bars + 3;
-  uint64_t* v_full = bars + 5;
-  uint64_t* v_empty = bars + 7;
-  uint64_t* bar_S = bars + 9;
-  uint64_t* bar_P = bars + 11;
-  uint64_t* bar_PV = bars + 13;  // [2]: PV(j) commits to bar_PV[j & 1]
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bars + 15);
+  uint64_t* k_full = bars + 1;                     // [kFwdMaxStages]
+  uint64_t* k_empty = k_full + kFwdMaxStages;
+  uint64_t* v_full = k_empty + kFwdMaxStages;
+  uint64_t* v_empty = v_full + kFwdMaxStages;
+  uint64_t* bar_S = v_empty + kFwdMaxStages;       // [2]
+  uint64_t* bar_P = bar_S + 2;                     // [2]
+  uint64_t* bar_PV = bar_P + 2;                    // [2]: PV(j) commits to bar_PV[j & 1]
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_PV + 2);
 
   const int warp = ptx::warp_idx_uniform(), lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
@@ -136,11 +137,13 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
     ptx::tma_prefetch_desc(&p.mapK);
     ptx::tma_prefetch_desc(&p.mapV);
     ptx::mbar_init(barQ, 1);
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < kFwdMaxStages; ++s) {
       ptx::mbar_init(&k_full[s], 1);
       ptx::mbar_init(&k_empty[s], 1);
       ptx::mbar_init(&v_full[s], 1);
       ptx::mbar_init(&v_empty[s], (uint32_t)p.npv);
+    }
+    for (int s = 0; s < 2; ++s) {
       ptx::mbar_init(&bar_S[s], 1);
       ptx::mbar_init(&bar_P[s], 256);
     }
@@ -397,7 +400,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
 // the exp2 / dS arithmetic of block i.
 constexpr int kBwdThreads = 672;
 constexpr int kBwdComputeThreads = 512;
-constexpr int kBwdMaxStages = 4;
+constexpr int kBwdMaxStages = 8;  // TMA latency under load is ~1.5 us and a block takes ~0.5 us: the ring must run well ahead
 
 struct BwdParams {
   CUtensorMap mapR1, mapR2, mapC1, mapC2;
@@ -843,11 +846,12 @@ extern "C" int sdb_attn_fwd(const void* q, long long ldq, const void* k, long lo
                          kMaxBiasBlocks * 128, Skv);
   const size_t tile = (size_t)p.atoms * kAtom128;
   const size_t fixed = tile + 4 * kAtom128 + (512 + 256) * sizeof(float) +
-                       (kbias2 ? (size_t)p.nkb * 128 * sizeof(float) : 0) + 128 /*barriers*/ + 1024 /*align*/;
+                       (kbias2 ? (size_t)p.nkb * 128 * sizeof(float) : 0) + 256 /*barriers*/ + 1024 /*align*/;
   const size_t budget = 227 * 1024;
-  p.kstages = p.vstages = (p.nkb > 1) ? 2 : 1;
-  if (fixed + (size_t)(p.kstages + p.vstages) * tile > budget) p.vstages = 1;
-  if (fixed + (size_t)(p.kstages + p.vstages) * tile > budget) p.kstages = 1;
+  p.kstages = p.vstages = (p.nkb < kFwdMaxStages) ? p.nkb : kFwdMaxStages;
+  while (fixed + (size_t)(p.kstages + p.vstages) * tile > budget && p.kstages + p.vstages > 2) {
+    if (p.vstages >= p.kstages) --p.vstages; else --p.kstages;
+  }
   const size_t smem_bytes = fixed + (size_t)(p.kstages + p.vstages) * tile;
   if (smem_bytes > budget) return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_fwd: head dim %d needs too much smem", d);
   static std::once_flag once;

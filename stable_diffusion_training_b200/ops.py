@@ -52,19 +52,23 @@ def _pixel_box(W: int, H: int, N: int, pixels: int):
 _TILE_CACHE: dict = {}
 
 
+_DELIVERY_CLKS = float(os.environ.get("SDB_DELIVERY_CLKS", "1200"))
+
+
 def _kblock_clks(mt: int, bn: int, b_mn: bool) -> float:
     """Cycles one 64-deep K block of a (128*mt x bn) tile occupies an SM — measured model (tools/mma_rate.cu and the
     SDB_GEMM_DBG experiments): the main loop runs at the slower of
-      * operand delivery: the smem ring holds `stages` K blocks and a refill takes ~3000 clk under load (the L2
+      * operand delivery: the smem ring holds `stages` K blocks and a refill takes ~1200 clk under load (in-step scan of SDB_DELIVERY_CLKS, profiles/r2b; the L2
         request queues are full: ~13 TB/s chip-wide), so one K block per 3000 / stages clk whatever its size —
         which is why fewer, larger tiles (less re-fetching of A and B) win until the ring gets too shallow;
-      * tcgen05.mma with both operands in shared memory: max(95, bn/2 + 40.5) clk per K=16 step from one issuing
-        thread; two issuing threads (mt == 2, one per 128-row half) overlap operand fetches: ~40 + 0.355*bn each."""
+      * tcgen05.mma with both operands in shared memory: bn/2 + 43 clk per K=16 step from one issuing warp (issued
+        back to back from uniform registers); two issuing warps (mt == 2, one per 128-row half) overlap their operand
+        fetches: 38.5 + 0.375*bn each."""
     bcols = -(-bn // 64) * 64 if b_mn else bn
     stage_bytes = (128 * mt + bcols) * 128
     stages = max(1, min(8, (225 * 1024) // stage_bytes))
-    delivery = 3000.0 / stages
-    mma = 4 * max(95.0, bn / 2 + 40.5) if mt == 1 else 8 * max(62.0, 40.0 + 0.355 * bn)
+    delivery = _DELIVERY_CLKS / stages
+    mma = 4 * (bn / 2 + 43.0) if mt == 1 else 8 * (38.5 + 0.375 * bn)
     return max(delivery, mma)
 
 
