@@ -388,6 +388,284 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
   }
 }
 
+// =============================================== forward, two query tiles per CTA ===============================================
+// For head dims <= 64 (the 64x64-latent layers of SD: d = 40 / 64). The one-tile kernel above keeps its 8 softmax warps in
+// lockstep (a 256-thread barrier per key block for the row-max exchange), so with two warps per scheduler neither the MUFU
+// pipe (40 %) nor the issue slots (39 %) are busy (profiles/r1n_ncu_full.md). Here a CTA owns 256 query rows as two
+// independent 128-row tiles, each with its own 8 softmax warps, S / P / O columns in tensor memory and issuing warp; the
+// two groups drift out of phase, so one group's exp2 pass overlaps the other's max pass, waits and MMAs, and every K / V
+// tile is fetched once per 256 rows. P goes to the PV product through tensor memory (A operand from TMEM): no shared-
+// memory staging, no proxy fence.
+//   warps 0-7 softmax group 0, 8-15 group 1 (thread = (row, key half)), 16 TMA, 17 / 18 issuers (17 owns TMEM)
+//   TMEM: [S0 128 | S1 128 | O0 dpad | O1 dpad | P0 64 | P1 64]  (P bf16: two keys per column)
+constexpr int kFwd2Threads = 608;
+
+__global__ void __launch_bounds__(kFwd2Threads, 1) attn_fwd2_kernel(const __grid_constant__ FwdParams p) {
+  sdb::pdl_trigger();
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = ptx::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+  const uint32_t tile_bytes = (uint32_t)p.atoms * kAtom128;
+  uint8_t* sQ = smem;                                            // [2 tiles]
+  uint8_t* sK = sQ + 2 * tile_bytes;
+  uint8_t* sV = sK + (size_t)p.kstages * tile_bytes;
+  float* sX = reinterpret_cast<float*>(sV + (size_t)p.vstages * tile_bytes);  // [2 grp][2 buf][2 half][128] row max
+  float* sL = sX + 1024;                                         // [2 grp][2 half][128] row-sum exchange
+  float* sKb = sL + 512;                                         // [nkb*128] per-key bias (only when kbias2 != null)
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sKb + (p.kbias2 ? p.nkb * 128 : 0));
+  uint64_t* barQ = bars;
+  uint64_t* k_full = bars + 1;                     // [kFwdMaxStages]
+  uint64_t* k_empty = k_full + kFwdMaxStages;      // count 2: both issuers
+  uint64_t* v_full = k_empty + kFwdMaxStages;
+  uint64_t* v_empty = v_full + kFwdMaxStages;
+  uint64_t* bar_S = v_empty + kFwdMaxStages;       // [2 grp] QK^T(j) complete
+  uint64_t* bar_Sfree = bar_S + 2;                 // [2 grp] the group holds S(j) in registers
+  uint64_t* bar_P = bar_Sfree + 2;                 // [2 grp] P(j) written to tensor memory
+  uint64_t* bar_PV = bar_P + 2;                    // [2 grp] PV(j) complete
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(bar_PV + 2);
+
+  const int warp = ptx::warp_idx_uniform(), lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * 256, h = blockIdx.y, b = blockIdx.z;
+
+  if (warp == 16 && lane == 0) {
+    ptx::tma_prefetch_desc(&p.mapQ);
+    ptx::tma_prefetch_desc(&p.mapK);
+    ptx::tma_prefetch_desc(&p.mapV);
+    ptx::mbar_init(barQ, 1);
+    for (int s = 0; s < kFwdMaxStages; ++s) {
+      ptx::mbar_init(&k_full[s], 1);
+      ptx::mbar_init(&k_empty[s], 2);
+      ptx::mbar_init(&v_full[s], 1);
+      ptx::mbar_init(&v_empty[s], 2);
+    }
+    for (int g = 0; g < 2; ++g) {
+      ptx::mbar_init(&bar_S[g], 1);
+      ptx::mbar_init(&bar_Sfree[g], 256);
+      ptx::mbar_init(&bar_P[g], 256);
+      ptx::mbar_init(&bar_PV[g], 1);
+    }
+    ptx::fence_barrier_init();
+  }
+  if (warp == 17) {
+    ptx::tmem_alloc(tmem_ptr_smem, 512);
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+  sdb::pdl_wait();
+  const uint32_t tO0 = tmem_base + 256u;
+  const uint32_t tP0 = tO0 + 2u * (uint32_t)p.dpad;
+
+  if (warp == 16) {
+    // ===================== TMA producer (whole warp; the TMA instructions under elect) =====================
+    if (ptx::elect_one()) {
+      ptx::mbar_expect_tx(barQ, 2 * tile_bytes);
+      tma_tile(sQ, &p.mapQ, barQ, p.atoms, kAtom128, q0, h, b);
+      tma_tile(sQ + tile_bytes, &p.mapQ, barQ, p.atoms, kAtom128, q0 + 128, h, b);
+    }
+    __syncwarp();
+    auto load_k = [&](int j) {
+      const int s = j % p.kstages, n = j / p.kstages;
+      ptx::mbar_wait_sleep(&k_empty[s], (uint32_t)((n & 1) ^ 1));
+      if (ptx::elect_one()) {
+        ptx::mbar_expect_tx(&k_full[s], tile_bytes);
+        tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &k_full[s], p.atoms, kAtom128, j * 128, h, b);
+      }
+      __syncwarp();
+    };
+    load_k(0);
+    for (int j = 0; j < p.nkb; ++j) {
+      if (j + 1 < p.nkb) load_k(j + 1);
+      const int s = j % p.vstages, n = j / p.vstages;
+      ptx::mbar_wait_sleep(&v_empty[s], (uint32_t)((n & 1) ^ 1));
+      if (ptx::elect_one()) {
+        ptx::mbar_expect_tx(&v_full[s], tile_bytes);
+        tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &v_full[s], p.atoms, kAtom128, j * 128, h, b);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 17 || warp == 18) {
+    // ===================== issuer of group g: QK^T(0), then QK^T(j) followed by PV(j-1), finally PV(last) ==========
+    const int g = warp - 17;
+    const uint32_t idescS = ptx::umma_idesc_bf16(128, 0, 0);
+    const uint32_t idescO = ptx::umma_idesc_bf16(p.dpad, 0, 1);
+    const uint64_t dQ = ptx::umma_desc_sw128(ptx::smem_u32(sQ + (size_t)g * tile_bytes), 0u, 1024u);
+    const uint64_t dK0 = ptx::umma_desc_sw128(ptx::smem_u32(sK), 0u, 1024u);
+    const uint64_t dV0 = ptx::umma_desc_sw128(ptx::smem_u32(sV), kAtom128, 1024u);  // MN-major: LBO = atom stride
+    const uint32_t tile16 = tile_bytes >> 4, atom16 = kAtom128 >> 4;
+    const uint32_t tSg = tmem_base + (uint32_t)g * 128u;
+    const uint32_t tOg = tO0 + (uint32_t)(g * p.dpad);
+    const uint32_t tPg = tP0 + (uint32_t)g * 64u;
+    const int ksteps = p.dpad / 16;
+    int ks = 0, vs = 0;
+    uint32_t kph = 0, vph = 0;
+    ptx::mbar_wait(barQ, 0);
+    for (int j = 0; j <= p.nkb; ++j) {
+      if (j < p.nkb) {
+        if (j >= 1) ptx::mbar_wait_sleep(&bar_Sfree[g], (uint32_t)((j - 1) & 1));
+        ptx::mbar_wait_sleep(&k_full[ks], kph);
+        ptx::tc_fence_after();
+        if (ptx::elect_one()) {
+          mma_ksteps<false>(tSg, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS, ksteps, 0u);
+          ptx::umma_commit(&k_empty[ks]);
+          ptx::umma_commit(&bar_S[g]);
+        }
+        __syncwarp();
+        if (++ks == p.kstages) { ks = 0; kph ^= 1u; }
+      }
+      if (j >= 1) {
+        ptx::mbar_wait_sleep(&bar_P[g], (uint32_t)((j - 1) & 1));
+        ptx::mbar_wait_sleep(&v_full[vs], vph);
+        ptx::tc_fence_after();
+        const uint64_t dV = dV0 + (uint32_t)vs * tile16;
+        if (ptx::elect_one()) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            ptx::umma_bf16_ts(tOg, tPg + 8u * (uint32_t)k, dV + 128u * (uint32_t)k, idescO, (k > 0 || j > 1) ? 1u : 0u);
+          ptx::umma_commit(&v_empty[vs]);
+          ptx::umma_commit(&bar_PV[g]);
+        }
+        __syncwarp();
+        if (++vs == p.vstages) { vs = 0; vph ^= 1u; }
+      }
+    }
+  } else {
+    // ===================== softmax / epilogue of group g: thread = (query row, key half) =====================
+    const int g = warp >> 3, wg = warp & 7;
+    const int q4 = wg & 3, half = wg >> 2;
+    const int row = q4 * 32 + lane;
+    const int gtid = (int)threadIdx.x & 255;
+    const uint32_t lane_base = ((uint32_t)(q4 * 32)) << 16;
+    const uint32_t tSg = tmem_base + (uint32_t)g * 128u + lane_base + (uint32_t)half * 64u;
+    const uint32_t tOg = tO0 + (uint32_t)(g * p.dpad) + lane_base;
+    const uint32_t tPg = tP0 + (uint32_t)g * 64u + lane_base + (uint32_t)half * 32u;
+    float* sXg = sX + g * 512;
+    if (p.kbias2 != nullptr) {
+      for (int i = gtid; i < p.nkb * 128; i += 256) if (g == 0) sKb[i] = (i < p.Skv) ? p.kbias2[i] : -INFINITY;
+      ptx::named_bar_sync(3, 512);
+    }
+    float m_used = -INFINITY, l = 0.f;
+    for (int j = 0; j < p.nkb; ++j) {
+      ptx::mbar_wait_sleep(&bar_S[g], (uint32_t)(j & 1), 20);
+      ptx::tc_fence_after();
+      const int key0 = j * 128 + half * 64;
+      const int emode = (p.kbias2 != nullptr) ? 2 : ((j * 128 + 128 > p.Skv) ? 1 : 0);
+      const float* kb = sKb + key0;
+      uint32_t sv[64];
+      ptx::tmem_ld_32x32(tSg, *reinterpret_cast<uint32_t(*)[32]>(&sv[0]));
+      ptx::tmem_ld_32x32(tSg + 32, *reinterpret_cast<uint32_t(*)[32]>(&sv[32]));
+      ptx::tmem_ld_wait();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&bar_Sfree[g]);  // the scores are in registers: QK^T(j+1) may overwrite S
+      float mx;
+      {
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+        if (emode == 0) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], u2f(sv[i]));
+          mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale2;
+        } else if (emode == 1) {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], (key0 + i < p.Skv) ? u2f(sv[i]) : -INFINITY);
+          mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3])) * p.scale2;
+        } else {
+#pragma unroll
+          for (int i = 0; i < 64; ++i) m4[i & 3] = fmaxf(m4[i & 3], fmaf(u2f(sv[i]), p.scale2, kb[i]));
+          mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+        }
+      }
+      float* xbuf = sXg + (j & 1) * 256;
+      xbuf[half * 128 + row] = mx;
+      ptx::named_bar_sync(1 + g, 256);
+      mx = fmaxf(mx, xbuf[(half ^ 1) * 128 + row]);
+      if (j == 0) {
+        m_used = mx;
+      } else {
+        // PV(j-1) has read P(j-1) and updated O: needed before P is overwritten below and before O is rescaled
+        ptx::mbar_wait_sleep(&bar_PV[g], (uint32_t)((j - 1) & 1), 20);
+        ptx::tc_fence_after();
+        const bool need = mx > m_used + 8.0f;
+        if (__any_sync(0xffffffffu, need)) {
+          const float alpha = need ? ptx::ex2_approx(m_used - mx) : 1.0f;
+          if (need) m_used = mx;
+          l *= alpha;
+          for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {  // the two warps of a row interleave 16-column chunks
+            uint32_t v[16];
+            ptx::tmem_ld_32x16(tOg + c0, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = __float_as_uint(u2f(v[i]) * alpha);
+            ptx::tmem_st_32x16(tOg + c0, v);
+          }
+        }
+      }
+      // P = exp2(s - m) as bf16 pairs into the group's P columns (16 keys = 8 columns per store)
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t o[8];
+#pragma unroll
+        for (int e2 = 0; e2 < 8; ++e2) {
+          float pv[2];
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int i = c * 16 + e2 * 2 + e;
+            if (emode == 0) pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used));
+            else if (emode == 1) pv[e] = (key0 + i < p.Skv) ? ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used)) : 0.f;
+            else pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, kb[i] - m_used));
+            l4[(e2 * 2 + e) & 3] += pv[e];
+          }
+          o[e2] = sdb::pack_bf16x2(pv[0], pv[1]);
+        }
+        ptx::tmem_st_32x8(tPg + 8u * (uint32_t)c, o);
+      }
+      l += (l4[0] + l4[1]) + (l4[2] + l4[3]);
+      ptx::tmem_st_wait();
+      ptx::tc_fence_before();
+      ptx::mbar_arrive(&bar_P[g]);
+    }
+    // ---- epilogue: O / l -> global, lse ----
+    float* sLg = sL + g * 256;
+    sLg[half * 128 + row] = l;
+    ptx::named_bar_sync(1 + g, 256);
+    l += sLg[(half ^ 1) * 128 + row];
+    ptx::mbar_wait(&bar_PV[g], (uint32_t)((p.nkb - 1) & 1));
+    ptx::tc_fence_after();
+    const int q = q0 + g * 128 + row;
+    const bool valid = q < p.Sq;
+    const float inv_l = 1.0f / l;
+    __nv_bfloat16* orow = p.o + ((long long)b * p.Sq + q) * p.ldo + (long long)h * p.d;
+    for (int c0 = half * 16; c0 < p.dpad; c0 += 32) {
+      uint32_t v[16];
+      ptx::tmem_ld_32x16(tOg + c0, v);
+      ptx::tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          if (c0 + c * 8 < p.d) {
+            uint4 o;
+            o.x = sdb::pack_bf16x2(u2f(v[c * 8 + 0]) * inv_l, u2f(v[c * 8 + 1]) * inv_l);
+            o.y = sdb::pack_bf16x2(u2f(v[c * 8 + 2]) * inv_l, u2f(v[c * 8 + 3]) * inv_l);
+            o.z = sdb::pack_bf16x2(u2f(v[c * 8 + 4]) * inv_l, u2f(v[c * 8 + 5]) * inv_l);
+            o.w = sdb::pack_bf16x2(u2f(v[c * 8 + 6]) * inv_l, u2f(v[c * 8 + 7]) * inv_l);
+            sdb::st_u4(orow + c0 + c * 8, o);
+          }
+        }
+      }
+    }
+    if (valid && half == 0) p.lse2[((long long)b * p.H + h) * p.Sq + q] = m_used + log2f(l);
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 17) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, 512);
+  }
+}
+
 // =============================================== backward ===============================================
 // 672 threads: warps 0-15 = compute (warps w, w+4, w+8, w+12 own the same 32 rows and split the 64 columns of a block in
 // quarters; no row reductions are needed in backward because lse and D are inputs), warp 17 = TMA producer, and FOUR
@@ -845,6 +1123,28 @@ extern "C" int sdb_attn_fwd(const void* q, long long ldq, const void* k, long lo
     return sdb_set_error(SDB_ERR_UNSUPPORTED, "sdb_attn_fwd: a per-key bias supports Skv <= %d (got %d)",
                          kMaxBiasBlocks * 128, Skv);
   const size_t tile = (size_t)p.atoms * kAtom128;
+  static const int fwd_env = [] { const char* e = getenv("SDB_ATTN_FWD"); return e ? atoi(e) : 0; }();
+  // two query tiles per CTA when S, O and a bf16 copy of P for both fit the 512 tensor-memory columns (head dim <= 64)
+  if (p.dpad <= 64 && Sq > 128 && fwd_env != 1) {
+    const size_t fixed2 = 2 * tile + (1024 + 512) * sizeof(float) +
+                          (kbias2 ? (size_t)p.nkb * 128 * sizeof(float) : 0) + 256 /*barriers*/ + 1024 /*align*/;
+    p.kstages = p.vstages = (p.nkb < kFwdMaxStages) ? p.nkb : kFwdMaxStages;
+    const size_t smem2 = fixed2 + (size_t)(p.kstages + p.vstages) * tile;
+    static std::once_flag once2;
+    static cudaError_t attr_err2 = cudaSuccess;
+    std::call_once(once2, [] {
+      attr_err2 = cudaFuncSetAttribute(attn_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    });
+    if (attr_err2 != cudaSuccess)
+      return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_fwd: cudaFuncSetAttribute: %s", cudaGetErrorString(attr_err2));
+    dim3 grid2((Sq + 255) / 256, H, B);
+    if (sdb::launch_pdl(attn_fwd2_kernel, grid2, dim3(kFwd2Threads), smem2, stream, p) != cudaSuccess) {
+      const cudaError_t e = cudaGetLastError();
+      return sdb_set_error(SDB_ERR_CUDA, "sdb_attn_fwd: launch failed: %s", cudaGetErrorString(e));
+    }
+    SDB_CUDA_LAUNCH_CHECK("sdb_attn_fwd");
+    return SDB_OK;
+  }
   const size_t fixed = tile + 4 * kAtom128 + (512 + 256) * sizeof(float) +
                        (kbias2 ? (size_t)p.nkb * 128 * sizeof(float) : 0) + 256 /*barriers*/ + 1024 /*align*/;
   const size_t budget = 227 * 1024;
