@@ -275,33 +275,51 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         for (int c0 = 0; c0 < ti.nw; c0 += 32) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
+          // every addend of the chunk is requested BEFORE waiting for the accumulator: the loads may not be hoisted over
+          // the previous chunk's stores (possible aliasing), so issued where they are used each 8-column group exposed
+          // a full load latency (40 per tile half: ~20 us of a 78 us convolution, SDB_GEMM_DBG experiments r2g)
+          float4 bv[8];
+          uint4 tv[4], rv[4];
+          if (valid) {
+#pragma unroll
+            for (int g8 = 0; g8 < 4; ++g8) {
+              if (c0 + g8 * 8 < ti.nw) {
+                if (bias) {
+                  bv[2 * g8] = __ldg(reinterpret_cast<const float4*>(bias + c0 + g8 * 8));
+                  bv[2 * g8 + 1] = __ldg(reinterpret_cast<const float4*>(bias + c0 + g8 * 8 + 4));
+                }
+                if (temb) tv[g8] = sdb::ld_u4(temb + c0 + g8 * 8);
+                if (res) rv[g8] = sdb::ld_u4(res + c0 + g8 * 8);
+              }
+            }
+          }
           ptx::tmem_ld_wait();
           if (valid) {
 #pragma unroll
-            for (int j8 = 0; j8 < 32; j8 += 8) {
+            for (int g8 = 0; g8 < 4; ++g8) {
+              const int j8 = g8 * 8;
               if (c0 + j8 < ti.nw) {
                 float f[8];
 #pragma unroll
                 for (int j = 0; j < 8; ++j) f[j] = __uint_as_float(v[j8 + j]);
                 if (bias) {
-                  const float4 b0 = __ldg(reinterpret_cast<const float4*>(bias + c0 + j8));
-                  const float4 b1 = __ldg(reinterpret_cast<const float4*>(bias + c0 + j8 + 4));
+                  const float4 b0 = bv[2 * g8], b1 = bv[2 * g8 + 1];
                   f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w;
                   f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
                 }
                 if (temb) {
-                  const uint4 tv = sdb::ld_u4(temb + c0 + j8);
-                  f[0] += sdb::bf16_lo(tv.x); f[1] += sdb::bf16_hi(tv.x);
-                  f[2] += sdb::bf16_lo(tv.y); f[3] += sdb::bf16_hi(tv.y);
-                  f[4] += sdb::bf16_lo(tv.z); f[5] += sdb::bf16_hi(tv.z);
-                  f[6] += sdb::bf16_lo(tv.w); f[7] += sdb::bf16_hi(tv.w);
+                  const uint4 t4 = tv[g8];
+                  f[0] += sdb::bf16_lo(t4.x); f[1] += sdb::bf16_hi(t4.x);
+                  f[2] += sdb::bf16_lo(t4.y); f[3] += sdb::bf16_hi(t4.y);
+                  f[4] += sdb::bf16_lo(t4.z); f[5] += sdb::bf16_hi(t4.z);
+                  f[6] += sdb::bf16_lo(t4.w); f[7] += sdb::bf16_hi(t4.w);
                 }
                 if (res) {
-                  const uint4 rv = sdb::ld_u4(res + c0 + j8);
-                  f[0] += sdb::bf16_lo(rv.x); f[1] += sdb::bf16_hi(rv.x);
-                  f[2] += sdb::bf16_lo(rv.y); f[3] += sdb::bf16_hi(rv.y);
-                  f[4] += sdb::bf16_lo(rv.z); f[5] += sdb::bf16_hi(rv.z);
-                  f[6] += sdb::bf16_lo(rv.w); f[7] += sdb::bf16_hi(rv.w);
+                  const uint4 r4 = rv[g8];
+                  f[0] += sdb::bf16_lo(r4.x); f[1] += sdb::bf16_hi(r4.x);
+                  f[2] += sdb::bf16_lo(r4.y); f[3] += sdb::bf16_hi(r4.y);
+                  f[4] += sdb::bf16_lo(r4.z); f[5] += sdb::bf16_hi(r4.z);
+                  f[6] += sdb::bf16_lo(r4.w); f[7] += sdb::bf16_hi(r4.w);
                 }
                 uint4 o;
                 o.x = sdb::pack_bf16x2(f[0], f[1]);
