@@ -50,6 +50,7 @@ struct alignas(64) TcParams {
   int tiles_m, tiles_n, total_tiles, kblocks;
   int splits, pb_per_split, total_pb;
   int stages, dbg, mt;
+  int st32;  // every output row segment the epilogue writes is 32-byte aligned: 32-byte stores
   uint32_t a_stage_bytes;
   uint32_t b_stage_bytes, stage_bytes;
   void* d;
@@ -295,6 +296,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
           }
           ptx::tmem_ld_wait();
           if (valid) {
+            uint4 prev;
 #pragma unroll
             for (int g8 = 0; g8 < 4; ++g8) {
               const int j8 = g8 * 8;
@@ -326,7 +328,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                 o.y = sdb::pack_bf16x2(f[2], f[3]);
                 o.z = sdb::pack_bf16x2(f[4], f[5]);
                 o.w = sdb::pack_bf16x2(f[6], f[7]);
-                sdb::st_u4(out + c0 + j8, o);
+                // pairs of 8-column groups go out as one 32-byte store (a last unpaired group on its own)
+                if (!p.st32 || ((g8 & 1) == 0 && c0 + j8 + 8 >= ti.nw)) sdb::st_u4(out + c0 + j8, o);
+                else if (g8 & 1) sdb::st_u8(out + c0 + j8 - 8, prev, o);
+                else prev = o;
               }
             }
           }
@@ -349,9 +354,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
                                "f"(__uint_as_float(v[j4])), "f"(__uint_as_float(v[j4 + 1])),
                                "f"(__uint_as_float(v[j4 + 2])), "f"(__uint_as_float(v[j4 + 3]))
                                : "memory");
-                } else {
+                } else if (!p.st32 || ((j4 & 4) == 0 && c0 + j4 + 4 >= ti.nw)) {
                   sdb::st_f4(dst, make_float4(__uint_as_float(v[j4]), __uint_as_float(v[j4 + 1]),
                                               __uint_as_float(v[j4 + 2]), __uint_as_float(v[j4 + 3])));
+                } else if (j4 & 4) {
+                  sdb::st_u8(dst - 4, make_uint4(v[j4 - 4], v[j4 - 3], v[j4 - 2], v[j4 - 1]),
+                             make_uint4(v[j4], v[j4 + 1], v[j4 + 2], v[j4 + 3]));
                 }
               }
             }
@@ -459,6 +467,12 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     p.dsW = d->d_strideW; p.dsH = d->d_strideH; p.dsN = d->d_strideN;
   } else {
     p.dsW = d->ldd; p.dsH = d->ldd * d->outW; p.dsN = d->ldd * d->outW * d->outH;
+  }
+  {  // tile column offsets and chunk starts are multiples of 16 elements; the base and the strides must be too
+    const int esz = (d->mode == SDB_GEMM_FWD) ? 2 : 4;
+    const long long unit = 32 / esz;
+    p.st32 = ((reinterpret_cast<uintptr_t>(d->d) & 31) == 0) && (p.dsW % unit == 0) && (p.dsH % unit == 0) &&
+             (p.dsN % unit == 0) && (p.ldd % unit == 0) && (p.BN % 16 == 0);
   }
   p.bias = d->bias;
   p.temb = reinterpret_cast<const __nv_bfloat16*>(d->temb); p.ldt = d->ldt;
