@@ -87,10 +87,10 @@ __device__ __forceinline__ void mma_ksteps(uint32_t tmem_d, uint64_t dA, uint32_
 // issuers. S is double-buffered in TMEM and P in shared memory, so QK^T of block j+1 and PV of block j-1 run on the
 // tensor pipe while the softmax warps (the MUFU-bound resource: 128x128 exp2 per block) work on block j.
 //
-// Why several issuing warps (tools/mma_rate.cu, measured on B200): ONE thread cannot issue tcgen05.mma faster than one
-// per ~63 ns whatever the shape, so the 3 + 8 narrow MMAs of a key block (N = 128 for QK^T, N = dpad <= 64 for PV)
-// cost ~0.7 us from a single issuer — more than the softmax of the block. Independent issuers overlap: QK^T gets its
-// own warp and PV is split by key halves (k-steps 0-3 / 4-7) into two accumulators that the epilogue adds.
+// Several issuing warps: each waits on its own barriers (S needs the K tile and a free S buffer, PV needs P and the V
+// tile), so QK^T gets its own warp and PV is split by key halves (k-steps 0-3 / 4-7) into two accumulators that the
+// epilogue adds. The issue loops run on the whole warp with the MMAs under elect.sync (ptx::elect_one): written
+// under `if (lane == 0)` every MMA cost ~120 clk of ELECT / R2UR serialisation (tools/mma_rate.cu).
 constexpr int kFwdThreads = 384;
 constexpr int kFwdMaxStages = 4;  // K and V rings: deep enough to cover the TMA latency under load
 constexpr int kMaxBiasBlocks = 16;  // per-key bias (cross-attention quirk / masks given by the caller): Skv <= 2048
@@ -667,15 +667,15 @@ __global__ void __launch_bounds__(kFwd2Threads, 1) attn_fwd2_kernel(const __grid
 }
 
 // =============================================== backward ===============================================
-// 672 threads: warps 0-15 = compute (warps w, w+4, w+8, w+12 own the same 32 rows and split the 64 columns of a block in
-// quarters; no row reductions are needed in backward because lse and D are inputs), warp 17 = TMA producer, and FOUR
-// tcgen05.mma issuers — warp 16 scores (+ TMEM owner), warp 18 dP, warp 19 first accumulator (dK / dQ), warp 20 second
-// accumulator (dV, mode 0) — because one thread issues at most one MMA per ~63 ns (see the forward kernel's note) and
-// a block needs 14 of them. Sixteen compute warps (four per scheduler) rather than eight: the kernel is bound by the
-// compute warps' exp2 / conversion / staging instruction stream, whose TMEM-load and MUFU latencies two warps per
-// scheduler could not hide (46 % issue utilisation, profiles/r1n_ncu_full.md). With nbuf = 2 (head dim <= 128) S / dP are double-buffered in TMEM and P^T / dS^T in shared
-// memory, so the tensor pipe computes block i+1's scores and block i-1's accumulations while the compute warps run
-// the exp2 / dS arithmetic of block i.
+// 672 threads: warps 0-15 = compute (two out-of-phase groups of 8 warps: group g owns the column blocks i = g, g+2, ..
+// and S / dP buffer g; thread = (row, column half) inside a group; no row reductions are needed in backward because
+// lse and D are inputs), warp 17 = TMA producer, and FOUR issuing warps — 16 scores (+ TMEM owner), 18 dP, 19 first
+// accumulator (dK / dQ), 20 second accumulator (dV, mode 0) — each waiting on its own barriers; the issue loops run on
+// the whole warp with the MMAs under elect.sync (ptx::elect_one). Sixteen compute warps (four per scheduler) rather
+// than eight: the kernel is bound by the compute warps' exp2 / conversion instruction stream, whose TMEM-load and MUFU
+// latencies two warps per scheduler could not hide (46 % issue utilisation, profiles/r1n_ncu_full.md). With nbuf = 2
+// (head dim <= 128) S / dP are double-buffered in TMEM; the bf16 P^T / dS^T operands of the accumulating MMAs are
+// written back to tensor memory (A operand from TMEM), so shared memory carries only the TMA tiles.
 constexpr int kBwdThreads = 672;
 constexpr int kBwdComputeThreads = 512;
 constexpr int kBwdMaxStages = 8;  // TMA latency under load is ~1.5 us and a block takes ~0.5 us: the ring must run well ahead
