@@ -41,6 +41,13 @@ extern "C" int sdb_attn_timeline(long long* host_out) {
 #define SDB_TL(role, i, slot) do {} while (0)
 #endif
 
+// waits of the producer / issuer warps: -DSDB_ISSUER_SPIN makes them pure try_wait loops (no nanosleep back-off)
+#ifdef SDB_ISSUER_SPIN
+#define SDB_ISSUER_WAIT(bar, ph) ptx::mbar_wait(bar, ph)
+#else
+#define SDB_ISSUER_WAIT(bar, ph) ptx::mbar_wait_sleep(bar, ph)
+#endif
+
 namespace {
 
 constexpr uint32_t kAtom128 = 128 * 128;  // bytes of a [128 rows x 64 bf16] swizzle atom column
@@ -173,7 +180,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       __syncwarp();
       auto load_k = [&](int j) {
         const int s = j % p.kstages, n = j / p.kstages;
-        ptx::mbar_wait_sleep(&k_empty[s], (uint32_t)((n & 1) ^ 1));
+        SDB_ISSUER_WAIT(&k_empty[s], (uint32_t)((n & 1) ^ 1));
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(&k_full[s], tile_bytes);
           tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &k_full[s], p.atoms, kAtom128, j * 128, h, b);
@@ -184,7 +191,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       for (int j = 0; j < p.nkb; ++j) {
         if (j + 1 < p.nkb) load_k(j + 1);  // K runs one block ahead of V: S(j+1) is issued before PV(j)
         const int s = j % p.vstages, n = j / p.vstages;
-        ptx::mbar_wait_sleep(&v_empty[s], (uint32_t)((n & 1) ^ 1));
+        SDB_ISSUER_WAIT(&v_empty[s], (uint32_t)((n & 1) ^ 1));
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(&v_full[s], tile_bytes);
           tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &v_full[s], p.atoms, kAtom128, j * 128, h, b);
@@ -205,8 +212,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       ptx::mbar_wait(barQ, 0);
       for (int j = 0; j < p.nkb; ++j) {
         // S buffer j&1 was last read by softmax(j-2): its arrival on bar_P comes after its TMEM loads
-        if (j >= 2) ptx::mbar_wait_sleep(&bar_P[j & 1], (uint32_t)(((j - 2) >> 1) & 1));
-        ptx::mbar_wait_sleep(&k_full[ks], kph);
+        if (j >= 2) SDB_ISSUER_WAIT(&bar_P[j & 1], (uint32_t)(((j - 2) >> 1) & 1));
+        SDB_ISSUER_WAIT(&k_full[ks], kph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           mma_ksteps<false>(tS + (uint32_t)(j & 1) * 128u, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS,
@@ -233,8 +240,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
       int vs = 0;
       uint32_t vph = 0;
       for (int j = 0; j < p.nkb; ++j) {
-        ptx::mbar_wait_sleep(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
-        ptx::mbar_wait_sleep(&v_full[vs], vph);
+        SDB_ISSUER_WAIT(&bar_P[j & 1], (uint32_t)((j >> 1) & 1));
+        SDB_ISSUER_WAIT(&v_full[vs], vph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           mma_ksteps<true>(tOh, dP0 + (uint32_t)(j & 1) * 2u * atom16 + a_off, atom16, dV0 + (uint32_t)vs * tile16 + b_off,
@@ -468,7 +475,7 @@ __global__ void __launch_bounds__(kFwd2Threads, 1) attn_fwd2_kernel(const __grid
     __syncwarp();
     auto load_k = [&](int j) {
       const int s = j % p.kstages, n = j / p.kstages;
-      ptx::mbar_wait_sleep(&k_empty[s], (uint32_t)((n & 1) ^ 1));
+      SDB_ISSUER_WAIT(&k_empty[s], (uint32_t)((n & 1) ^ 1));
       if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&k_full[s], tile_bytes);
         tma_tile(sK + (size_t)s * tile_bytes, &p.mapK, &k_full[s], p.atoms, kAtom128, j * 128, h, b);
@@ -479,7 +486,7 @@ __global__ void __launch_bounds__(kFwd2Threads, 1) attn_fwd2_kernel(const __grid
     for (int j = 0; j < p.nkb; ++j) {
       if (j + 1 < p.nkb) load_k(j + 1);
       const int s = j % p.vstages, n = j / p.vstages;
-      ptx::mbar_wait_sleep(&v_empty[s], (uint32_t)((n & 1) ^ 1));
+      SDB_ISSUER_WAIT(&v_empty[s], (uint32_t)((n & 1) ^ 1));
       if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&v_full[s], tile_bytes);
         tma_tile(sV + (size_t)s * tile_bytes, &p.mapV, &v_full[s], p.atoms, kAtom128, j * 128, h, b);
@@ -504,8 +511,8 @@ __global__ void __launch_bounds__(kFwd2Threads, 1) attn_fwd2_kernel(const __grid
     ptx::mbar_wait(barQ, 0);
     for (int j = 0; j <= p.nkb; ++j) {
       if (j < p.nkb) {
-        if (j >= 1) ptx::mbar_wait_sleep(&bar_Sfree[g], (uint32_t)((j - 1) & 1));
-        ptx::mbar_wait_sleep(&k_full[ks], kph);
+        if (j >= 1) SDB_ISSUER_WAIT(&bar_Sfree[g], (uint32_t)((j - 1) & 1));
+        SDB_ISSUER_WAIT(&k_full[ks], kph);
         ptx::tc_fence_after();
         if (ptx::elect_one()) {
           mma_ksteps<false>(tSg, dQ, atom16, dK0 + (uint32_t)ks * tile16, atom16, idescS, ksteps, 0u);
@@ -516,8 +523,8 @@ __global__ void __launch_bounds__(kFwd2Threads, 1) attn_fwd2_kernel(const __grid
         if (++ks == p.kstages) { ks = 0; kph ^= 1u; }
       }
       if (j >= 1) {
-        ptx::mbar_wait_sleep(&bar_P[g], (uint32_t)((j - 1) & 1));
-        ptx::mbar_wait_sleep(&v_full[vs], vph);
+        SDB_ISSUER_WAIT(&bar_P[g], (uint32_t)((j - 1) & 1));
+        SDB_ISSUER_WAIT(&v_full[vs], vph);
         ptx::tc_fence_after();
         const uint64_t dV = dV0 + (uint32_t)vs * tile16;
         if (ptx::elect_one()) {
@@ -781,7 +788,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       __syncwarp();
       for (int i = 0; i < p.ncb; ++i) {
         const int s = i % p.stages, n = i / p.stages;
-        ptx::mbar_wait_sleep(&c_empty[s], (uint32_t)((n & 1) ^ 1));
+        SDB_ISSUER_WAIT(&c_empty[s], (uint32_t)((n & 1) ^ 1));
         if (ptx::elect_one()) {
           ptx::mbar_expect_tx(&c_full[s], 2 * ctile);
           tma_tile(sC1 + (size_t)s * ctile, &p.mapC1, &c_full[s], p.atoms, catom, i * p.bc, h, b);
@@ -808,12 +815,12 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         // S/dP buffer `buf` was last read by compute(i - NBUF), which arrives on bar_Sfree as soon as the scores are
         // in its registers (before the exp2 / pack / store work on them)
         if (i >= NBUF) {
-          ptx::mbar_wait_sleep(&bar_Sfree[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
+          SDB_ISSUER_WAIT(&bar_Sfree[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
           // aliased operands live in the S / dP columns until the accumulations of that block have read them
-          if (p.alias) ptx::mbar_wait_sleep(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
+          if (p.alias) SDB_ISSUER_WAIT(&bar_acc[buf], (uint32_t)(((i - NBUF) >> (NBUF - 1)) & 1));
         }
         SDB_TL(second ? 1 : 0, i, 0);
-        ptx::mbar_wait_sleep(&c_full[ss], sph);
+        SDB_ISSUER_WAIT(&c_full[ss], sph);
         ptx::tc_fence_after();
         SDB_TL(second ? 1 : 0, i, 1);
         const uint32_t tSi = tS + (uint32_t)buf * 2u * (uint32_t)p.bc + (second ? (uint32_t)p.bc : 0u);
@@ -840,8 +847,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
       for (int i = 0; i < p.ncb; ++i) {
         const int buf = i & (NBUF - 1);
         SDB_TL(second ? 3 : 2, i, 0);
-        ptx::mbar_wait_sleep(&bar_PdS[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
-        ptx::mbar_wait_sleep(&c_full[as], aph);  // already complete (the scores of block i used it); orders the async proxy
+        SDB_ISSUER_WAIT(&bar_PdS[buf], (uint32_t)((i >> (NBUF - 1)) & 1));
+        SDB_ISSUER_WAIT(&c_full[as], aph);  // already complete (the scores of block i used it); orders the async proxy
         ptx::tc_fence_after();
         SDB_TL(second ? 3 : 2, i, 1);
         const uint32_t aop = op_base(buf, second);
