@@ -623,6 +623,7 @@ size_t gn_ws_bytes(const GnShape& s) {
 
 // ---------------------------------------------------------------------------------------------------------------
 // LayerNorm: one warp per row; lane l owns vectors l, l+32, ... (C <= 2048).
+__device__ __forceinline__ void opaque_u4(uint4& v) { asm volatile("" : "+r"(v.x), "+r"(v.y), "+r"(v.z), "+r"(v.w)); }
 constexpr int kLnMaxVec = 8;  // C <= 8*32*8 = 2048
 constexpr int kLnRowsPerBlock = 8;
 
@@ -633,36 +634,58 @@ ln_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gam
   sdb::pdl_trigger();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nv = C / 8;
-  for (int row = blockIdx.x * kLnRowsPerBlock + warp; row < rows; row += gridDim.x * kLnRowsPerBlock) {
-    float xv[NV][8];
-    float s0 = 0.f, s1 = 0.f;
+  // R rows of a warp are in flight together (all their 16-byte loads are issued before the first reduction): one row
+  // at a time left the kernel latency-bound (a row is only 640 B .. 2.5 KB)
+  constexpr int R = (NV <= 2) ? 4 : (NV <= 4 ? 2 : 1);
+  const int wstride = gridDim.x * kLnRowsPerBlock;
+  for (int row0 = blockIdx.x * kLnRowsPerBlock + warp; row0 < rows; row0 += R * wstride) {
+    uint4 xr[R][NV];
+    float s0[R], s1[R];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
-      if (v < nv) {
-        unpack8(sdb::ld_u4(x + (size_t)row * C + v * 8), xv[k]);
+    for (int r = 0; r < R; ++r) {
+      const int row = row0 + r * wstride;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { s0 += xv[k][i]; s1 = fmaf(xv[k][i], xv[k][i], s1); }
+      for (int k = 0; k < NV; ++k) {
+        const int v = lane + 32 * k;
+        xr[r][k] = (row < rows && v < nv) ? sdb::ld_u4(x + (size_t)row * C + v * 8) : make_uint4(0u, 0u, 0u, 0u);
       }
     }
-    s0 = sdb::warp_sum(s0);
-    s1 = sdb::warp_sum(s1);
-    const float mean = s0 / (float)C;
-    const float var = fmaxf(0.0f, s1 / (float)C - mean * mean);
-    const float rstd = rsqrtf(var + eps);
-    if (lane == 0 && stats != nullptr) stats[row] = make_float2(mean, rstd);
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
-      if (v < nv) {
-        float o[8];
-        const float4 g0 = sdb::ld_f4(gamma + v * 8), g1 = sdb::ld_f4(gamma + v * 8 + 4);
-        const float4 b0 = sdb::ld_f4(beta + v * 8), b1 = sdb::ld_f4(beta + v * 8 + 4);
-        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    for (int r = 0; r < R; ++r) {
+      s0[r] = 0.f; s1[r] = 0.f;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) o[i] = fmaf((xv[k][i] - mean) * rstd, g[i], bb[i]);
-        sdb::st_u4(y + (size_t)row * C + v * 8, pack8(o));
+      for (int k = 0; k < NV; ++k) {
+        float xv[8];
+        unpack8(xr[r][k], xv);  // vectors past the row are zero: they add nothing
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { s0[r] += xv[i]; s1[r] = fmaf(xv[i], xv[i], s1[r]); }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) { s0[r] = sdb::warp_sum(s0[r]); s1[r] = sdb::warp_sum(s1[r]); }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const int row = row0 + r * wstride;
+      if (row >= rows) break;
+      const float mean = s0[r] / (float)C;
+      const float var = fmaxf(0.0f, s1[r] / (float)C - mean * mean);
+      const float rstd = rsqrtf(var + eps);
+      if (lane == 0 && stats != nullptr) stats[row] = make_float2(mean, rstd);
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int v = lane + 32 * k;
+        if (v < nv) {
+          float xv[8], o[8];
+          opaque_u4(xr[r][k]);
+          unpack8(xr[r][k], xv);
+          const float4 g0 = sdb::ld_f4(gamma + v * 8), g1 = sdb::ld_f4(gamma + v * 8 + 4);
+          const float4 b0 = sdb::ld_f4(beta + v * 8), b1 = sdb::ld_f4(beta + v * 8 + 4);
+          const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] = fmaf((xv[i] - mean) * rstd, g[i], bb[i]);
+          sdb::st_u4(y + (size_t)row * C + v * 8, pack8(o));
+        }
       }
     }
   }
@@ -685,39 +708,68 @@ ln_bwd_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restri
 #pragma unroll
     for (int i = 0; i < 8; ++i) { dg[k][i] = 0.f; db[k][i] = 0.f; g[k][i] = (v < nv) ? gamma[v * 8 + i] : 0.f; }
   }
-  for (int row = blockIdx.x * kLnRowsPerBlock + warp; row < rows; row += gridDim.x * kLnRowsPerBlock) {
-    const float2 st = stats[row];
-    float xh[NV][8], gd[NV][8];
-    float s0 = 0.f, s1 = 0.f;
+  // R rows of a warp in flight together; x / dy stay packed in registers and are unpacked again for the second pass
+  // (the second unpack is hidden from CSE: keeping the unpacked floats of every row alive would not fit the registers)
+  constexpr int R = (NV <= 2) ? 2 : 1;
+  const int wstride = gridDim.x * kLnRowsPerBlock;
+  for (int row0 = blockIdx.x * kLnRowsPerBlock + warp; row0 < rows; row0 += R * wstride) {
+    uint4 xr[R][NV], dr[R][NV];
+    float2 st[R];
+    float s0[R], s1[R];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
-      if (v < nv) {
+    for (int r = 0; r < R; ++r) {
+      const int row = row0 + r * wstride;
+      st[r] = (row < rows) ? stats[row] : make_float2(0.f, 0.f);
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int v = lane + 32 * k;
+        const bool in = row < rows && v < nv;
+        xr[r][k] = in ? sdb::ld_u4(x + (size_t)row * C + v * 8) : make_uint4(0u, 0u, 0u, 0u);
+        dr[r][k] = in ? sdb::ld_u4(dy + (size_t)row * C + v * 8) : make_uint4(0u, 0u, 0u, 0u);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      s0[r] = 0.f; s1[r] = 0.f;
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
         float xv[8], dv[8];
-        unpack8(sdb::ld_u4(x + (size_t)row * C + v * 8), xv);
-        unpack8(sdb::ld_u4(dy + (size_t)row * C + v * 8), dv);
+        unpack8(xr[r][k], xv);
+        unpack8(dr[r][k], dv);  // dy = 0 past the row / the rows: nothing is added
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          xh[k][i] = (xv[i] - st.x) * st.y;
-          gd[k][i] = g[k][i] * dv[i];
-          s0 += gd[k][i];
-          s1 = fmaf(gd[k][i], xh[k][i], s1);
-          dg[k][i] = fmaf(dv[i], xh[k][i], dg[k][i]);
+          const float xh = (xv[i] - st[r].x) * st[r].y;
+          const float gd = g[k][i] * dv[i];
+          s0[r] += gd;
+          s1[r] = fmaf(gd, xh, s1[r]);
+          dg[k][i] = fmaf(dv[i], xh, dg[k][i]);
           db[k][i] += dv[i];
         }
       }
     }
-    s0 = sdb::warp_sum(s0) / (float)C;
-    s1 = sdb::warp_sum(s1) / (float)C;
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-      const int v = lane + 32 * k;
-      if (v < nv) {
-        float o[8], av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (add != nullptr) unpack8(sdb::ld_u4(add + (size_t)row * C + v * 8), av);
+    for (int r = 0; r < R; ++r) { s0[r] = sdb::warp_sum(s0[r]) / (float)C; s1[r] = sdb::warp_sum(s1[r]) / (float)C; }
 #pragma unroll
-        for (int i = 0; i < 8; ++i) o[i] = st.y * (gd[k][i] - s0 - xh[k][i] * s1) + av[i];
-        sdb::st_u4(dx + (size_t)row * C + v * 8, pack8(o));
+    for (int r = 0; r < R; ++r) {
+      const int row = row0 + r * wstride;
+      if (row >= rows) break;
+#pragma unroll
+      for (int k = 0; k < NV; ++k) {
+        const int v = lane + 32 * k;
+        if (v < nv) {
+          float xv[8], dv[8], o[8], av[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+          opaque_u4(xr[r][k]);
+          opaque_u4(dr[r][k]);
+          unpack8(xr[r][k], xv);
+          unpack8(dr[r][k], dv);
+          if (add != nullptr) unpack8(sdb::ld_u4(add + (size_t)row * C + v * 8), av);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float xh = (xv[i] - st[r].x) * st[r].y;
+            o[i] = st[r].y * (g[k][i] * dv[i] - s0[r] - xh * s1[r]) + av[i];
+          }
+          sdb::st_u4(dx + (size_t)row * C + v * 8, pack8(o));
+        }
       }
     }
   }
