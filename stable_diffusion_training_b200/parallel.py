@@ -20,6 +20,7 @@ it with gloo, world_size 2); streams/events are used only for CUDA tensors.
 from __future__ import annotations
 
 import os
+import sys
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch
@@ -176,12 +177,21 @@ def _replay_finish(red: GradReducer, buckets: Sequence[int], loss: torch.Tensor)
         return
     _replay_buckets(red, buckets)
     dev = red.grad.device
-    ev = torch.cuda.Event()
+    debug = os.environ.get("SDB_DP_DEBUG") == "1"
+    ev = torch.cuda.Event(enable_timing=debug)
     ev.record(torch.cuda.current_stream(dev))
     red.comm_stream.wait_event(ev)
     with torch.cuda.stream(red.comm_stream):
         dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=red.group)
         loss.mul_(1.0 / red.world_size)
+        if debug:  # exposed communication: end of this rank's backward -> last all-reduce complete (printed one step late)
+            prev = getattr(red, "_dbg_events", None)
+            if prev is not None and dist.get_rank(red.group) == 0:
+                prev[1].synchronize()
+                print(f"[sdb dp] exposed all-reduce tail {prev[0].elapsed_time(prev[1]):.3f} ms", file=sys.stderr)
+            ev1 = torch.cuda.Event(enable_timing=True)
+            ev1.record(red.comm_stream)
+            red._dbg_events = (ev, ev1)
     torch.cuda.current_stream(dev).wait_stream(red.comm_stream)
 
 
