@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SDB200_ABI_VERSION 2
+#define SDB200_ABI_VERSION 3
 
 #ifndef __CUDA_RUNTIME_H__
 typedef struct CUstream_st* cudaStream_t;
@@ -127,7 +127,9 @@ typedef struct {
   int N;                /* output columns */
   int K;                /* FWD: reduction length per tap (channels of A) */
   int block_n;          /* N tile width, multiple of 16, <= 256 */
-  int splits;           /* WGRAD only */
+  int splits;           /* WGRAD: split of the pixel range. FWD: split-K (> 1: D is an fp32 [pixels, N] buffer, row
+                           stride ldd, that the call zeroes and accumulates partial sums into with red.global.add;
+                           bias / temb / residual / d_stride* must be unset; finish with sdb_splitk_finish) */
   void* d;
   long long ldd;
   long long d_strideW, d_strideH, d_strideN; /* FWD only: element strides of the output pixel grid; all 0 = dense
@@ -210,6 +212,14 @@ int sdb_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, cud
 int sdb_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, long long rows, int cols, int accumulate,
                     cudaStream_t stream);
 int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStream_t stream);
+
+/* Epilogue of a split-K forward GEMM: out[r, c] = bf16(acc[r, c] + bias[c] + temb[r / rows_per_image, c] + residual[r, c])
+ * (bias fp32 [N], temb bf16 [images, ldt], residual bf16 [rows, ldr]; each may be NULL). Replaces the fused epilogue of
+ * sdb_gemm_tc for the low-resolution layers of the UNet (flax nn.Conv / nn.Dense bias add, the time-embedding add of
+ * FlaxResnetBlock2D and the residual adds, diffusers 0.21.4 resnet_flax.py / attention_flax.py). */
+int sdb_splitk_finish(const float* acc, long long lda, const float* bias, const void* temb, long long ldt,
+                      long long rows_per_image, const void* residual, long long ldr, void* out, long long ldo,
+                      long long rows, int N, cudaStream_t stream);
 size_t sdb_colsum_workspace_bytes(long long rows, int cols);
 int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long rows_per_seg, int cols, float* out_total,
                     void* out_seg_bf16, void* workspace, size_t ws_bytes, cudaStream_t stream);

@@ -84,6 +84,7 @@ SIGNATURES = {
     "sdb_upsample2x_bwd": (_I, [_P, _P, _I, _I, _I, _I, _P]),
     "sdb_copy2d_bf16": (_I, [_P, _LL, _P, _LL, _LL, _I, _I, _P]),
     "sdb_add_bf16": (_I, [_P, _P, _P, _LL, _P]),
+    "sdb_splitk_finish": (_I, [_P, _LL, _P, _P, _LL, _LL, _P, _LL, _P, _LL, _LL, _I, _P]),
     "sdb_colsum_workspace_bytes": (_SZ, [_LL, _I]),
     "sdb_colsum_bf16": (_I, [_P, _LL, _I, _LL, _I, _P, _P, _P, _SZ, _P]),
     "sdb_silu_fwd": (_I, [_P, _P, _LL, _P]),

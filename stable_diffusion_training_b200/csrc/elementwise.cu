@@ -318,6 +318,55 @@ extern "C" int sdb_copy2d_bf16(const void* src, long long lds, void* dst, long l
   return SDB_OK;
 }
 
+// out[r, c] = bf16(acc[r, c] + bias[c] + temb[r / rows_per_image, c] + residual[r, c]): the epilogue of a split-K forward
+// GEMM (sdb_gemm_tc with splits > 1 leaves fp32 partial sums in acc)
+__global__ void splitk_finish_kernel(const float* __restrict__ acc, long long lda, const float* __restrict__ bias,
+                                     const __nv_bfloat16* __restrict__ temb, long long ldt, long long rows_per_image,
+                                     const __nv_bfloat16* __restrict__ residual, long long ldr,
+                                     __nv_bfloat16* __restrict__ out, long long ldo, long long rows, int nvec) {
+  sdb::pdl_trigger();
+  const long long total = rows * nvec;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const long long r = i / nvec;
+    const int c = (int)(i - r * nvec) * 8;
+    const float4 a0 = sdb::ld_f4(acc + r * lda + c), a1 = sdb::ld_f4(acc + r * lda + c + 4);
+    float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    if (bias != nullptr) {
+      const float4 b0 = sdb::ld_f4(bias + c), b1 = sdb::ld_f4(bias + c + 4);
+      f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w; f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
+    }
+    if (temb != nullptr) {
+      float t[8];
+      unpack8(sdb::ld_u4(temb + (r / rows_per_image) * ldt + c), t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += t[j];
+    }
+    if (residual != nullptr) {
+      float t[8];
+      unpack8(sdb::ld_u4(residual + r * ldr + c), t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) f[j] += t[j];
+    }
+    sdb::st_u4(out + r * ldo + c, pack8(f));
+  }
+}
+
+extern "C" int sdb_splitk_finish(const float* acc, long long lda, const float* bias, const void* temb, long long ldt,
+                                 long long rows_per_image, const void* residual, long long ldr, void* out, long long ldo,
+                                 long long rows, int N, cudaStream_t stream) {
+  SDB_CHECK_ARG(acc != nullptr && out != nullptr && rows > 0 && N > 0, "sdb_splitk_finish: bad arguments");
+  SDB_CHECK_ARG(N % 8 == 0 && lda % 4 == 0 && ldo % 8 == 0 && ldt % 8 == 0 && ldr % 8 == 0 && rows_per_image > 0,
+                "sdb_splitk_finish: N %% 8, lda %% 4, ldo/ldt/ldr %% 8 and rows_per_image > 0 required");
+  SDB_CHECK_ARG((((uintptr_t)acc | (uintptr_t)out | (uintptr_t)bias | (uintptr_t)temb | (uintptr_t)residual) & 15) == 0,
+                "sdb_splitk_finish: 16-byte alignment required");
+  splitk_finish_kernel<<<ew_grid(rows * (N / 8)), 256, 0, stream>>>(
+      acc, lda, bias, reinterpret_cast<const __nv_bfloat16*>(temb), ldt, rows_per_image,
+      reinterpret_cast<const __nv_bfloat16*>(residual), ldr, reinterpret_cast<__nv_bfloat16*>(out), ldo, rows, N / 8);
+  SDB_CUDA_LAUNCH_CHECK("sdb_splitk_finish");
+  return SDB_OK;
+}
+
 extern "C" int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStream_t stream) {
   SDB_CHECK_ARG(n % 8 == 0, "sdb_add_bf16: n must be a multiple of 8");
   if (n == 0) return SDB_OK;

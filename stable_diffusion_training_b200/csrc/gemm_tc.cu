@@ -72,8 +72,11 @@ struct Tile {
 __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
   Tile ti;
   if (p.mode == SDB_GEMM_FWD) {
-    int n_tile = t % p.tiles_n;
-    int m_tile = t / p.tiles_n;
+    // split-K (p.splits > 1): consecutive tile indices are the K ranges of one output tile
+    int split = t % p.splits;
+    int tt = t / p.splits;
+    int n_tile = tt % p.tiles_n;
+    int m_tile = tt / p.tiles_n;
     int iw = m_tile % p.tw;
     int r = m_tile / p.tw;
     int ih = r % p.th;
@@ -84,8 +87,8 @@ __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
     ti.n_off = n_tile * p.BN;
     ti.tap = 0;
     ti.m_off = 0;
-    ti.kb_begin = 0;
-    ti.num_k = p.ntaps * p.kblocks;
+    ti.kb_begin = split * p.pb_per_split;
+    ti.num_k = min(p.total_pb, ti.kb_begin + p.pb_per_split) - ti.kb_begin;
   } else {
     int split = t % p.splits;
     int r = t / p.splits;
@@ -165,8 +168,9 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
           } else if (SDB_DBG(p, 1)) {  // experiment: no TMA traffic (SDB_GEMM_DBG=1)
             ptx::mbar_expect_tx(&full_bar[stage], 0u);
           } else if (MODE == SDB_GEMM_FWD) {
-            const int tap = it / p.kblocks;
-            const int kb = it - tap * p.kblocks;
+            const int kk = ti.kb_begin + it;
+            const int tap = kk / p.kblocks;
+            const int kb = kk - tap * p.kblocks;
             const uint32_t bbytes = p.b_mn ? (uint32_t)ti.nboxes * kBoxBytes : p.b_stage_bytes;
             ptx::mbar_expect_tx(&full_bar[stage], p.a_stage_bytes + bbytes);
             ptx::tma_load_4d(sa, &p.mapA[p.tap_src[tap]], &full_bar[stage], kb * kBlockK, ti.w0 + p.tap_dw[tap],
@@ -273,6 +277,25 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const __nv_bfloat16* res = p.residual ? p.residual + grow * p.ldr + ti.n_off : nullptr;
         const float* bias = p.bias ? p.bias + ti.n_off : nullptr;
         const __nv_bfloat16* temb = p.temb ? p.temb + (long long)n * p.ldt + ti.n_off : nullptr;
+        if (p.splits > 1) {
+          // split-K: fp32 partial sums into the (zeroed) [pixels, N] buffer; sdb_splitk_finish adds the rest
+          float* acc_out = reinterpret_cast<float*>(p.d) + grow * p.ldd + ti.n_off;
+          for (int c0 = 0; c0 < ti.nw; c0 += 32) {
+            uint32_t v[32];
+            ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
+            ptx::tmem_ld_wait();
+            if (valid) {
+#pragma unroll
+              for (int j4 = 0; j4 < 32; j4 += 4) {
+                if (c0 + j4 < ti.nw)
+                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(acc_out + c0 + j4),
+                               "f"(__uint_as_float(v[j4])), "f"(__uint_as_float(v[j4 + 1])),
+                               "f"(__uint_as_float(v[j4 + 2])), "f"(__uint_as_float(v[j4 + 3]))
+                               : "memory");
+              }
+            }
+          }
+        } else
         for (int c0 = 0; c0 < ti.nw; c0 += 32) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
@@ -499,8 +522,19 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     p.K = d->K;
     p.kblocks = sdb::ceil_div(p.K, kBlockK);
     p.tiles_m = p.tw * p.th * p.tn;
-    p.total_tiles = p.tiles_m * p.tiles_n;
-    p.splits = 1;
+    p.total_pb = p.ntaps * p.kblocks;  // K blocks of one output tile
+    int splits = d->splits < 1 ? 1 : d->splits;
+    if (splits > p.total_pb) splits = p.total_pb;
+    p.pb_per_split = sdb::ceil_div(p.total_pb, splits);
+    p.splits = sdb::ceil_div(p.total_pb, p.pb_per_split);
+    p.total_tiles = p.tiles_m * p.tiles_n * p.splits;
+    if (p.splits > 1) {
+      SDB_CHECK_ARG(d->bias == nullptr && d->temb == nullptr && d->residual == nullptr && d->d_strideW == 0 &&
+                        d->d_strideH == 0 && d->d_strideN == 0 && d->N % 4 == 0 && d->ldd % 4 == 0,
+                    "sdb_gemm_tc: split-K forward accumulates plain fp32 partial sums (no epilogue terms, dense output)");
+      const cudaError_t me = cudaMemsetAsync(d->d, 0, (size_t)p.W * p.H * p.NI * (size_t)d->ldd * sizeof(float), stream);
+      if (me != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: memset: %s", cudaGetErrorString(me));
+    }
     if (p.b_mn) {
       rc = encode_view(&p.mapB, d->b, 64, 64, 1, 1, "B (weights [K,N])");
       p.b_stage_bytes = (uint32_t)(((p.BN + 63) / 64) * kBoxBytes);

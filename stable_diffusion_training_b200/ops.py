@@ -117,6 +117,70 @@ def _pick_tile(N: int, pix, b_mn: bool, nkb: int):
     return best
 
 
+_INGEST_B_PER_CLK = 48.0  # bytes per cycle an SM takes in from L2 under full-chip load (r2g / r2f: 46-48 for every shape)
+_SPLITK_CACHE: dict = {}
+
+
+def _ingest_kblock_clks(mt: int, bn: int, b_mn: bool) -> float:
+    bcols = -(-bn // 64) * 64 if b_mn else bn
+    stage_bytes = (128 * mt + bcols) * 128
+    mma = 4 * (bn / 2 + 43.0) if mt == 1 else 8 * (38.5 + 0.375 * bn)
+    return max(stage_bytes / _INGEST_B_PER_CLK, mma)
+
+
+def _model_time(N, pix, b_mn, nkb, mt, bn, splits):
+    """Modelled cycles of a forward GEMM with (mt, bn) tiles and `splits` K ranges per tile, or None if illegal."""
+    W, H, NI = pix
+    try:
+        bw, bh, bn_ = _pixel_box(W, H, NI, 128 * mt)
+    except AssertionError:
+        return None
+    if mt == 2 and W * H * NI < 256:
+        return None
+    m_tiles = -(-W // bw) * -(-H // bh) * -(-NI // bn_)
+    tiles_n = -(-N // bn)
+    if bn * (tiles_n - 1) >= N:
+        return None
+    per = -(-nkb // splits)
+    if splits > 1 and per * (splits - 1) >= nkb:
+        return None
+    fixed = 1500.0 if mt == 1 else 4000.0 + 16.0 * bn
+    waves = -(-(m_tiles * tiles_n * splits) // NUM_SMS)
+    t = waves * (per * _ingest_kblock_clks(mt, bn, b_mn) + fixed)
+    if splits > 1:  # memset + red.add traffic + the finishing pass (two extra launches); fitted to r2v measurements
+        t += 24000.0 + W * H * NI * N * (4.0 * splits + 14.0) / 3300.0
+    return t
+
+
+def _pick_splitk(N: int, pix, b_mn: bool, nkb: int, mt0: int, bn0: int):
+    """(mt, bn, splits) when splitting K over several CTAs per output tile beats the regular pick by >= 15 % in the
+    ingest model — the low-resolution layers (M = 512 / 2048 pixels) have too few 128 x ~144 tiles to afford large
+    ones, and small tiles move more operand bytes per FLOP than an SM can take in (~48 B/clk)."""
+    key = (N, pix, b_mn, nkb, mt0, bn0)
+    if key in _SPLITK_CACHE:
+        return _SPLITK_CACHE[key]
+    best = None
+    force = os.environ.get("SDB_SPLITK_FORCE")
+    if os.environ.get("SDB_SPLITK", "1") != "0":
+        if force:
+            mt, bn, sp = (int(v) for v in force.split(","))
+            if _model_time(N, pix, b_mn, nkb, mt, min(bn, (N + 15) // 16 * 16), sp) is not None and sp > 1:
+                best = (mt, min(bn, (N + 15) // 16 * 16), sp)
+        else:
+            t0 = _model_time(N, pix, b_mn, nkb, mt0, bn0, 1)
+            best_t = None if t0 is None else 0.85 * t0
+            for mt in (1, 2):
+                for bn in (128, 160, 192, 256):
+                    if bn > (N + 15) // 16 * 16:
+                        continue
+                    for sp in range(2, 9):
+                        t = _model_time(N, pix, b_mn, nkb, mt, bn, sp)
+                        if t is not None and best_t is not None and t < best_t:
+                            best, best_t = (mt, bn, sp), t
+    _SPLITK_CACHE[key] = best
+    return best
+
+
 _SKIP_GEMM = set(x for x in os.environ.get("SDB_SKIP", "").split(",") if x.startswith("gemm_"))
 
 
@@ -151,11 +215,30 @@ def gemm_fwd(a_views, taps, b: torch.Tensor, b_mn: bool, out: torch.Tensor, pix,
     _set_taps(d, taps)
     d.outW, d.outH, d.outN = W, H, NI
     d.N, d.K = N, K
-    mt, d.block_n = _pick_tile(N, (W, H, NI), bool(b_mn), len(taps) * -(-K // 64))
+    nkb = len(taps) * -(-K // 64)
+    mt, d.block_n = _pick_tile(N, (W, H, NI), bool(b_mn), nkb)
+    out2 = out.view(-1, out.shape[-1])
+    sk = _pick_splitk(N, (W, H, NI), bool(b_mn), nkb, mt, d.block_n) if (impl == "tc" and d_strides is None) else None
+    if sk is not None:
+        # split-K: fp32 partial sums in scratch, then one pass adds bias / time embedding / residual and converts
+        mt, d.block_n, d.splits = sk
+        d.m_halves = mt
+        d.bw, d.bh, d.bn = _pixel_box(W, H, NI, 128 * mt)
+        rows = W * H * NI
+        ws = workspace(out.device, rows * N * 4)
+        d.d = ws.data_ptr()
+        d.ldd = N
+        _launch(d, impl)
+        r2 = residual.view(-1, residual.shape[-1]) if residual is not None else None
+        _lib.check(_lib.lib().sdb_splitk_finish(
+            ws.data_ptr(), N, _lib.ptr(bias), temb.data_ptr() if temb is not None else None,
+            temb.stride(0) if temb is not None else 0, W * H, r2.data_ptr() if r2 is not None else None,
+            r2.stride(0) if r2 is not None else 0, out2.data_ptr() + d_offset * out2.element_size(), out2.stride(0),
+            rows, N, _lib.stream_ptr()), "sdb_splitk_finish")
+        return
     d.m_halves = mt
     d.bw, d.bh, d.bn = _pixel_box(W, H, NI, 128 * mt)
     d.splits = 1
-    out2 = out.view(-1, out.shape[-1])
     d.d = out2.data_ptr() + d_offset * out2.element_size()
     d.ldd = out2.stride(0)
     if d_strides is not None:

@@ -171,6 +171,57 @@ def test_conv3x3_tile_shapes(cuda, force_tile, mt, bn, B, H, W, Cin, Cout):
     assert err <= 2e-3 * max(1.0, ref_dw.abs().max().item()), err
 
 
+@pytest.fixture
+def force_splitk(monkeypatch):
+    """Force the split-K forward path (SDB_SPLITK_FORCE = "halves,block_n,splits") and drop the picker caches."""
+    def _set(spec):
+        monkeypatch.setenv("SDB_SPLITK_FORCE", spec)
+        ops._SPLITK_CACHE.clear()
+    yield _set
+    ops._SPLITK_CACHE.clear()
+
+
+@pytest.mark.parametrize("spec", ["1,128,2", "1,256,3", "2,256,7", "2,160,4"])
+@pytest.mark.parametrize("B,H,W,Cin,Cout", [(8, 16, 16, 320, 320), (8, 8, 8, 192, 640), (2, 16, 16, 64, 96),
+                                            (3, 12, 20, 64, 200)])
+def test_conv3x3_splitk(cuda, force_splitk, spec, B, H, W, Cin, Cout):
+    """Split-K forward / dgrad (fp32 partial sums with red.global.add, then sdb_splitk_finish adds bias, time embedding
+    and residual) gives the same result as the fused-epilogue kernel: every K range, ragged last split, 256-row tiles."""
+    force_splitk(spec)
+    x = _rand((B, H, W, Cin), cuda, seed=1)
+    w = _rand((3, 3, Cin, Cout), cuda, 1.0 / (9 * Cin) ** 0.5, seed=2)
+    bias = torch.randn(Cout, device=cuda)
+    temb = _rand((B, Cout), cuda, seed=7)
+    res = _rand((B, H, W, Cout), cuda, seed=5)
+    y = ops.conv3x3(x, w, bias=bias, temb=temb, residual=res)
+    xt = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wt = w.float().permute(3, 2, 0, 1).contiguous().requires_grad_(True)
+    ref = torch.nn.functional.conv2d(xt, wt, bias, padding=1)
+    torch.cuda.synchronize()
+    _close(y, ref.permute(0, 2, 3, 1) + res.float() + temb.float()[:, None, None, :])
+    dy = _rand((B, H, W, Cout), cuda, seed=3)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = ops.conv3x3_dgrad(dy, w)
+    torch.cuda.synchronize()
+    _close(dx, xt.grad.permute(0, 2, 3, 1), atol=4e-2)
+
+
+@pytest.mark.parametrize("spec", ["1,128,2", "2,256,5"])
+@pytest.mark.parametrize("M,K,N", [(2048, 1280, 320), (616, 768, 320), (300, 192, 200)])
+def test_linear_splitk(cuda, force_splitk, spec, M, K, N):
+    force_splitk(spec)
+    x = _rand((M, K), cuda, seed=1)
+    w = _rand((K, N), cuda, 1.0 / K ** 0.5, seed=2)
+    bias = torch.randn(N, device=cuda)
+    res = _rand((M, N), cuda, seed=4)
+    y = ops.linear(x, w, bias=bias, residual=res)
+    dy = _rand((M, N), cuda, seed=3)
+    dx = ops.linear_dgrad(dy, w)
+    torch.cuda.synchronize()
+    _close(y, x.float() @ w.float() + bias + res.float())
+    _close(dx, dy.float() @ w.float().t(), atol=4e-2)
+
+
 @pytest.mark.parametrize("mt", [1, 2])
 @pytest.mark.parametrize("M,K,N", [(512, 320, 320), (8192, 640, 1280), (616, 768, 320), (300, 64, 200)])
 def test_linear_tile_shapes(cuda, force_tile, mt, M, K, N):

@@ -1,0 +1,5 @@
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > gpurun_out/r2u_pytest.log
+timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/r2u_smoke.log 2>&1
+timeout 900 python bench.py > gpurun_out/r2u_bench.json 2> gpurun_out/r2u_bench.err
+timeout 300 python bench.py --impl reference --steps 1 --warmup 0 > gpurun_out/r2u_bench_ref.json 2> gpurun_out/r2u_bench_ref.err
+true

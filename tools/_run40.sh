@@ -1,0 +1,4 @@
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > gpurun_out/r2w_pytest.log
+timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu --no-kernels > gpurun_out/r2w_bench.json 2> gpurun_out/r2w_bench.err
+SDB_SPLITK=0 timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu --no-kernels > gpurun_out/r2w_bench_nosplit.json 2>> gpurun_out/r2w_bench.err
+true
