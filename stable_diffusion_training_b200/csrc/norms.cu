@@ -53,7 +53,15 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   o.z = sdb::pack_bf16x2(f[4], f[5]); o.w = sdb::pack_bf16x2(f[6], f[7]);
   return o;
 }
-__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
+// MUFU.EX2 + MUFU.RCP (2 ulp): the IEEE division of `1.0f / (...)` costs ~10 instructions with its fix-up path, and these
+// kernels are instruction-bound (profiles/r1n_ncu_full.md); the result is rounded to bf16 anyway
+__device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+// MUFU.TANH (max relative error 2^-11) instead of the ~25-instruction tanhf
+__device__ __forceinline__ float tanh_approx_f(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // GroupNorm pass 1: per (sample, chunk, channel) partial sums.
@@ -825,13 +833,13 @@ int ln_grid(int rows) {
 // GEGLU: u [rows, 2*H] = [lin | gate]; out [rows, H] = lin * gelu_tanh(gate)
 __device__ __forceinline__ float gelu_tanh_f(float z) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
-  const float t = tanhf(k0 * (z + k1 * z * z * z));
+  const float t = tanh_approx_f(k0 * (z + k1 * z * z * z));
   return 0.5f * z * (1.0f + t);
 }
 __device__ __forceinline__ void gelu_tanh_both(float z, float* val, float* grad) {
   const float k0 = 0.7978845608028654f, k1 = 0.044715f;
   const float inner = k0 * (z + k1 * z * z * z);
-  const float t = tanhf(inner);
+  const float t = tanh_approx_f(inner);
   *val = 0.5f * z * (1.0f + t);
   *grad = 0.5f * (1.0f + t) + 0.5f * z * (1.0f - t * t) * k0 * (1.0f + 3.0f * k1 * z * z);
 }
