@@ -328,7 +328,7 @@ __global__ void splitk_finish_kernel(const float* __restrict__ acc, long long ld
   const long long total = rows * nvec;
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-    const long long r = i / nvec;
+    const long long r = (long long)((unsigned int)i / (unsigned int)nvec);  // rows * nvec < 2^31 (checked on the host)
     const int c = (int)(i - r * nvec) * 8;
     const float4 a0 = sdb::ld_f4(acc + r * lda + c), a1 = sdb::ld_f4(acc + r * lda + c + 4);
     float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
@@ -338,7 +338,7 @@ __global__ void splitk_finish_kernel(const float* __restrict__ acc, long long ld
     }
     if (temb != nullptr) {
       float t[8];
-      unpack8(sdb::ld_u4(temb + (r / rows_per_image) * ldt + c), t);
+      unpack8(sdb::ld_u4(temb + (long long)((unsigned int)r / (unsigned int)rows_per_image) * ldt + c), t);
 #pragma unroll
       for (int j = 0; j < 8; ++j) f[j] += t[j];
     }
@@ -356,6 +356,7 @@ extern "C" int sdb_splitk_finish(const float* acc, long long lda, const float* b
                                  long long rows_per_image, const void* residual, long long ldr, void* out, long long ldo,
                                  long long rows, int N, cudaStream_t stream) {
   SDB_CHECK_ARG(acc != nullptr && out != nullptr && rows > 0 && N > 0, "sdb_splitk_finish: bad arguments");
+  SDB_CHECK_ARG(rows * (N / 8) < (1ll << 31) && rows_per_image < (1ll << 31), "sdb_splitk_finish: too many elements");
   SDB_CHECK_ARG(N % 8 == 0 && lda % 4 == 0 && ldo % 8 == 0 && ldt % 8 == 0 && ldr % 8 == 0 && rows_per_image > 0,
                 "sdb_splitk_finish: N %% 8, lda %% 4, ldo/ldt/ldr %% 8 and rows_per_image > 0 required");
   SDB_CHECK_ARG((((uintptr_t)acc | (uintptr_t)out | (uintptr_t)bias | (uintptr_t)temb | (uintptr_t)residual) & 15) == 0,
