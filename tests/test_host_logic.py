@@ -81,3 +81,30 @@ def test_c_abi_exports_every_declared_symbol():
     assert isinstance(lib.sdb_last_error_string(), bytes)
     # struct layout agreement between ctypes and the header
     assert ctypes.sizeof(_lib.View4) == 48
+
+
+def test_tile_and_splitk_pickers_return_legal_shapes():
+    """The GEMM tile picker and the split-K decision are pure host logic: every answer must be a shape sdb_gemm_tc
+    accepts (block_n a multiple of 16 <= 256, 1 or 2 halves, a pixel box of 128 * halves, no empty last K range)."""
+    from stable_diffusion_training_b200 import ops
+    shapes = [(320, (64, 64, 8), True, 45), (640, (32, 32, 8), False, 90), (1280, (16, 16, 8), True, 180),
+              (1280, (8, 8, 8), False, 180), (1280, (16, 16, 8), True, 360), (2560, (8, 8, 8), False, 180),
+              (10240, (2048, 1, 1), True, 20), (320, (616, 1, 1), True, 12), (200, (300, 1, 1), True, 3)]
+    for N, pix, b_mn, nkb in shapes:
+        mt, bn = ops._pick_tile(N, pix, b_mn, nkb)
+        assert mt in (1, 2) and bn % 16 == 0 and 16 <= bn <= 256
+        bw, bh, bn_ = ops._pixel_box(*pix, 128 * mt)
+        assert bw * bh * bn_ == 128 * mt
+        sk = ops._pick_splitk(N, pix, b_mn, nkb, mt, bn)
+        if sk is not None:
+            smt, sbn, sp = sk
+            assert smt in (1, 2) and sbn % 16 == 0 and sbn <= 256 and 2 <= sp <= 8
+            per = -(-nkb // sp)
+            assert per * (sp - 1) < nkb  # the last K range is not empty
+            t_split = ops._model_time(N, pix, b_mn, nkb, smt, sbn, sp)
+            t_plain = ops._model_time(N, pix, b_mn, nkb, mt, bn, 1)
+            assert t_split < 0.85 * t_plain
+    # the 8x8 level of SD-1.5 (512 pixels, N = 1280, K = 9 * 1280) is the case split-K exists for
+    assert ops._pick_splitk(1280, (8, 8, 8), True, 180, *ops._pick_tile(1280, (8, 8, 8), True, 180)) is not None
+    # the 64x64 level has enough tiles: no split
+    assert ops._pick_splitk(320, (64, 64, 8), True, 45, *ops._pick_tile(320, (64, 64, 8), True, 45)) is None
