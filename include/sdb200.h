@@ -107,7 +107,7 @@ typedef struct {
  * mode SDB_GEMM_WGRAD: dW[tap_brow[t] + m, n] (+)= sum_pixels A_src(tap)[pixel + (dh,dw), m] * B[pixel, n]
  *      A and B are both pixel-major activations (B is passed as `b`, a 4-D view over the same pixel space);
  *      a K block is a box (bw, bh, bn) of 64 pixels; output fp32 with row stride ldd; `splits` > 1 splits the pixel
- *      range and accumulates with red.global.add (the caller zeroes D first); splits == 1 stores.  */
+ *      range and accumulates with red.global.add (the call zeroes the rows of D it covers first); splits == 1 stores.  */
 enum { SDB_GEMM_FWD = 0, SDB_GEMM_WGRAD = 1 };
 
 typedef struct {

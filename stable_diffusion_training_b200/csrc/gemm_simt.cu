@@ -142,6 +142,13 @@ extern "C" int sdb_gemm_simt(const sdb_gemm_desc* d, cudaStream_t stream) {
     int chunks = d->splits < 1 ? 1 : d->splits;
     if (chunks > npix) chunks = (int)npix;
     p.pixel_chunks = chunks;
+    if (chunks > 1) {  // same contract as sdb_gemm_tc: the call zeroes the rows it accumulates into
+      int last_row = 0;
+      for (int t = 0; t < d->ntaps; ++t) last_row = d->tap_brow[t] > last_row ? d->tap_brow[t] : last_row;
+      const cudaError_t me = cudaMemset2DAsync(d->d, (size_t)d->ldd * sizeof(float), 0, (size_t)d->N * sizeof(float),
+                                               (size_t)last_row + (size_t)d->M, stream);
+      if (me != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_simt: memset: %s", cudaGetErrorString(me));
+    }
     dim3 grid((unsigned)blocks, (unsigned)chunks);
     simt_wgrad_kernel<<<grid, 256, 0, stream>>>(p);
   }

@@ -558,6 +558,13 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     p.total_tiles = p.ntaps * p.tiles_m * p.tiles_n * p.splits;
     rc = encode_view(&p.mapB, d->b, 64, d->bw, d->bh, d->bn, "B (wgrad output gradients)");
     if (rc) return rc;
+    if (p.splits > 1) {  // the pixel ranges are accumulated with red.global.add: start from zero (a memset node, no SMs)
+      int last_row = 0;
+      for (int t = 0; t < d->ntaps; ++t) last_row = d->tap_brow[t] > last_row ? d->tap_brow[t] : last_row;
+      const cudaError_t me = cudaMemset2DAsync(d->d, (size_t)d->ldd * sizeof(float), 0, (size_t)d->N * sizeof(float),
+                                               (size_t)last_row + (size_t)d->M, stream);
+      if (me != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: memset: %s", cudaGetErrorString(me));
+    }
     p.b_stage_bytes = (uint32_t)(((p.BN + 63) / 64) * kBoxBytes);
   }
   p.b_stage_bytes = (p.b_stage_bytes + 1023u) & ~1023u;

@@ -277,9 +277,7 @@ def gemm_wgrad(a_views, taps, b_view: View4, out: torch.Tensor, pix, M: int, N: 
     tiles = len(taps) * -(-M // (128 * d.m_halves)) * -(-N // d.block_n)
     total_pb = -(-W // d.bw) * -(-H // d.bh) * -(-NI // d.bn)
     splits = max(1, min(total_pb, (2 * NUM_SMS) // max(1, tiles)))
-    d.splits = splits
-    if splits > 1:
-        out.zero_()
+    d.splits = splits  # > 1: sdb_gemm_tc zeroes the output rows itself (memset node) before the red.add accumulation
     d.d = out.data_ptr()
     d.ldd = out.stride(0)
     _launch(d, impl)
