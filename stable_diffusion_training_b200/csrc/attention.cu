@@ -64,14 +64,6 @@ __device__ __forceinline__ void tma_tile(uint8_t* dst, const CUtensorMap* m, uin
   for (int a = 0; a < atoms; ++a) ptx::tma_load_4d(dst + a * atom_bytes, m, bar, 64 * a, row0, h, b);
 }
 
-// UMMA descriptors for the two operand flavours used here
-__device__ __forceinline__ uint64_t desc_kmajor(uint32_t base, uint32_t atom_bytes, int kstep) {
-  return ptx::umma_desc_sw128(base + (uint32_t)(kstep >> 2) * atom_bytes + (uint32_t)(kstep & 3) * 32u, 0u, 1024u);
-}
-__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t base, uint32_t atom_bytes, int kstep) {
-  return ptx::umma_desc_sw128(base + (uint32_t)kstep * 2048u, atom_bytes, 1024u);
-}
-
 // Issue `ksteps` K = 16 MMAs from precomputed base descriptors. The smem address field is the low 14 bits of the
 // descriptor (16-byte units), so stepping along K is an integer add: +2 per step inside a 64-column swizzle atom and a
 // jump to the next atom every 4 steps (K-major), or +128 per 16 K-rows (MN-major). Keeping this loop free of divisions
