@@ -117,7 +117,8 @@ def _pick_tile(N: int, pix, b_mn: bool, nkb: int):
     return best
 
 
-_INGEST_B_PER_CLK = 48.0  # bytes per cycle an SM takes in from L2 under full-chip load (r2g / r2f: 46-48 for every shape)
+_INGEST_B_PER_CLK = 48.0  # bytes per cycle the GEMM main loop moves per SM (r2g / r2f: 46-48 for every tile shape; a
+# property of its 4-deep operand ring, not of the fabric: tools/ingest_rate.cu reaches 110 B/clk without the MMAs)
 _SPLITK_CACHE: dict = {}
 
 
