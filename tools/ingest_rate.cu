@@ -10,10 +10,11 @@
 #include <cuda_runtime.h>
 #include "../stable_diffusion_training_b200/csrc/ptx_sm100.cuh"
 
-constexpr int kBoxBytes = 64 * 128;  // 64 rows x 64 bf16
+constexpr int kBoxBytes = 64 * 128;  // 64 rows x 64 bf16 (the unit of the stage sizes below)
 
+// box_mult: rows of one TMA box / 64 (1: 8 KB per instruction, 4: 32 KB per instruction like the GEMM's 256-pixel A box)
 __global__ void __launch_bounds__(64, 1) ingest_kernel(const __grid_constant__ CUtensorMap map, int stages, int boxes,
-                                                      int iters, int rows_total, long long* out) {
+                                                      int iters, int rows_total, long long* out, int box_mult) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = ptx::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -38,10 +39,10 @@ __global__ void __launch_bounds__(64, 1) ingest_kernel(const __grid_constant__ C
       ptx::mbar_wait(&empty[stage], phase ^ 1u);
       if (ptx::elect_one()) {
         ptx::mbar_expect_tx(&full[stage], (uint32_t)(boxes * kBoxBytes));
-        for (int j = 0; j < boxes; ++j) {
+        for (int j = 0; j < boxes; j += box_mult) {
           ptx::tma_load_4d(smem + ((size_t)stage * boxes + j) * kBoxBytes, &map, &full[stage], 0, row, 0, 0);
-          row += 64;
-          if (row + 64 > rows_total) row = 0;
+          row += 64 * box_mult;
+          if (row + 64 * box_mult > rows_total) row = 0;
         }
       }
       __syncwarp();
@@ -79,9 +80,11 @@ int main() {
   cudaFuncSetAttribute(ingest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
   // {source MB, row pitch in bytes}: pitch 128 = every box is 8 KB contiguous; pitch 640 / 2560 = a 64-channel K block of
   // an NHWC activation with 320 / 1280 channels (128-byte pieces, one per pixel), which is what the implicit GEMM reads
-  const size_t sizes_mb[4] = {32, 4096, 32, 32};
-  const size_t pitches[4] = {128, 128, 640, 2560};
-  for (int si = 0; si < 4; ++si) {
+  const size_t sizes_mb[5] = {32, 4096, 32, 32, 32};
+  const size_t pitches[5] = {128, 128, 640, 2560, 640};
+  const int box_mults[5] = {1, 1, 1, 1, 4};
+  for (int si = 0; si < 5; ++si) {
+    const int box_mult = box_mults[si];
     const size_t bytes = sizes_mb[si] << 20;
     const size_t pitch = pitches[si];
     void* buf;
@@ -91,21 +94,22 @@ int main() {
     CUtensorMap map;
     cuuint64_t gdim[4] = {64, (cuuint64_t)rows_total, 1, 1};
     cuuint64_t gstr[3] = {pitch, (cuuint64_t)rows_total * pitch, (cuuint64_t)rows_total * pitch};
-    cuuint32_t box[4] = {64, 64, 1, 1};
+    cuuint32_t box[4] = {64, (cuuint32_t)(64 * box_mult), 1, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = enc(&map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, buf, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                      CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { printf("encode failed %d\n", (int)r); return 1; }
     printf("source %zu MB (%s), row pitch %zu B: B/clk per SM, all 148 SMs streaming (max cycles over SMs)\n",
            sizes_mb[si], sizes_mb[si] <= 64 ? "L2-resident" : "HBM", pitch);
+    if (box_mult > 1) printf("  (one TMA instruction per %d KB)\n", 8 * box_mult);
     const int cfgs[][2] = {{2, 8}, {4, 4}, {4, 6}, {8, 2}, {8, 3}, {2, 12}, {7, 4}, {3, 8}};  // {boxes per stage, stages}
     for (auto& c : cfgs) {
       const int boxes = c[0], stages = c[1];
       const size_t smem = (size_t)stages * boxes * kBoxBytes + 1024 + 256;
-      if (smem > 227 * 1024) continue;
+      if (smem > 227 * 1024 || boxes % box_mult) continue;
       const int iters = 4000 / boxes;
       for (int rep = 0; rep < 2; ++rep) {
-        ingest_kernel<<<148, 64, smem>>>(map, stages, boxes, iters, rows_total, out);
+        ingest_kernel<<<148, 64, smem>>>(map, stages, boxes, iters, rows_total, out, box_mult);
         if (cudaDeviceSynchronize() != cudaSuccess) { printf("kernel failed: %s\n", cudaGetErrorString(cudaGetLastError())); return 1; }
       }
       long long h[148], mx = 0;
