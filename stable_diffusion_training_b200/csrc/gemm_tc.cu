@@ -30,6 +30,22 @@
 #define SDB_DBG(p, bit) 0
 #endif
 
+// -DSDB_GEMM_TIMELINE: CTA 0 records clock64() per K block (its first 512) at the hand-off points of the operand ring —
+// producer: stage free / TMA issued; issuers: stage landed / MMAs issued (tools/gemm_timeline.py). Off by default.
+#ifdef SDB_GEMM_TIMELINE
+__device__ long long g_gemm_tl[3 * 512 * 2];
+#define SDB_GTL(role, k, slot)                                                              \
+  do {                                                                                      \
+    if (blockIdx.x == 0 && (k) < 512 && (threadIdx.x & 31) == 0)                            \
+      g_gemm_tl[((role) * 512 + (k)) * 2 + (slot)] = clock64();                             \
+  } while (0)
+extern "C" int sdb_gemm_timeline(long long* host_out) {
+  return (int)cudaMemcpyFromSymbol(host_out, g_gemm_tl, sizeof(long long) * 3 * 512 * 2);
+}
+#else
+#define SDB_GTL(role, k, slot) do {} while (0)
+#endif
+
 namespace {
 
 constexpr int kThreads = 224;                // warp 0 TMA, warp 1 MMA issuer (half 0), warps 2-5 epilogue, warp 6 MMA issuer (half 1)
@@ -157,10 +173,12 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     {
       int stage = 0;
       uint32_t phase = 0;
+      int gk = 0;  // K blocks of this CTA so far (timeline index)
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
         const Tile ti = decode_tile(p, t);
-        for (int it = 0; it < ti.num_k; ++it) {
+        for (int it = 0; it < ti.num_k; ++it, ++gk) {
           ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
+          SDB_GTL(0, gk, 0);
           uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
           uint8_t* sb = sa + p.a_stage_bytes;
           if (!ptx::elect_one()) {
@@ -198,6 +216,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
               ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j, pw0, ph0, pn0);
           }
           __syncwarp();
+          SDB_GTL(0, gk, 1);
           if (++stage == p.stages) {
             stage = 0;
             phase ^= 1u;
@@ -212,6 +231,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       int stage = 0;
       uint32_t phase = 0;
       int tile_count = 0;
+      int gk = 0;
       const int a_mn = (MODE == SDB_GEMM_WGRAD) ? 1 : 0;
       const int b_mn = (MODE == SDB_GEMM_WGRAD) ? 1 : p.b_mn;
       const uint32_t a_lbo = a_mn ? kBoxBytes : 0u, a_kadv = a_mn ? 2048u : 32u;
@@ -227,9 +247,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const uint32_t idesc = ptx::umma_idesc_bf16(ti.umma_n, a_mn, b_mn);
         // a WGRAD half whose dW rows all lie past M has nothing to compute (it still takes part in the barriers)
         const bool live = (MODE != SDB_GEMM_WGRAD) || (ti.m_off + half * 128 < p.M);
-        for (int it = 0; it < ti.num_k; ++it) {
+        for (int it = 0; it < ti.num_k; ++it, ++gk) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after();
+          SDB_GTL(1 + half, gk, 0);
           const uint32_t sa = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes) + (uint32_t)half * kAStageBytes;
           const uint32_t sb = ptx::smem_u32(smem + (size_t)stage * p.stage_bytes) + p.a_stage_bytes;
           if (ptx::elect_one()) {
@@ -243,6 +264,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             if (it == ti.num_k - 1) ptx::umma_commit(&tmem_full[acc]);  // accumulator complete -> epilogue
           }
           __syncwarp();
+          SDB_GTL(1 + half, gk, 1);
           if (++stage == p.stages) {
             stage = 0;
             phase ^= 1u;
