@@ -176,6 +176,76 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       int gk = 0;  // K blocks of this CTA so far (timeline index)
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
         const Tile ti = decode_tile(p, t);
+#ifdef SDB_GEMM_FAST_PRODUCER
+        // Candidate for the next round (r3g timeline: one producer iteration costs 500-600 clk — the integer division,
+        // the tap-indexed parameter loads and the box arithmetic sit in front of every TMA — and that, not the MMAs
+        // (320 clk) or the fetch latency (440 clk), paces the 128-row GEMMs of the 16x16 / 8x8 levels). Everything that
+        // depends on the tap or the pixel block is carried incrementally; off by default until validated on a GPU.
+        int f_tap = 0, f_kb = 0, f_cw = 0, f_ch = 0, f_brow = 0, f_iw = 0, f_ih = 0, f_in = 0;
+        const CUtensorMap* f_ma = &p.mapA[0];
+        if (MODE == SDB_GEMM_FWD) {
+          f_tap = ti.kb_begin / p.kblocks;
+          f_kb = ti.kb_begin - f_tap * p.kblocks;
+          f_ma = &p.mapA[p.tap_src[f_tap]];
+          f_cw = ti.w0 + p.tap_dw[f_tap];
+          f_ch = ti.h0 + p.tap_dh[f_tap];
+          f_brow = p.tap_brow[f_tap];
+        } else {
+          f_iw = ti.kb_begin % p.tw;
+          const int r = ti.kb_begin / p.tw;
+          f_ih = r % p.th;
+          f_in = r / p.th;
+          f_ma = &p.mapA[p.tap_src[ti.tap]];
+          f_cw = p.tap_dw[ti.tap];
+          f_ch = p.tap_dh[ti.tap];
+        }
+        const uint32_t f_bytes = p.a_stage_bytes + ((MODE == SDB_GEMM_FWD && !p.b_mn) ? p.b_stage_bytes
+                                                                                        : (uint32_t)ti.nboxes * kBoxBytes);
+        for (int it = 0; it < ti.num_k; ++it, ++gk) {
+          ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
+          SDB_GTL(0, gk, 0);
+          uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
+          uint8_t* sb = sa + p.a_stage_bytes;
+          if (ptx::elect_one()) {
+            ptx::mbar_expect_tx(&full_bar[stage], f_bytes);
+            if (MODE == SDB_GEMM_FWD) {
+              ptx::tma_load_4d(sa, f_ma, &full_bar[stage], f_kb * kBlockK, f_cw, f_ch, ti.n0);
+              if (p.b_mn) {
+                for (int j = 0; j < ti.nboxes; ++j)
+                  ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j,
+                                   f_brow + f_kb * kBlockK, 0, 0);
+              } else {
+                ptx::tma_load_4d(sb, &p.mapB, &full_bar[stage], f_kb * kBlockK, f_brow + ti.n_off, 0, 0);
+              }
+            } else {
+              const int pw0 = f_iw * p.bw, ph0 = f_ih * p.bh, pn0 = f_in * p.bn;
+              for (int i = 0; i < 2 * MT; ++i)
+                ptx::tma_load_4d(sa + i * kBoxBytes, f_ma, &full_bar[stage], ti.m_off + 64 * i, pw0 + f_cw, ph0 + f_ch, pn0);
+              for (int j = 0; j < ti.nboxes; ++j)
+                ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j, pw0, ph0, pn0);
+            }
+          }
+          __syncwarp();
+          SDB_GTL(0, gk, 1);
+          if (MODE == SDB_GEMM_FWD) {
+            if (++f_kb == p.kblocks && it + 1 < ti.num_k) {  // next tap
+              f_kb = 0;
+              ++f_tap;
+              f_ma = &p.mapA[p.tap_src[f_tap]];
+              f_cw = ti.w0 + p.tap_dw[f_tap];
+              f_ch = ti.h0 + p.tap_dh[f_tap];
+              f_brow = p.tap_brow[f_tap];
+            }
+          } else if (++f_iw == p.tw) {  // next pixel block: w fastest, then h, then image
+            f_iw = 0;
+            if (++f_ih == p.th) { f_ih = 0; ++f_in; }
+          }
+          if (++stage == p.stages) {
+            stage = 0;
+            phase ^= 1u;
+          }
+        }
+#else
         for (int it = 0; it < ti.num_k; ++it, ++gk) {
           ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
           SDB_GTL(0, gk, 0);
@@ -222,6 +292,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             phase ^= 1u;
           }
         }
+#endif
       }
     }
   } else if (warp == 1 || warp == 6) {

@@ -117,8 +117,9 @@ def _pick_tile(N: int, pix, b_mn: bool, nkb: int):
     return best
 
 
-_INGEST_B_PER_CLK = 48.0  # bytes per cycle the GEMM main loop moves per SM (r2g / r2f: 46-48 for every tile shape; a
-# property of its 4-deep operand ring, not of the fabric: tools/ingest_rate.cu reaches 110 B/clk without the MMAs)
+_INGEST_B_PER_CLK = 48.0  # empirical: whole-kernel bytes per cycle and SM (r2g / r2f: 46-48 for every tile shape). Not a
+# fabric limit (tools/ingest_rate.cu: 110 B/clk without MMAs): it folds the producer warp's ~600-clk iteration, the exposed
+# epilogue and the launch overhead into one number (profiles/r3g_gemm_timeline.md); refit when those change
 _SPLITK_CACHE: dict = {}
 
 
