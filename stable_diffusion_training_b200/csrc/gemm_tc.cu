@@ -48,7 +48,16 @@ extern "C" int sdb_gemm_timeline(long long* host_out) {
 
 namespace {
 
+// -DSDB_GEMM_EPI2 (candidate, default off): a second set of four epilogue warps (7-10). MT == 2: set e drains half e, which
+// should halve the 5.4 K-cycle tile-boundary gap of profiles/r3g_gemm_timeline.md; MT == 1: the sets alternate 32-column
+// chunks. A first measurement (r2i, before the timeline existed) showed no gain: re-measure with tools/gemm_timeline.py.
+#ifdef SDB_GEMM_EPI2
+constexpr int kThreads = 352;
+constexpr int kEpiSets = 2;
+#else
 constexpr int kThreads = 224;                // warp 0 TMA, warp 1 MMA issuer (half 0), warps 2-5 epilogue, warp 6 MMA issuer (half 1)
+constexpr int kEpiSets = 1;
+#endif
 constexpr int kBlockK = 64;                 // bf16 elements per K block (one 128-byte swizzle row)
 constexpr uint32_t kAStageBytes = 128 * 128;  // 16 KB: 128 rows x 128 B, or two 64-row MN-major boxes
 constexpr uint32_t kBoxBytes = 64 * 128;      // one 64-row box
@@ -154,7 +163,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
     }
     for (int a = 0; a < 2; ++a) {
       ptx::mbar_init(&tmem_full[a], 1);
-      ptx::mbar_init(&tmem_empty[a], 128);
+      ptx::mbar_init(&tmem_empty[a], (kEpiSets == 2 && MT == 1) ? 256 : 128);
     }
     ptx::fence_barrier_init();
   }
@@ -346,10 +355,13 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int eset = (kEpiSets == 2 && warp >= 7) ? 1 : 0;
+    const int c_first = (kEpiSets == 2 && MT == 1) ? eset * 32 : 0, c_step = (kEpiSets == 2 && MT == 1) ? 64 : 32;
+    const int half_lo = (kEpiSets == 2 && MT == 2) ? eset : 0, half_hi = (kEpiSets == 2 && MT == 2) ? eset + 1 : MT;
     int tile_count = 0;
     for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++tile_count) {
       const Tile ti = decode_tile(p, t);
-     for (int half = 0; half < MT; ++half) {
+     for (int half = half_lo; half < half_hi; ++half) {
       const int row = half * 128 + q * 32 + lane;
       const int acc = (MT == 1) ? (tile_count & 1) : half;
       const uint32_t acc_phase = (MT == 1) ? ((uint32_t)(tile_count >> 1) & 1u) : ((uint32_t)tile_count & 1u);
@@ -373,7 +385,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         if (p.splits > 1) {
           // split-K: fp32 partial sums into the (zeroed) [pixels, N] buffer; sdb_splitk_finish adds the rest
           float* acc_out = reinterpret_cast<float*>(p.d) + grow * p.ldd + ti.n_off;
-          for (int c0 = 0; c0 < ti.nw; c0 += 32) {
+          for (int c0 = c_first; c0 < ti.nw; c0 += c_step) {
             uint32_t v[32];
             ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
             ptx::tmem_ld_wait();
@@ -389,7 +401,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             }
           }
         } else
-        for (int c0 = 0; c0 < ti.nw; c0 += 32) {
+        for (int c0 = c_first; c0 < ti.nw; c0 += c_step) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
           // every addend of the chunk is requested BEFORE waiting for the accumulator: the loads may not be hoisted over
@@ -456,7 +468,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const int m = ti.m_off + row;
         const bool valid = (m < p.M) && !SDB_DBG(p, 2);
         float* out = reinterpret_cast<float*>(p.d) + ((long long)p.tap_brow[ti.tap] + m) * p.ldd + ti.n_off;
-        for (int c0 = 0; c0 < ti.nw; c0 += 32) {
+        for (int c0 = c_first; c0 < ti.nw; c0 += c_step) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
           ptx::tmem_ld_wait();
