@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SDB200_ABI_VERSION 3
+#define SDB200_ABI_VERSION 4
 
 #ifndef __CUDA_RUNTIME_H__
 typedef struct CUstream_st* cudaStream_t;
@@ -36,20 +36,29 @@ long long sdb_launch_count(void); /* kernels this library has launched in this p
                                      gpu_launches is the difference across the timed region) */
 
 /* ---- 8-bit Lion (lion_quant.py:20-156, chain 201-211; optax clip/apply as wired at training_utils.py:355-382, 732)
- * One launch over a flat fp32 segment. Block b of 16 consecutive elements has int8 codes[16*b .. 16*b+15] and the
- * RECIPROCAL absmax inv_scales[b] (lion_quant.py:66-80). `gnorm_dev` (nullable) is the global gradient norm: when
- * it is >= max_norm the gradient is divided by it first (optax.clip_by_global_norm).
+ * One launch over a flat fp32 segment. Block b of `block_size` (16, 32 or 64; lion_quant.py:66-80 reshapes to any
+ * block, the reference config uses 16, lion_8bit's default is 64) consecutive elements has int8
+ * codes[bs*b .. bs*b+bs-1] and the RECIPROCAL absmax inv_scales[b]. The scale dtype is fp32
+ * (lion_quant.py:47 canonicalize_dtype(None)); other mu_scale_dtype values are not built. `gnorm_dev` (nullable) is
+ * the global gradient norm: when it is >= max_norm the gradient is divided by it first (optax.clip_by_global_norm).
  * mode 0: out = p + (-lr) * (sign(c) + wd*p)   (out may alias p_in; optax.apply_updates fused)
  * mode 1: out =     (-lr) * (sign(c) + wd*p)   (the optax `updates` tree, parameters untouched)
- * shadow_bf16 (nullable, mode 0 only): bf16 copy of the new parameters for the GEMM operands. */
+ * shadow_bf16 (nullable, mode 0 only): bf16 copy of the new parameters for the GEMM operands.
+ * ema (nullable, mode 0 only): fp32 exponential moving average of the parameters, updated in the same pass with the
+ *   NEW parameters: ema = ema_rate * ema + (1 - ema_rate) * out  (compute_model_ema, training_utils.py:537-544,
+ *   applied at 735-739). */
 int sdb_lion8_update(const float* g, const float* p_in, float* out, void* shadow_bf16, int8_t* codes,
                      float* inv_scales, long long n, int block_size, double b1, double b2, double lr, double wd,
-                     int wd_flag, const float* gnorm_dev, double max_norm, int mode, cudaStream_t stream);
+                     int wd_flag, const float* gnorm_dev, double max_norm, int mode, float* ema, double ema_rate,
+                     cudaStream_t stream);
 
 /* Unquantised-state leaves of the same optimizer (lion_quant.py:109, 145). */
 int sdb_lion_fp32_update(const float* g, const float* p_in, float* out, void* shadow_bf16, float* mu, long long n,
                          double b1, double b2, double lr, double wd, int wd_flag, const float* gnorm_dev,
-                         double max_norm, int mode, cudaStream_t stream);
+                         double max_norm, int mode, float* ema, double ema_rate, cudaStream_t stream);
+
+/* compute_model_ema as a stand-alone leaf op (training_utils.py:537-544): ema = ema_rate * ema + (1 - ema_rate) * p. */
+int sdb_ema_update(float* ema, const float* params, long long n, double ema_rate, cudaStream_t stream);
 
 /* optax.global_norm over a flat fp32 buffer: gnorm_out[0] = sqrt(sum x^2 [+ carried sum if accumulate]).
  * Deterministic (fixed grid, fixed reduction tree). Workspace: sdb_sumsq_workspace_bytes(). */
@@ -62,11 +71,13 @@ int sdb_clip_by_global_norm_f32(const float* g, float* out, long long n, const f
                                 cudaStream_t stream);
 int sdb_add_f32(const float* a, const float* b, float* out, long long n, cudaStream_t stream);
 
-/* ---- schedulers (schedulers/scheduling_utils_flax.py:316-343; scheduling_ddpm_flax.py:196-297) ---- */
+/* ---- schedulers (schedulers/scheduling_utils_flax.py:316-343; scheduling_ddpm_flax.py:196-297) ----
+ * alphas_cumprod has num_timesteps entries; a timestep outside the table is wrapped once if negative and clamped,
+ * as jnp's gather does (it never reads out of bounds). */
 int sdb_add_noise(const float* original_samples, const float* noise, const int* timesteps, const float* alphas_cumprod,
-                  float* noisy, int batch, long long per_sample, cudaStream_t stream);
+                  int num_timesteps, float* noisy, int batch, long long per_sample, cudaStream_t stream);
 int sdb_get_velocity(const float* sample, const float* noise, const int* timesteps, const float* alphas_cumprod,
-                     float* velocity, int batch, long long per_sample, cudaStream_t stream);
+                     int num_timesteps, float* velocity, int batch, long long per_sample, cudaStream_t stream);
 /* prediction_type: 0 epsilon, 1 sample, 2 v_prediction. Scalars are computed by the host in fp32 exactly as the
  * reference does (scheduling_ddpm_flax.py:229-264); noise == NULL means t == 0 (no variance term). */
 int sdb_ddpm_step(const float* model_output, const float* sample, const float* noise, float* prev_sample, long long n,
@@ -77,9 +88,30 @@ int sdb_ddpm_step(const float* model_output, const float* sample, const float* n
  * pred: UNet output NHWC bf16 [B,HW,C]; target: NCHW fp32 [B,C,HW]; sample_weight: nullable fp32 [B].
  * loss[0] = mean(w_b (target-pred)^2); dpred (nullable) = d loss / d pred * loss_grad_scale, NHWC bf16. */
 size_t sdb_mse_workspace_bytes(void);
+/* min_snr_gamma_loss_rescale (training_utils.py:546-568): weight[b] = min(snr, gamma) / snr  (epsilon) or
+ * / (snr + 1) (v_prediction), snr = ac[t_b] / (1 - ac[t_b]); fp32 IEEE division; no host round trip. */
+int sdb_min_snr_weight(const float* alphas_cumprod, int num_timesteps, const int* timesteps, int batch, float gamma,
+                       int v_prediction, float* weight, cudaStream_t stream);
 int sdb_mse_fwd_bwd(const void* pred_nhwc_bf16, const float* target_nchw, const float* sample_weight,
                     void* dpred_nhwc_bf16, float* loss, int B, int C, int HW, float loss_grad_scale, void* workspace,
                     size_t ws_bytes, cudaStream_t stream);
+
+/* ---- in-step sampling (training_utils.py:590-624): jax.random's Threefry-2x32-20 counter-based generator ----
+ * Keys are two uint32 words (jax.random.PRNGKey / split, done on the host: jax_random.py). Arrays are drawn as jax
+ * draws them — element i of threefry_2x32(key, iota(n_total)) — and a caller may ask for the sub-range
+ * [offset, offset + n_local) only (a data-parallel rank's rows of the global batch). Bits and randint are bit-exact
+ * with jax's published algorithm; normal = sqrt(2) * erf_inv(uniform) follows XLA's F32 ErfInv polynomial. */
+int sdb_threefry_bits(uint32_t key0, uint32_t key1, uint32_t* out, long long n_total, long long offset,
+                      long long n_local, cudaStream_t stream);
+/* noise[b,c,p] = N(noise_key) (+ N(offset_key)[b,c] * offset_noise_magnitude) (+ perturbation_noise_magnitude *
+ * N(perturb_key)[b,c,p]) for rows batch_begin .. batch_begin + batch_local - 1 of a [batch_global, channels, hw]
+ * draw; keys are 2-word HOST arrays (offset / perturb keys may be NULL when their magnitude is 0). */
+int sdb_sample_noise(const uint32_t* noise_key_host, const uint32_t* offset_key_host, const uint32_t* perturb_key_host,
+                     float offset_noise_magnitude, float perturbation_noise_magnitude, float* noise_out,
+                     int batch_global, int batch_begin, int batch_local, int channels, int hw, cudaStream_t stream);
+/* jax.random.randint(key, (n_total,), minval, maxval) -> int32, sub-range as above. */
+int sdb_threefry_randint(uint32_t key0, uint32_t key1, int* out, long long n_total, long long offset, long long n_local,
+                         int minval, int maxval, cudaStream_t stream);
 
 /* ---- tensor-core GEMM / implicit-GEMM convolution (tcgen05 + TMEM + TMA) ----
  * Replaces flax nn.Conv / nn.Dense forward and their VJPs inside FlaxUNet2DConditionModel (diffusers 0.21.4,
@@ -207,6 +239,10 @@ int sdb_attn_bwd(const void* q, long long ldq, const void* k, long long ldk, con
  * concatenate, FlaxTimesteps sinusoid, silu(temb), NCHW->NHWC entry transpose [upstream diffusers 0.21.4]) ---- */
 int sdb_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream);
 int sdb_nchw_f32_to_nhwc_bf16(const float* src, void* dst, int B, int C, int HW, cudaStream_t stream);
+int sdb_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int HW, cudaStream_t stream);
+/* += 1 on up to three int32 device counters (NULL = skip): TrainState.step, ScaleBy8bitLionState.count
+ * (lion_quant.py:151), ScaleByScheduleState.count — one launch instead of three framework kernels. */
+int sdb_bump_counters(int* a, int* b, int* c, cudaStream_t stream);
 int sdb_upsample2x_fwd(const void* x, void* y, int B, int H, int W, int C, cudaStream_t stream); /* H,W: input */
 int sdb_upsample2x_bwd(const void* dy, void* dx, int B, int H, int W, int C, cudaStream_t stream);
 int sdb_copy2d_bf16(const void* src, long long lds, void* dst, long long ldd, long long rows, int cols, int accumulate,

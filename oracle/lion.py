@@ -119,6 +119,29 @@ def lion_leaf_update(g, p, state, *, b1=0.9, b2=0.99, lr=1e-6 / 7, wd=0.07, wd_f
     return p + upd, new_state, upd
 
 
+def ema_update(ema: np.ndarray, p: np.ndarray, ema_rate: float) -> np.ndarray:
+    """compute_model_ema (training_utils.py:537-544): `ema_rate * leaf_ema + (1 - ema_rate) * leaf_model` with a python
+    float rate — jnp weak typing rounds `ema_rate` and the python-double `1 - ema_rate` to fp32 once each, then two fp32
+    products and one fp32 sum, individually rounded."""
+    r = np.float32(ema_rate)
+    omr = np.float32(1.0 - float(ema_rate))
+    a = (r * ema.astype(np.float32)).astype(np.float32)
+    b = (omr * p.astype(np.float32)).astype(np.float32)
+    return (a + b).astype(np.float32)
+
+
+def min_snr_weight(alphas_cumprod: np.ndarray, timesteps: np.ndarray, gamma: float, v_prediction: bool) -> np.ndarray:
+    """min_snr_gamma_loss_rescale (training_utils.py:546-568), the per-sample weight: snr = ac / (1 - ac) over the
+    whole table, gather by timestep, min(snr, gamma) / snr  (or / (snr + 1) for v_prediction). fp32."""
+    ac = np.asarray(alphas_cumprod, dtype=np.float32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        snrs = (ac / (np.float32(1) - ac).astype(np.float32)).astype(np.float32)
+        snr = snrs[np.asarray(timesteps).astype(np.int64)]
+        m = np.minimum(snr, np.float32(gamma))
+        w = m / (snr + np.float32(1)).astype(np.float32) if v_prediction else m / snr
+    return w.astype(np.float32)
+
+
 def code_magnitude(a: np.ndarray) -> np.ndarray:
     """|code| as a function of a = |y + offset| >= 0 (monotone non-decreasing)."""
     return np.rint(_pow_fifth_root(a.astype(F32)) * F32(127)).astype(np.int32)

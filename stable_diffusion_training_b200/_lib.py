@@ -42,6 +42,7 @@ _LL = C.c_longlong
 _D = C.c_double
 _F = C.c_float
 _SZ = C.c_size_t
+_U32 = C.c_uint32
 
 # name -> (restype, argtypes). Must list every symbol include/sdb200.h declares (tests/test_abi.py checks it).
 SIGNATURES = {
@@ -49,16 +50,21 @@ SIGNATURES = {
     "sdb_abi_version": (_I, []),
     "sdb_check_device": (_I, [_I]),
     "sdb_launch_count": (_LL, []),
-    "sdb_lion8_update": (_I, [_P, _P, _P, _P, _P, _P, _LL, _I, _D, _D, _D, _D, _I, _P, _D, _I, _P]),
-    "sdb_lion_fp32_update": (_I, [_P, _P, _P, _P, _P, _LL, _D, _D, _D, _D, _I, _P, _D, _I, _P]),
+    "sdb_lion8_update": (_I, [_P, _P, _P, _P, _P, _P, _LL, _I, _D, _D, _D, _D, _I, _P, _D, _I, _P, _D, _P]),
+    "sdb_lion_fp32_update": (_I, [_P, _P, _P, _P, _P, _LL, _D, _D, _D, _D, _I, _P, _D, _I, _P, _D, _P]),
+    "sdb_ema_update": (_I, [_P, _P, _LL, _D, _P]),
     "sdb_sumsq_workspace_bytes": (_SZ, []),
     "sdb_global_norm": (_I, [_P, _LL, _P, _SZ, _P, _I, _P]),
     "sdb_clip_by_global_norm_f32": (_I, [_P, _P, _LL, _P, _D, _P]),
     "sdb_add_f32": (_I, [_P, _P, _P, _LL, _P]),
-    "sdb_add_noise": (_I, [_P, _P, _P, _P, _P, _I, _LL, _P]),
-    "sdb_get_velocity": (_I, [_P, _P, _P, _P, _P, _I, _LL, _P]),
+    "sdb_add_noise": (_I, [_P, _P, _P, _P, _I, _P, _I, _LL, _P]),
+    "sdb_get_velocity": (_I, [_P, _P, _P, _P, _I, _P, _I, _LL, _P]),
     "sdb_ddpm_step": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _F, _I, _I, _P]),
     "sdb_mse_workspace_bytes": (_SZ, []),
+    "sdb_min_snr_weight": (_I, [_P, _I, _P, _I, _F, _I, _P, _P]),
+    "sdb_threefry_bits": (_I, [_U32, _U32, _P, _LL, _LL, _LL, _P]),
+    "sdb_sample_noise": (_I, [_P, _P, _P, _F, _F, _P, _I, _I, _I, _I, _I, _P]),
+    "sdb_threefry_randint": (_I, [_U32, _U32, _P, _LL, _LL, _LL, _I, _I, _P]),
     "sdb_mse_fwd_bwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _SZ, _P]),
     "sdb_gemm_tc": (_I, [C.POINTER(GemmDesc), _P]),
     "sdb_gemm_simt": (_I, [C.POINTER(GemmDesc), _P]),
@@ -80,6 +86,8 @@ SIGNATURES = {
                           _I, _I, _F, _P, _SZ, _P]),
     "sdb_cast_f32_bf16": (_I, [_P, _P, _LL, _P]),
     "sdb_nchw_f32_to_nhwc_bf16": (_I, [_P, _P, _I, _I, _I, _P]),
+    "sdb_nhwc_bf16_to_nchw_f32": (_I, [_P, _P, _I, _I, _I, _P]),
+    "sdb_bump_counters": (_I, [_P, _P, _P, _P]),
     "sdb_upsample2x_fwd": (_I, [_P, _P, _I, _I, _I, _I, _P]),
     "sdb_upsample2x_bwd": (_I, [_P, _P, _I, _I, _I, _I, _P]),
     "sdb_copy2d_bf16": (_I, [_P, _LL, _P, _LL, _LL, _I, _I, _P]),
@@ -125,9 +133,10 @@ def check(rc: int, what: str = "") -> None:
         raise SdbError(f"{what} failed ({rc}): {msg}")
 
 
-def stream_ptr() -> int:
+def stream_ptr(device=None) -> int:
+    """Raw handle of torch's current stream on `device` (default: the current device)."""
     import torch
-    return torch.cuda.current_stream().cuda_stream
+    return torch.cuda.current_stream(device).cuda_stream
 
 
 def ptr(t) -> int:

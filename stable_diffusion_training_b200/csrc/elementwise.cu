@@ -270,6 +270,44 @@ __global__ void timestep_embedding_kernel(const int* __restrict__ t, __nv_bfloat
 
 }  // namespace
 
+// dst NCHW fp32 [B,C,HW] <- src NHWC bf16 [B,HW,C]: the transpose back at the end of FlaxUNet2DConditionModel.__call__
+namespace {
+__global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int B, int C, int HW) {
+  sdb::pdl_trigger();
+  const long long total = (long long)B * C * HW;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {  // i indexes NCHW
+    const int p = (int)(i % HW);
+    const long long bc = i / HW;
+    const int c = (int)(bc % C);
+    const int b = (int)(bc / C);
+    dst[i] = __bfloat162float(src[((long long)b * HW + p) * C + c]);
+  }
+}
+// TrainState.step, ScaleBy8bitLionState.count, ScaleByScheduleState.count: += 1 (flax TrainState.apply_gradients,
+// lion_quant.py:151, optax scale_by_schedule)
+__global__ void bump_counters_kernel(int* a, int* b, int* c) {
+  sdb::pdl_trigger();
+  if (threadIdx.x == 0 && a) *a += 1;
+  if (threadIdx.x == 1 && b) *b += 1;
+  if (threadIdx.x == 2 && c) *c += 1;
+}
+}  // namespace
+
+extern "C" int sdb_nhwc_bf16_to_nchw_f32(const void* src, float* dst, int B, int C, int HW, cudaStream_t stream) {
+  SDB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "sdb_nhwc_bf16_to_nchw_f32: bad shape");
+  nhwc_to_nchw_kernel<<<ew_grid((long long)B * C * HW), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(src),
+                                                                          dst, B, C, HW);
+  SDB_CUDA_LAUNCH_CHECK("sdb_nhwc_bf16_to_nchw_f32");
+  return SDB_OK;
+}
+
+extern "C" int sdb_bump_counters(int* a, int* b, int* c, cudaStream_t stream) {
+  bump_counters_kernel<<<1, 32, 0, stream>>>(a, b, c);
+  SDB_CUDA_LAUNCH_CHECK("sdb_bump_counters");
+  return SDB_OK;
+}
+
 extern "C" int sdb_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream) {
   SDB_CHECK_ARG(n >= 0 && (((uintptr_t)src) & 15) == 0 && (((uintptr_t)dst) & 7) == 0, "sdb_cast_f32_bf16: alignment");
   if (n == 0) return SDB_OK;

@@ -11,17 +11,24 @@
 
 namespace {
 
+// jnp `table[t]`: a negative index wraps once, then the index is clamped into the table (jax gather semantics: an
+// out-of-range timestep never reads outside alphas_cumprod).
+__device__ __forceinline__ int gather_index(int t, int n) {
+  if (t < 0) t += n;
+  return min(max(t, 0), n - 1);
+}
+
 // mode 0: out = a*x0 + s*noise (add_noise); mode 1: out = a*noise - s*x0 (velocity)
 template <int MODE>
 __global__ void __launch_bounds__(256)
 noise_mix_kernel(const float* __restrict__ x0, const float* __restrict__ noise, const int* __restrict__ timesteps,
-                 const float* __restrict__ alphas_cumprod, float* __restrict__ out, int per_sample_vec4,
-                 long long total_vec4) {
+                 const float* __restrict__ alphas_cumprod, int num_timesteps, float* __restrict__ out,
+                 int per_sample_vec4, long long total_vec4) {
   sdb::pdl_trigger();
   const long long stride = (long long)gridDim.x * blockDim.x;
   for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < total_vec4; v += stride) {
     const int b = (int)(v / per_sample_vec4);
-    const float ac = __ldg(alphas_cumprod + __ldg(timesteps + b));
+    const float ac = __ldg(alphas_cumprod + gather_index(__ldg(timesteps + b), num_timesteps));
     const float a = __fsqrt_rn(ac);
     const float s = __fsqrt_rn(__fsub_rn(1.0f, ac));
     const float4 x = sdb::ld_f4(x0 + 4 * v);
@@ -125,33 +132,60 @@ int grid_cap(long long work, int threads, int per_sm) {
 
 }  // namespace
 
-static int noise_mix(int mode, const float* x0, const float* noise, const int* timesteps, const float* ac, float* out,
-                     int batch, long long per_sample, cudaStream_t stream, const char* name) {
+static int noise_mix(int mode, const float* x0, const float* noise, const int* timesteps, const float* ac,
+                     int num_timesteps, float* out, int batch, long long per_sample, cudaStream_t stream,
+                     const char* name) {
+  SDB_CHECK_ARG(num_timesteps > 0, "%s: num_timesteps must be positive", name);
   SDB_CHECK_ARG(batch > 0 && per_sample > 0 && per_sample % 4 == 0, "%s: per-sample size (%lld) must be a multiple of 4",
                 name, per_sample);
   SDB_CHECK_ARG((((uintptr_t)x0 | (uintptr_t)noise | (uintptr_t)out) & 15) == 0, "%s: 16-byte alignment required", name);
   const long long total_vec4 = (long long)batch * per_sample / 4;
   const int grid = grid_cap(total_vec4, 256, 8);
   if (mode == 0)
-    noise_mix_kernel<0><<<grid, 256, 0, stream>>>(x0, noise, timesteps, ac, out, (int)(per_sample / 4), total_vec4);
+    noise_mix_kernel<0><<<grid, 256, 0, stream>>>(x0, noise, timesteps, ac, num_timesteps, out, (int)(per_sample / 4), total_vec4);
   else
-    noise_mix_kernel<1><<<grid, 256, 0, stream>>>(x0, noise, timesteps, ac, out, (int)(per_sample / 4), total_vec4);
+    noise_mix_kernel<1><<<grid, 256, 0, stream>>>(x0, noise, timesteps, ac, num_timesteps, out, (int)(per_sample / 4), total_vec4);
   SDB_CUDA_LAUNCH_CHECK(name);
   return SDB_OK;
 }
 
 extern "C" int sdb_add_noise(const float* original_samples, const float* noise, const int* timesteps,
-                             const float* alphas_cumprod, float* noisy, int batch, long long per_sample,
-                             cudaStream_t stream) {
-  return noise_mix(0, original_samples, noise, timesteps, alphas_cumprod, noisy, batch, per_sample, stream,
-                   "sdb_add_noise");
+                             const float* alphas_cumprod, int num_timesteps, float* noisy, int batch,
+                             long long per_sample, cudaStream_t stream) {
+  return noise_mix(0, original_samples, noise, timesteps, alphas_cumprod, num_timesteps, noisy, batch, per_sample,
+                   stream, "sdb_add_noise");
 }
 
 extern "C" int sdb_get_velocity(const float* sample, const float* noise, const int* timesteps,
-                                const float* alphas_cumprod, float* velocity, int batch, long long per_sample,
-                                cudaStream_t stream) {
-  return noise_mix(1, sample, noise, timesteps, alphas_cumprod, velocity, batch, per_sample, stream,
+                                const float* alphas_cumprod, int num_timesteps, float* velocity, int batch,
+                                long long per_sample, cudaStream_t stream) {
+  return noise_mix(1, sample, noise, timesteps, alphas_cumprod, num_timesteps, velocity, batch, per_sample, stream,
                    "sdb_get_velocity");
+}
+
+// min_snr_gamma_loss_rescale (training_utils.py:546-568): snr = ac / (1 - ac); w = min(snr, gamma) / snr
+// (epsilon) or / (snr + 1) (v_prediction). fp32, IEEE division, one weight per sample; stays on the device.
+namespace {
+__global__ void min_snr_weight_kernel(const float* __restrict__ alphas_cumprod, int num_timesteps,
+                                      const int* __restrict__ timesteps, int batch, float gamma, int v_pred,
+                                      float* __restrict__ weight) {
+  sdb::pdl_trigger();
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  const float ac = alphas_cumprod[gather_index(timesteps[b], num_timesteps)];
+  const float snr = __fdiv_rn(ac, __fsub_rn(1.0f, ac));
+  const float m = fminf(snr, gamma);
+  weight[b] = v_pred ? __fdiv_rn(m, __fadd_rn(snr, 1.0f)) : __fdiv_rn(m, snr);
+}
+}  // namespace
+
+extern "C" int sdb_min_snr_weight(const float* alphas_cumprod, int num_timesteps, const int* timesteps, int batch,
+                                  float gamma, int v_prediction, float* weight, cudaStream_t stream) {
+  SDB_CHECK_ARG(batch > 0 && num_timesteps > 0, "sdb_min_snr_weight: bad sizes");
+  min_snr_weight_kernel<<<(batch + 127) / 128, 128, 0, stream>>>(alphas_cumprod, num_timesteps, timesteps, batch, gamma,
+                                                                v_prediction, weight);
+  SDB_CUDA_LAUNCH_CHECK("sdb_min_snr_weight");
+  return SDB_OK;
 }
 
 extern "C" int sdb_ddpm_step(const float* model_output, const float* sample, const float* noise, float* prev_sample,

@@ -122,11 +122,23 @@ def _lion_leaf(g, p, m, *, b1, b2, lr, wd, wd_flag, gnorm, max_norm, mode, out, 
         codes, inv = m
         _lib.check(l.sdb_lion8_update(g.data_ptr(), p.data_ptr(), out.data_ptr(), _lib.ptr(shadow), codes.data_ptr(),
                                       inv.data_ptr(), n, block_size, b1, b2, lr, wd, int(wd_flag), _gn_ptr(gnorm),
-                                      max_norm, mode, _lib.stream_ptr()), "sdb_lion8_update")
+                                      max_norm, mode, 0, 0.0, _lib.stream_ptr()), "sdb_lion8_update")
     else:
         _lib.check(l.sdb_lion_fp32_update(g.data_ptr(), p.data_ptr(), out.data_ptr(), _lib.ptr(shadow), m.data_ptr(), n,
-                                          b1, b2, lr, wd, int(wd_flag), _gn_ptr(gnorm), max_norm, mode,
+                                          b1, b2, lr, wd, int(wd_flag), _gn_ptr(gnorm), max_norm, mode, 0, 0.0,
                                           _lib.stream_ptr()), "sdb_lion_fp32_update")
+
+
+def compute_model_ema(ema_params, update_params, ema_rate: float):
+    """training_utils.py:537-544: ema <- ema_rate * ema + (1 - ema_rate) * params, leaf by leaf, IN PLACE on the EMA
+    tree (the reference's jit donates it). train_step itself fuses this into the optimizer launch."""
+    l = _lib.lib()
+
+    def leaf(e, p):
+        _lib.check(l.sdb_ema_update(e.data_ptr(), p.data_ptr(), e.numel(), float(ema_rate), _lib.stream_ptr()),
+                   "sdb_ema_update")
+        return e
+    return tree_map(leaf, ema_params, update_params)
 
 
 def scale_by_lion_8bit(b1: float = 0.9, b2: float = 0.99, mu_scale_dtype: Optional[Any] = None,
@@ -137,6 +149,8 @@ def scale_by_lion_8bit(b1: float = 0.9, b2: float = 0.99, mu_scale_dtype: Option
     (the reference's jit donates it, training_utils.py:846-851)."""
     if mu_scale_dtype not in (None, torch.float32, "float32", "fp32"):
         raise NotImplementedError("mu_scale_dtype: only float32 (the reference's canonicalize_dtype(None)) is built")
+    if block_size not in (16, 32, 64):
+        raise NotImplementedError(f"block_size {block_size}: the kernels are built for 16, 32 and 64")
 
     def init_fn(params):
         flags = _expand_mask(excluded_layer_mask, params)

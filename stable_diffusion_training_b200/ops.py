@@ -472,12 +472,26 @@ class side_workspace:
         return False
 
 
+_WS_RETIRED: list = []
+_WS_FROZEN = False
+
+
+def freeze_workspaces() -> None:
+    """Called before the first CUDA-graph capture: graphs bake the scratch pointers into their kernel nodes, so from
+    here on a workspace that has to grow keeps its predecessor alive (never freed, never handed to another tensor)."""
+    global _WS_FROZEN
+    _WS_FROZEN = True
+
+
 def workspace(device, nbytes: int = 64 << 20) -> torch.Tensor:
     """One stream-ordered scratch buffer per device and stream role (partials of reductions; every op finishes with it
-    in-stream)."""
+    in-stream). Growth after a graph capture retires the old buffer instead of freeing it (captured graphs of other
+    batch shapes still write to it)."""
     key = (device.type, device.index, _WS_TAG)
     ws = _WS.get(key)
     if ws is None or ws.numel() < nbytes:
+        if ws is not None and _WS_FROZEN:
+            _WS_RETIRED.append(ws)
         ws = torch.empty(max(nbytes, 64 << 20), dtype=torch.uint8, device=device)
         _WS[key] = ws
     return ws

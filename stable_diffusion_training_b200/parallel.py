@@ -58,6 +58,7 @@ class GradReducer:
         self.grad = grad_flat
         self.group = group
         self.world_size = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.buckets = build_buckets(ranges, max(1, bucket_bytes // grad_flat.element_size()))
         if total_elems is not None and self.buckets:  # trailing padding of the arena belongs to the last bucket
             s, e, names = self.buckets[-1]
@@ -198,10 +199,41 @@ def _replay_finish(red: GradReducer, buckets: Sequence[int], loss: torch.Tensor)
 GradReducer.replay_finish = _replay_finish
 
 
-def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES) -> GradReducer:
-    """Give a TrainState its data-parallel reducer (train_step then shards nothing itself: each rank is handed its own
-    slice of the global batch, as the reference's PartitionSpec("data_parallel", None) does)."""
+def _replicate_state(state, group, sync: str) -> None:
+    """The reference replicates parameters and optimizer state from ONE host copy (jax.device_put with
+    PartitionSpec(), training_utils.py:446-483). Here every rank builds its own state, so attach() makes that true:
+    sync="broadcast" copies rank 0's masters / Lion codes / scales / fp32 momentum / EMA to every rank;
+    sync="verify" only compares checksums and raises on a mismatch; sync="none" trusts the caller."""
+    if sync == "none" or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
     a = state.arena
+    bufs = [a.master, a.codes, a.inv_scales, a.mu] + ([a.ema] if a.ema is not None else [])
+    if sync == "broadcast":
+        for t in bufs:
+            dist.broadcast(t, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        a.refresh_shadow()
+        return
+    if sync != "verify":
+        raise ValueError(f"parallel.attach: sync must be 'broadcast', 'verify' or 'none', got {sync!r}")
+    sums = torch.stack([t.view(torch.uint8).to(torch.int64).sum() if t.dtype == torch.int8 else
+                        t.view(torch.int32).to(torch.int64).sum() for t in bufs])
+    lo, hi = sums.clone(), sums.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    if not torch.equal(lo, hi):
+        raise RuntimeError("parallel.attach: parameters / optimizer state differ between ranks "
+                           "(use sync='broadcast' or load identical states)")
+
+
+def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, sync: str = "broadcast") -> GradReducer:
+    """Give a TrainState its data-parallel reducer (train_step then shards nothing itself: each rank is handed its own
+    slice of the global batch, as the reference's PartitionSpec("data_parallel", None) does). `sync` makes the
+    replicated-state contract hold at attach time (see _replicate_state)."""
+    a = state.arena
+    if a.device.type == "cuda" and torch.cuda.current_device() != a.device.index:
+        raise RuntimeError(f"parallel.attach: the state lives on {a.device}, the current device is "
+                           f"cuda:{torch.cuda.current_device()} (call torch.cuda.set_device(local_rank) first)")
+    _replicate_state(state, group, sync)
     ranges = {}
     for n, shape in a.shapes.items():
         numel = 1

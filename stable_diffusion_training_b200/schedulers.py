@@ -118,14 +118,34 @@ class FlaxDDPMSchedulerOutput(FlaxSchedulerOutput):
     state: DDPMSchedulerState
 
 
+def _as_f32(t: torch.Tensor, device, what: str) -> torch.Tensor:
+    """The kernels read fp32: bf16 / fp16 / fp64 inputs (the reference's VAE runs in bf16, training_utils.py:209-222)
+    are promoted like jnp would promote them against the fp32 schedule; anything on another device is an error."""
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{what}: expected a torch tensor, got {type(t).__name__}")
+    if t.device != device:
+        raise ValueError(f"{what}: tensor is on {t.device}, the scheduler state on {device}")
+    if not t.dtype.is_floating_point:
+        raise TypeError(f"{what}: expected a floating-point tensor, got {t.dtype}")
+    return t.to(torch.float32).contiguous()
+
+
 def _noise_mix(fn_name, state: CommonSchedulerState, a, noise, timesteps):
     l = _lib.lib()
-    a = a.contiguous()
-    noise = noise.contiguous()
-    t = timesteps.to(torch.int32).contiguous()
-    out = torch.empty_like(a)
+    ac = state.alphas_cumprod
+    a = _as_f32(a, ac.device, fn_name)
+    noise = _as_f32(noise, ac.device, fn_name)
+    if noise.shape != a.shape:
+        raise ValueError(f"{fn_name}: sample {tuple(a.shape)} and noise {tuple(noise.shape)} shapes differ")
+    if timesteps.device != ac.device:
+        raise ValueError(f"{fn_name}: timesteps are on {timesteps.device}, the scheduler state on {ac.device}")
+    t = timesteps.to(torch.int32).contiguous().view(-1)
     B = a.shape[0]
-    _lib.check(getattr(l, fn_name)(a.data_ptr(), noise.data_ptr(), t.data_ptr(), state.alphas_cumprod.data_ptr(),
+    if t.numel() != B:
+        raise ValueError(f"{fn_name}: {t.numel()} timesteps for a batch of {B}")
+    out = torch.empty_like(a)
+    # out-of-range timesteps are wrapped / clamped inside the kernel like jnp's gather (never read out of bounds)
+    _lib.check(getattr(l, fn_name)(a.data_ptr(), noise.data_ptr(), t.data_ptr(), ac.data_ptr(), ac.numel(),
                                    out.data_ptr(), B, a.numel() // B, _lib.stream_ptr()), fn_name)
     return out
 

@@ -7,10 +7,14 @@
   create_lion_optimizer    the optax chain of training_utils.py:355-382: clip_by_global_norm(1) -> lion_8bit(lr/7, .9,
                            .99, wd*7, block 16, masks)
   train_step(state, batch, rng) -> (state, metrics)
-                           training_utils.py:504-762 restricted to the UNet (north-star surface): add_noise, UNet
-                           forward, epsilon / v target, MSE (+ min-SNR-gamma), backward, [data-parallel gradient mean],
-                           clip + 8-bit Lion + apply, step + 1. The state is DONATED (updated in place), as the
-                           reference's jit does (training_utils.py:846-851); the loss stays on the device.
+                           training_utils.py:504-762 restricted to the UNet (north-star surface): key split + noise /
+                           timestep sampling with jax's Threefry generator (530, 590-624; offset / perturbation noise),
+                           add_noise, UNet forward, epsilon / v target, MSE (+ min-SNR-gamma, weights computed on the
+                           device), backward, [data-parallel gradient mean], clip + 8-bit Lion + apply (+ EMA of the
+                           new parameters fused into the same launches, 537-544 / 735-739), step + 1. The state and the
+                           EMA tree are DONATED (updated in place), as the reference's jit does
+                           (training_utils.py:846-851); the loss stays on the device; `return_rng=True` appends
+                           `new_train_rng` to the result like the reference's tuple (755-762).
 
 Parameters, gradients, bf16 GEMM operands and optimizer state live in flat arenas so that the optimizer is three kernel
 launches and the gradient all-reduce runs over contiguous buckets; `state.params` / `state.opt_state` are zero-copy
@@ -26,6 +30,7 @@ import numpy as np
 import torch
 
 from . import _lib, ops
+from . import jax_random as JR
 from . import lion_quant as LQ
 from .lion_quant import create_mask, flatten_dict, unflatten_dict
 from .schedulers import FlaxDDPMScheduler
@@ -55,6 +60,8 @@ class TrainingConfig:
     offset_noise_magnitude: float = 0.0
     min_snr_gamma_magnitude: float = 0.0
     perturbation_noise_magnitude: float = 0.0
+    accumulate_unet_ema: bool = False   # model_properties_example.json:38
+    ema_rate: float = 0.0               # model_properties_example.json:40 uses 0.99998
 
 
 def create_lion_optimizer(params: dict, cfg: TrainingConfig = TrainingConfig()) -> LQ.GradientTransformation:
@@ -76,14 +83,14 @@ class ParamArena:
 
     Leaves are grouped in four segments by (quantised state?, weight decay?) and, inside a segment, ordered as the
     backward pass produces their gradients, so that gradient buckets complete front to back. Every leaf starts on a
-    16-element boundary; padding stays zero forever (zero gradient -> zero update)."""
-
-    ALIGN = 16
+    boundary of max(16, block_size) elements (quantisation blocks never straddle leaves); padding stays zero forever
+    (zero gradient -> zero update)."""
 
     def __init__(self, shapes: Dict[str, tuple], quant: Dict[str, bool], decay: Dict[str, bool], order: List[str],
                  device, block_size: int = 16):
         self.device = torch.device(device)
         self.block_size = block_size
+        self.ALIGN = max(16, int(block_size))
         self.shapes = dict(shapes)
         rank = {n: i for i, n in enumerate(order)}
         names = sorted(shapes, key=lambda n: rank.get(n, len(rank)))
@@ -120,6 +127,16 @@ class ParamArena:
         l = _lib.lib()
         self.norm_ws = torch.empty(l.sdb_sumsq_workspace_bytes(), dtype=torch.uint8, device=dev)
         self.gnorm = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.ema: Optional[torch.Tensor] = None   # flat fp32 EMA of the masters (create_ema)
+        self.e: Dict[str, torch.Tensor] = {}
+
+    def create_ema(self) -> Dict[str, torch.Tensor]:
+        """EMA copy of the parameters (training_utils.py:466-483 copies the loaded params) as one flat buffer with the
+        arena's layout, so the moving average rides in the optimizer launches."""
+        if self.ema is None:
+            self.ema = self.master.clone()
+            self.e = {n: self._view(self.ema, n) for n in self.shapes}
+        return self.e
 
     def _view(self, flat, name):
         o = self.offset[name]
@@ -147,10 +164,13 @@ class ParamArena:
                 out[n] = self.mu[o - self.n_quant:o - self.n_quant + numel].view(shape)
         return unflatten_dict(out)
 
-    def optimizer_step(self, *, lr: float, b1: float, b2: float, wd: float, max_norm: Optional[float]) -> None:
-        """clip_by_global_norm -> lion_8bit -> apply_updates over the whole arena (+ bf16 operand refresh)."""
+    def optimizer_step(self, *, lr: float, b1: float, b2: float, wd: float, max_norm: Optional[float],
+                       ema_rate: float = 0.0) -> None:
+        """clip_by_global_norm -> lion_8bit -> apply_updates over the whole arena (+ bf16 operand refresh, + the EMA of
+        the new parameters when `ema_rate` is set and create_ema() was called)."""
         l = _lib.lib()
-        st = _lib.stream_ptr()
+        st = _lib.stream_ptr(self.device)
+        ema0 = self.ema.data_ptr() if (ema_rate and self.ema is not None) else 0
         gn = 0
         if max_norm is not None:
             _lib.check(l.sdb_global_norm(self.grad.data_ptr(), self.n_total, self.norm_ws.data_ptr(),
@@ -160,15 +180,17 @@ class ParamArena:
         for q, wdf, s, e in self.segments:
             n = e - s
             g, p, sh = self.grad.data_ptr() + s * es4, self.master.data_ptr() + s * es4, self.shadow.data_ptr() + s * es2
+            em = ema0 + s * es4 if ema0 else 0
             if q:
                 _lib.check(l.sdb_lion8_update(g, p, p, sh, self.codes.data_ptr() + s,
                                               self.inv_scales.data_ptr() + (s // self.block_size) * 4, n,
                                               self.block_size, b1, b2, lr, wd, int(wdf), gn,
-                                              1.0 if max_norm is None else max_norm, 0, st), "sdb_lion8_update")
+                                              1.0 if max_norm is None else max_norm, 0, em, float(ema_rate), st),
+                           "sdb_lion8_update")
             else:
                 _lib.check(l.sdb_lion_fp32_update(g, p, p, sh, self.mu.data_ptr() + (s - self.n_quant) * 4, n, b1, b2,
-                                                  lr, wd, int(wdf), gn, 1.0 if max_norm is None else max_norm, 0, st),
-                           "sdb_lion_fp32_update")
+                                                  lr, wd, int(wdf), gn, 1.0 if max_norm is None else max_norm, 0,
+                                                  em, float(ema_rate), st), "sdb_lion_fp32_update")
 
 
 def backward_param_order(cfg: UNetConfig) -> List[str]:
@@ -210,7 +232,10 @@ class UNetModel:
         ctx = ops.cast_bf16(encoder_hidden_states.to(torch.float32).contiguous())
         pred = st.net.forward(x, timesteps.to(torch.int32), ctx)
         st.net.graph = None
-        out = pred.v.view(B, H, W, -1).permute(0, 3, 1, 2).float()  # layout change of the result only
+        Co = pred.v.shape[-1]
+        out = torch.empty((B, Co, H, W), dtype=torch.float32, device=pred.v.device)
+        _lib.check(_lib.lib().sdb_nhwc_bf16_to_nchw_f32(pred.v.data_ptr(), out.data_ptr(), B, Co, H * W,
+                                                        _lib.stream_ptr(out.device)), "sdb_nhwc_bf16_to_nchw_f32")
         from types import SimpleNamespace
         return SimpleNamespace(sample=out)
 
@@ -229,6 +254,15 @@ class TrainState:
         self.hyper = hyper
         self.dp = None  # data-parallel reducer (parallel.GradReducer), attached by parallel.attach()
         self._host_step = 0
+        self.ema_params: Optional[dict] = None
+
+    def create_ema(self) -> dict:
+        """unet_ema_params: a copy of the parameters to be averaged (training_utils.py:466-483), laid out like the
+        arena so that train_step(..., unet_ema_params=<this tree>, ema_rate=r) fuses the average into the optimizer
+        launches. Returns the tree (views)."""
+        if self.ema_params is None:
+            self.ema_params = unflatten_dict(self.arena.create_ema())
+        return self.ema_params
 
     @classmethod
     def create(cls, *, apply_fn, params: dict, tx: LQ.GradientTransformation, device="cuda",
@@ -263,9 +297,10 @@ class TrainState:
         model._state = st
         return st
 
-    def apply_gradients(self, *, grads: Optional[dict] = None) -> "TrainState":
+    def apply_gradients(self, *, grads: Optional[dict] = None, ema_rate: float = 0.0) -> "TrainState":
         """tx.update + optax.apply_updates + step+1, in place (the state is donated). `grads=None` or the state's own
-        gradient tree uses the gradients already in the arena (what train_step produces)."""
+        gradient tree uses the gradients already in the arena (what train_step produces). `ema_rate` (with
+        create_ema()) also updates the EMA tree from the new parameters in the same launches."""
         a = self.arena
         if grads is not None and grads is not getattr(self, "_grad_tree", None):
             for n, g in flatten_dict(grads).items():
@@ -277,10 +312,11 @@ class TrainState:
         if callable(lr):
             lr = lr(self._host_step)  # host mirror of ScaleByScheduleState.count: no device sync per step
         self._host_step += 1
-        a.optimizer_step(lr=float(lr), b1=h["b1"], b2=h["b2"], wd=h["weight_decay"], max_norm=h["max_norm"])
-        lion.lion.count.add_(1)
-        lion.schedule.count.add_(1)
-        self.step.add_(1)
+        a.optimizer_step(lr=float(lr), b1=h["b1"], b2=h["b2"], wd=h["weight_decay"], max_norm=h["max_norm"],
+                         ema_rate=ema_rate)
+        _lib.check(_lib.lib().sdb_bump_counters(self.step.data_ptr(), lion.lion.count.data_ptr(),
+                                                lion.schedule.count.data_ptr(), _lib.stream_ptr(a.device)),
+                   "sdb_bump_counters")
         return self
 
     @property
@@ -305,8 +341,9 @@ def _parse_chain(h: dict) -> dict:
     if lion is None:
         raise NotImplementedError("TrainState: the optimizer chain must contain lion_8bit")
     out.update(lion)
-    if out["block_size"] != 16:
-        raise NotImplementedError("the fused optimizer path is built for block_size 16 (model_properties_example.json:41)")
+    if out["block_size"] not in (16, 32, 64):
+        raise NotImplementedError("the optimizer kernels are built for block_size 16 (model_properties_example.json:41), "
+                                  "32 and 64 (lion_8bit's default)")
     return out
 
 
@@ -314,21 +351,60 @@ def _parse_chain(h: dict) -> dict:
 _KEY = {}
 
 
-def _generator(rng, device):
-    if isinstance(rng, torch.Generator):
-        return rng
-    g = torch.Generator(device=device)
-    g.manual_seed(int(rng) if rng is not None else 0)
-    return g
+def _dp_rows(state: "TrainState", B: int) -> Tuple[int, int]:
+    """(global batch rows, first row of this rank): the reference draws noise / timesteps for the GLOBAL batch and
+    shards it on dim 0 (training_utils.py:835-840); rank r owns rows [r*B, (r+1)*B)."""
+    dp = state.dp
+    if dp is None or dp.world_size == 1:
+        return B, 0
+    return B * dp.world_size, B * dp.rank
 
 
-def train_step(state: TrainState, batch: dict, rng, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
-               offset_noise_magnitude: float = 0.0, min_snr_gamma_magnitude: float = 0.0,
-               perturbation_noise_magnitude: float = 0.0):
-    """One denoising train step (training_utils.py:504-762, UNet part). batch: {"latents" f32 [B,4,H,W],
-    "encoder_hidden_states" [B,L,D], optional "noise" f32 [B,4,H,W], "timesteps" int [B]} (device tensors).
-    Returns (state, {"loss": 0-d device tensor}); `rng` (a torch.Generator or seed) is consumed for whatever the batch
-    does not supply. Raises ValueError for an unknown prediction type (training_utils.py:697-701)."""
+def draw_noise_and_timesteps(state: "TrainState", shape, rng, num_train_timesteps: int, *, need_noise: bool,
+                             need_timesteps: bool, offset_noise_magnitude: float = 0.0,
+                             perturbation_noise_magnitude: float = 0.0, noise_out=None, timesteps_out=None):
+    """training_utils.py:530, 590-624 on the device: returns (noise | None, timesteps | None, new_train_rng).
+    `rng` is the step's `train_rng` (a key, an int seed or a jax_random.RngStream, which is advanced in place)."""
+    keys = JR.train_step_keys(rng)
+    dev = state.arena.device
+    B = int(shape[0])
+    Bg, b0 = _dp_rows(state, B)
+    noise = timesteps = None
+    if need_noise:
+        noise = JR.sample_noise(keys["noise"], shape, dev, offset_key=keys["offset"],
+                                offset_noise_magnitude=offset_noise_magnitude, perturb_key=keys["perturb"],
+                                perturbation_noise_magnitude=perturbation_noise_magnitude, batch_global=Bg,
+                                batch_begin=b0, out=noise_out)
+    if need_timesteps:
+        timesteps = JR.randint(keys["timestep"], B, 0, num_train_timesteps, dev, n_global=Bg, begin=b0,
+                               out=timesteps_out)
+    if isinstance(rng, JR.RngStream):
+        rng.key = keys["new_train"]
+    return noise, timesteps, keys["new_train"]
+
+
+def _check_rng(rng, return_rng: bool, what: str) -> None:
+    if rng is None:
+        raise ValueError(f"{what}: the batch has no 'noise' / 'timesteps', so a train_rng is needed (a jax_random key, "
+                         "an int seed or a jax_random.RngStream)")
+    if not isinstance(rng, JR.RngStream) and not return_rng:
+        raise ValueError(f"{what}: sampling from a raw key without return_rng=True would draw the same noise and "
+                         "timesteps every step; pass return_rng=True and feed new_train_rng back "
+                         "(training_utils.py:530, 755-762) or pass a jax_random.RngStream")
+
+
+def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
+               unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
+               min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0, ema_rate: float = 0.0,
+               return_rng: bool = False):
+    """One denoising train step (training_utils.py:504-762, UNet part). batch: {"latents" [B,4,H,W],
+    "encoder_hidden_states" [B,L,D], optional "noise" [B,4,H,W], "timesteps" int [B]} (device tensors; floating
+    inputs of any width are promoted to fp32 like jnp would). Whatever the batch does not supply is drawn from `rng`
+    exactly as the reference draws it (split(train_rng, 3) / split(sample_rng, 4), jax.random.normal / randint; offset
+    and perturbation noise apply to drawn noise only, as in the reference).
+    Returns (state, {"loss": 0-d device tensor}) and, with return_rng=True, new_train_rng as third element. `state`
+    and `unet_ema_params` (state.create_ema(); updated when ema_rate != 0, training_utils.py:735-739) are donated.
+    Raises ValueError for an unknown prediction type (training_utils.py:697-701)."""
     if frozen_noise_scheduler_state is None:
         frozen_noise_scheduler_state = default_scheduler(state.arena.device)
     sched: FlaxDDPMScheduler = frozen_noise_scheduler_state.call
@@ -336,30 +412,41 @@ def train_step(state: TrainState, batch: dict, rng, frozen_noise_scheduler_state
     ptype = sched.config.prediction_type
     if ptype not in ("epsilon", "v_prediction"):
         raise ValueError(f"Unknown prediction type {ptype}")
+    dev = state.arena.device
+    if torch.cuda.current_device() != dev.index:
+        raise RuntimeError(f"train_step: the state lives on {dev} but the current CUDA device is "
+                           f"cuda:{torch.cuda.current_device()} (call torch.cuda.set_device first)")
     lat = batch["latents"]
-    dev = lat.device
+    if lat.device != dev:
+        raise ValueError(f"train_step: batch['latents'] is on {lat.device}, the state on {dev}")
+    if lat.dtype != torch.float32 or not lat.is_contiguous():
+        lat = lat.to(torch.float32).contiguous()
     B = lat.shape[0]
-    gen = None
     noise = batch.get("noise")
-    if noise is None:
-        gen = _generator(rng, dev)
-        noise = torch.randn(lat.shape, generator=gen, device=dev, dtype=torch.float32)
-        if offset_noise_magnitude:
-            noise = noise + torch.randn((B, lat.shape[1], 1, 1), generator=gen, device=dev) * offset_noise_magnitude
-        if perturbation_noise_magnitude:
-            noise = noise + perturbation_noise_magnitude * torch.randn(lat.shape, generator=gen, device=dev)
     timesteps = batch.get("timesteps")
-    if timesteps is None:
-        gen = gen or _generator(rng, dev)
-        timesteps = torch.randint(0, sched.config.num_train_timesteps, (B,), generator=gen, device=dev)
+    new_rng = None
+    if noise is None or timesteps is None:
+        _check_rng(rng, return_rng, "train_step")
+        n_, t_, new_rng = draw_noise_and_timesteps(
+            state, lat.shape, rng, sched.config.num_train_timesteps, need_noise=noise is None,
+            need_timesteps=timesteps is None, offset_noise_magnitude=offset_noise_magnitude,
+            perturbation_noise_magnitude=perturbation_noise_magnitude)
+        noise = n_ if noise is None else noise
+        timesteps = t_ if timesteps is None else timesteps
+    elif return_rng and rng is not None:
+        new_rng = JR.train_step_keys(rng)["new_train"]  # the key still advances (training_utils.py:530)
+        if isinstance(rng, JR.RngStream):
+            rng.key = new_rng
+    if noise.dtype != torch.float32 or not noise.is_contiguous():
+        noise = noise.to(torch.float32).contiguous()
     timesteps = timesteps.to(torch.int32)
 
     noisy = sched.add_noise(sstate, lat, noise, timesteps)
     target = noise if ptype == "epsilon" else sched.get_velocity(sstate, lat, noise, timesteps)
     weight = None
     if min_snr_gamma_magnitude:
-        weight = _min_snr_weight(sstate.common.alphas_cumprod, timesteps, float(min_snr_gamma_magnitude),
-                                 ptype == "v_prediction")
+        weight = min_snr_weight(sstate.common.alphas_cumprod, timesteps, float(min_snr_gamma_magnitude),
+                                ptype == "v_prediction")
     x = ops.nchw_to_nhwc_bf16(noisy)
     ctx = batch["encoder_hidden_states"]
     if ctx.dtype != torch.bfloat16:
@@ -375,8 +462,24 @@ def train_step(state: TrainState, batch: dict, rng, frozen_noise_scheduler_state
     net.backward(pred, dpred, on_grad)
     if state.dp is not None:
         loss = state.dp.finish(loss)
-    state.apply_gradients(grads=None)
-    return state, {"loss": loss}
+    fused_ema = bool(ema_rate) and unet_ema_params is not None and unet_ema_params is state.ema_params
+    state.apply_gradients(grads=None, ema_rate=float(ema_rate) if fused_ema else 0.0)
+    if ema_rate and unet_ema_params is not None and not fused_ema:
+        # a foreign EMA tree (not laid out like the arena): leaf-by-leaf compute_model_ema, training_utils.py:537-544
+        LQ.compute_model_ema(unet_ema_params, state.params, float(ema_rate))
+    metrics = {"loss": loss}
+    return (state, metrics, new_rng) if return_rng else (state, metrics)
+
+
+def min_snr_weight(alphas_cumprod: torch.Tensor, timesteps: torch.Tensor, gamma: float, v_pred: bool) -> torch.Tensor:
+    """training_utils.py:546-568 — one weight per sample, computed on the device (no host round trip: the step stays
+    asynchronous and CUDA-graph capturable)."""
+    B = timesteps.numel()
+    w = torch.empty((B,), dtype=torch.float32, device=alphas_cumprod.device)
+    _lib.check(_lib.lib().sdb_min_snr_weight(alphas_cumprod.data_ptr(), alphas_cumprod.numel(), timesteps.data_ptr(), B,
+                                             float(gamma), int(v_pred), w.data_ptr(),
+                                             _lib.stream_ptr(w.device)), "sdb_min_snr_weight")
+    return w
 
 
 def mse_loss_and_grad(pred_nhwc: torch.Tensor, target_nchw: torch.Tensor, weight, grad_scale: float = 1.0):
@@ -390,15 +493,6 @@ def mse_loss_and_grad(pred_nhwc: torch.Tensor, target_nchw: torch.Tensor, weight
                                  loss.data_ptr(), B, Cc, H * W, grad_scale, ws.data_ptr(), ws.numel(),
                                  _lib.stream_ptr()), "sdb_mse_fwd_bwd")
     return loss.view(()), dpred
-
-
-def _min_snr_weight(alphas_cumprod, timesteps, gamma: float, v_pred: bool):
-    """training_utils.py:546-568 — B scalars; host arithmetic in fp32 on the gathered alphas."""
-    ac = alphas_cumprod[timesteps.long()].cpu().numpy().astype(np.float32)
-    snr = ac / (np.float32(1) - ac)
-    m = np.minimum(snr, np.float32(gamma))
-    w = m / (snr + np.float32(1)) if v_pred else m / snr
-    return torch.from_numpy(w.astype(np.float32)).to(alphas_cumprod.device)
 
 
 def default_scheduler(device, beta_schedule: str = "scaled_linear", prediction_type: str = "epsilon") -> FrozenModel:
@@ -420,63 +514,70 @@ class CompiledTrainStep:
 
     Per shape: the first call runs eagerly (fills the lazily built caches: workspaces, key-bias tables, function
     attributes), the second call captures and replays, later calls only copy the batch into the graph's static input
-    buffers and replay. Noise / timesteps missing from the batch are drawn OUTSIDE the graph into those buffers.
+    buffers and replay. Noise / timesteps missing from the batch are drawn OUTSIDE the graph into those buffers (one
+    or two Threefry kernels, training_utils.py:590-624); min-SNR weights and the EMA update are inside the graph.
     The loss returned in `metrics` is a static device tensor, overwritten by the next call (async, like the reference's
     futures: the host blocks only when it reads it)."""
 
     def __init__(self, state: TrainState, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
-                 offset_noise_magnitude: float = 0.0, min_snr_gamma_magnitude: float = 0.0,
-                 perturbation_noise_magnitude: float = 0.0):
-        if min_snr_gamma_magnitude:
-            raise NotImplementedError("CompiledTrainStep: min-SNR weighting gathers on the host; use train_step")
+                 unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
+                 min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0,
+                 ema_rate: float = 0.0):
         lr = state.hyper["learning_rate"]
         if callable(lr) and lr(0) != lr(1_000_000):
+            # the learning rate is a kernel argument baked into the graph; the reference only ever uses
+            # optax.constant_schedule (training_utils.py:355-357)
             raise NotImplementedError("CompiledTrainStep: only a constant learning-rate schedule can be baked in")
+        if ema_rate and unet_ema_params is not None and unet_ema_params is not state.ema_params:
+            raise ValueError("CompiledTrainStep: unet_ema_params must be the tree returned by state.create_ema()")
         self.state = state
         self.sched = frozen_noise_scheduler_state or default_scheduler(state.arena.device)
         self.offset = float(offset_noise_magnitude)
         self.perturb = float(perturbation_noise_magnitude)
+        self.min_snr = float(min_snr_gamma_magnitude)
+        self.ema_params = unet_ema_params
+        self.ema_rate = float(ema_rate)
         self._entries: Dict[tuple, dict] = {}
         self.launches_per_replay = 0
 
-    def _eager(self, batch, rng):
-        return train_step(self.state, batch, rng, self.sched, offset_noise_magnitude=self.offset,
-                          perturbation_noise_magnitude=self.perturb)
+    def _flags(self) -> dict:
+        return dict(unet_ema_params=self.ema_params, ema_rate=self.ema_rate, min_snr_gamma_magnitude=self.min_snr)
 
-    def _fill(self, e, batch, rng):
-        dev = self.state.arena.device
+    def _eager(self, batch, rng, return_rng):
+        return train_step(self.state, batch, rng, self.sched, offset_noise_magnitude=self.offset,
+                          perturbation_noise_magnitude=self.perturb, return_rng=return_rng, **self._flags())
+
+    def _fill(self, e, batch, rng, return_rng):
+        """Copy / draw the step's inputs into the graph's static buffers (outside the graph). Returns new_train_rng."""
         buf = e["buf"]
         buf["latents"].copy_(batch["latents"], non_blocking=True)
-        ctx = batch["encoder_hidden_states"]
-        buf["encoder_hidden_states"].copy_(ctx, non_blocking=True)
-        B = buf["latents"].shape[0]
-        gen = None
-        if batch.get("noise") is not None:
+        buf["encoder_hidden_states"].copy_(batch["encoder_hidden_states"], non_blocking=True)
+        have_n, have_t = batch.get("noise") is not None, batch.get("timesteps") is not None
+        if have_n:
             buf["noise"].copy_(batch["noise"], non_blocking=True)
-        else:
-            gen = _generator(rng, dev)
-            shape = buf["latents"].shape
-            noise = torch.randn(shape, generator=gen, device=dev, dtype=torch.float32)
-            if self.offset:
-                noise = noise + torch.randn((B, shape[1], 1, 1), generator=gen, device=dev) * self.offset
-            if self.perturb:
-                noise = noise + self.perturb * torch.randn(shape, generator=gen, device=dev)
-            buf["noise"].copy_(noise)
-        if batch.get("timesteps") is not None:
+        if have_t:
             buf["timesteps"].copy_(batch["timesteps"], non_blocking=True)
-        else:
-            gen = gen or _generator(rng, dev)
-            buf["timesteps"].copy_(torch.randint(0, self.sched.call.config.num_train_timesteps, (B,), generator=gen,
-                                                 device=dev).to(torch.int32))
+        new_rng = None
+        if not (have_n and have_t):
+            _check_rng(rng, return_rng, "CompiledTrainStep")
+            _, _, new_rng = draw_noise_and_timesteps(
+                self.state, buf["latents"].shape, rng, self.sched.call.config.num_train_timesteps,
+                need_noise=not have_n, need_timesteps=not have_t, offset_noise_magnitude=self.offset,
+                perturbation_noise_magnitude=self.perturb, noise_out=buf["noise"], timesteps_out=buf["timesteps"])
+        elif return_rng and rng is not None:
+            new_rng = JR.train_step_keys(rng)["new_train"]
+            if isinstance(rng, JR.RngStream):
+                rng.key = new_rng
+        return new_rng
 
-    def __call__(self, state: TrainState, batch: dict, rng=None):
+    def __call__(self, state: TrainState, batch: dict, rng=None, return_rng: bool = False):
         if state is not self.state:
             raise ValueError("CompiledTrainStep: called with a different TrainState than it was compiled for")
         key = (tuple(batch["latents"].shape), tuple(batch["encoder_hidden_states"].shape))
         e = self._entries.get(key)
         if e is None:
             self._entries[key] = {"graph": None}
-            return self._eager(batch, rng)  # also the warm-up of every lazily built cache
+            return self._eager(batch, rng, return_rng)  # also the warm-up of every lazily built cache
         if e["graph"] is None:
             dev = state.arena.device
             e["buf"] = {"latents": torch.empty(key[0], dtype=torch.float32, device=dev),
@@ -484,13 +585,14 @@ class CompiledTrainStep:
                         "timesteps": torch.empty((key[0][0],), dtype=torch.int32, device=dev),
                         "encoder_hidden_states": torch.empty(key[1], dtype=batch["encoder_hidden_states"].dtype,
                                                              device=dev)}
-            self._fill(e, batch, rng)
+            new_rng = self._fill(e, batch, rng, return_rng)
+            ops.freeze_workspaces()  # the graphs bake the scratch pointers: growth would leave them dangling
             self._capture(e)
         else:
-            self._fill(e, batch, rng)
+            new_rng = self._fill(e, batch, rng, return_rng)
         self._replay(e)
         state._host_step += 1
-        return state, e["metrics"]
+        return (state, e["metrics"], new_rng) if return_rng else (state, e["metrics"])
 
     def _capture(self, e) -> None:
         """Capture the step as a chain of CUDA-graph segments sharing one memory pool. Without data parallelism that
@@ -526,7 +628,7 @@ class CompiledTrainStep:
                 dp.capture = cut
             try:
                 begin()
-                _, metrics = train_step(state, e["buf"], None, self.sched)
+                _, metrics = train_step(state, e["buf"], None, self.sched, **self._flags())
                 cur["g"].capture_end()
                 segs.append((cur["g"], [], False))
             finally:

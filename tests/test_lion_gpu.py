@@ -20,7 +20,7 @@ def _run_gpu(dev, g, p, codes, inv, gnorm, wd_flag, mode=0, shadow=False):
     tgn = None if gnorm is None else torch.tensor([gnorm], dtype=torch.float32, device=dev)
     _lib.check(l.sdb_lion8_update(tg.data_ptr(), tp.data_ptr(), out.data_ptr(), _lib.ptr(sh), tc.data_ptr(),
                                   ti.data_ptr(), g.size, 16, 0.9, 0.99, 1e-6 / 7, 0.07, int(wd_flag), _lib.ptr(tgn),
-                                  1.0, mode, _lib.stream_ptr()), "lion8")
+                                  1.0, mode, 0, 0.0, _lib.stream_ptr()), "lion8")
     torch.cuda.synchronize()
     return out.cpu().numpy(), tc.cpu().numpy(), ti.cpu().numpy(), None if sh is None else sh.float().cpu().numpy()
 
@@ -93,7 +93,7 @@ def test_lion_fp32_state_bit_exact(cuda, n):
         tg, tp, tm = (torch.from_numpy(a).to(cuda) for a in (g, p, mu))
         gn = torch.tensor([2.5], dtype=torch.float32, device=cuda)
         _lib.check(l.sdb_lion_fp32_update(tg.data_ptr(), tp.data_ptr(), tp.data_ptr(), 0, tm.data_ptr(), n, 0.9, 0.99,
-                                          1e-6 / 7, 0.07, int(wd_flag), gn.data_ptr(), 1.0, 0, _lib.stream_ptr()), "l32")
+                                          1e-6 / 7, 0.07, int(wd_flag), gn.data_ptr(), 1.0, 0, 0, 0.0, _lib.stream_ptr()), "l32")
         torch.cuda.synchronize()
         assert np.array_equal(tp.cpu().numpy().view(np.uint32), want_p.view(np.uint32))
         assert np.array_equal(tm.cpu().numpy().view(np.uint32), want_m.view(np.uint32))

@@ -26,8 +26,8 @@ def test_add_noise_velocity_bit_exact(cuda, schedule, shape):
     out = torch.empty_like(tx)
     per = int(np.prod(shape[1:]))
     for fn, ref in ((l.sdb_add_noise, O.add_noise), (l.sdb_get_velocity, O.get_velocity)):
-        _lib.check(fn(tx.data_ptr(), te.data_ptr(), tt.data_ptr(), ac.data_ptr(), out.data_ptr(), shape[0], per,
-                      _lib.stream_ptr()), "noise")
+        _lib.check(fn(tx.data_ptr(), te.data_ptr(), tt.data_ptr(), ac.data_ptr(), ac.numel(), out.data_ptr(), shape[0],
+                      per, _lib.stream_ptr()), "noise")
         torch.cuda.synchronize()
         want = ref(st["alphas_cumprod"], x0, eps, t)
         assert np.array_equal(out.cpu().numpy().view(np.uint32), want.view(np.uint32))

@@ -38,7 +38,7 @@ elif what == "lion":
     inv = torch.ones(n // 16, device=dev)
     for _ in range(3):
         _lib.check(_lib.lib().sdb_lion8_update(g.data_ptr(), p.data_ptr(), p.data_ptr(), sh.data_ptr(), codes.data_ptr(),
-                                               inv.data_ptr(), n, 16, 0.9, 0.99, 1e-6 / 7, 0.07, 1, 0, 1.0, 0,
+                                               inv.data_ptr(), n, 16, 0.9, 0.99, 1e-6 / 7, 0.07, 1, 0, 1.0, 0, 0, 0.0,
                                                _lib.stream_ptr()), "lion8")
 elif what == "gn":
     for (B, HW, C) in [(8, 4096, 320), (8, 1024, 640)]:
