@@ -1,0 +1,169 @@
+#!/usr/bin/env python
+"""Data-parallel correctness on hardware (/root/reference/training_utils.py:835-840,
+852-931: batch sharded on dim 0, everything else replicated, loss / gradients = global mean).
+
+    torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tools/dp_check.py \
+        [--config sd15|tiny] [--batch B] [--steps K] [--out profiles/rX_dp_check.json]
+
+Checks, on N ranks (N = WORLD_SIZE):
+ (a) N ranks x B  ==  1 rank x N*B on the concatenated batch, same weights: loss per step, the gradient arena after
+     step 1 (fp32 sum-order tolerance: all-reduce + split weight gradients add in another order), Lion codes /
+     masters after K steps (fraction of differing elements — a sign flip of a near-zero momentum moves a weight by lr);
+ (b) masters, Lion codes, reciprocal-absmax scales, fp32 momentum and the gradient arena are BIT-IDENTICAL across ranks
+     after every step, in eager mode and in segmented-CUDA-graph mode (CompiledTrainStep);
+ (c) in-step sampling: with noise / timesteps drawn from train_rng, rank r draws rows [r*B, (r+1)*B) of the global
+     draw (the N-rank losses equal the 1-rank loss on the concatenated batch).
+Rank 0 prints one JSON object and (with --out) writes it.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from stable_diffusion_training_b200 import jax_random as JR
+from stable_diffusion_training_b200 import lion_quant as LQ
+from stable_diffusion_training_b200 import parallel
+from stable_diffusion_training_b200 import training_utils as TU
+from stable_diffusion_training_b200 import unet as PU
+
+
+def checksum(t: torch.Tensor) -> int:
+    v = t.contiguous().view(torch.uint8) if t.dtype == torch.int8 else t.contiguous().view(torch.int32)
+    # position-dependent 64-bit checksum (a plain sum would miss swapped elements)
+    idx = torch.arange(v.numel(), device=v.device, dtype=torch.int64)
+    return int(((v.to(torch.int64) * ((idx % 1000003) + 1)).sum()).item())
+
+
+def ranks_identical(state, world) -> dict:
+    a = state.arena
+    out = {}
+    for name, t in (("master", a.master), ("codes", a.codes), ("inv_scales", a.inv_scales), ("mu", a.mu),
+                    ("grad", a.grad), ("shadow", a.shadow.view(torch.int16).to(torch.int32))):
+        c = torch.tensor([checksum(t)], dtype=torch.int64, device=a.device)
+        lo, hi = c.clone(), c.clone()
+        if world > 1:
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        out[name] = bool(lo.item() == hi.item())
+    return out
+
+
+def make_state(cfg, params_np, dev):
+    tree = LQ.unflatten_dict({k: torch.from_numpy(v) for k, v in params_np.items()})
+    return TU.TrainState.create(apply_fn=TU.UNetModel(cfg).apply, params=tree, tx=TU.create_lion_optimizer(tree),
+                                device=dev)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", default="sd15", choices=["sd15", "tiny"])
+    ap.add_argument("--batch", type=int, default=2)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    rank, local, world = parallel.init_process_group_from_env("nccl")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    cfg = PU.SD15 if args.config == "sd15" else PU.TINY
+    H = 64 if args.config == "sd15" else 32
+    B, K = args.batch, args.steps
+    params_np = PU.init_params_numpy(cfg, 0)
+    sched = TU.default_scheduler(dev, "scaled_linear", "epsilon")
+    rng = np.random.default_rng(77)
+    G = B * world
+    gbatches = [{"latents": rng.standard_normal((G, 4, H, H), dtype=np.float32),
+                 "noise": rng.standard_normal((G, 4, H, H), dtype=np.float32),
+                 "timesteps": rng.integers(0, 1000, G).astype(np.int32),
+                 "encoder_hidden_states": rng.standard_normal((G, 77, cfg.cross_attention_dim), dtype=np.float32)}
+                for _ in range(K)]
+
+    def shard(b, with_noise=True):
+        keys = b.keys() if with_noise else ("latents", "encoder_hidden_states")
+        return {k: torch.from_numpy(b[k][rank * B:(rank + 1) * B]).to(dev) for k in keys}
+
+    def whole(b, with_noise=True):
+        keys = b.keys() if with_noise else ("latents", "encoder_hidden_states")
+        return {k: torch.from_numpy(b[k]).to(dev) for k in keys}
+
+    report = {"config": args.config, "world": world, "batch_per_rank": B, "steps": K, "modes": {}}
+    # ---- reference run: 1 rank x N*B (every rank does it redundantly: no communication involved) ----
+    ref = make_state(cfg, params_np, dev)
+    ref_loss, ref_grad1 = [], None
+    for i in range(K):
+        ref, m = TU.train_step(ref, whole(gbatches[i]), None, sched)
+        ref_loss.append(float(m["loss"]))
+        if i == 0:
+            ref_grad1 = ref.arena.grad.clone()
+    ref_master, ref_codes = ref.arena.master.clone(), ref.arena.codes.clone()
+    ref2 = make_state(cfg, params_np, dev)
+    ref2, m = TU.train_step(ref2, whole(gbatches[0], False), JR.RngStream(5), sched, offset_noise_magnitude=0.1)
+    ref_loss_sampled = float(m["loss"])
+    del ref, ref2
+    torch.cuda.empty_cache()
+
+    for mode in ("eager", "graph"):
+        st = make_state(cfg, params_np, dev)
+        if world > 1:
+            parallel.attach(st, sync="verify")
+        step = TU.compile_train_step(st, sched) if mode == "graph" else \
+            (lambda s, b, r: TU.train_step(s, b, r, sched))
+        losses, ident, grad_rel = [], [], None
+        reps = K + (1 if mode == "graph" else 0)  # graph mode: call 1 is the eager warm-up, captured from call 2 on
+        for i in range(K):
+            st, m = step(st, shard(gbatches[i]), None)
+            torch.cuda.synchronize()
+            losses.append(float(m["loss"]))
+            ident.append(ranks_identical(st, world))
+            if i == 0:
+                grad_rel = float((st.arena.grad - ref_grad1).double().norm() / ref_grad1.double().norm())
+        frac_master = float((st.arena.master != ref_master).float().mean())
+        frac_codes = float((st.arena.codes != ref_codes).float().mean())
+        max_master = float((st.arena.master - ref_master).abs().max())
+        report["modes"][mode] = {
+            "loss": losses, "loss_1rank": ref_loss,
+            "grad_step1_rel_diff_vs_1rank": grad_rel,
+            "masters_differing_frac_vs_1rank": frac_master, "codes_differing_frac_vs_1rank": frac_codes,
+            "masters_max_abs_diff_vs_1rank": max_master,
+            "ranks_bit_identical_per_step": ident,
+            "bytes_all_reduced": int(st.dp.bytes_reduced) if st.dp is not None else 0,
+        }
+        ok = all(all(d.values()) for d in ident)
+        ok = ok and all(abs(a - b) <= 2e-3 * abs(b) for a, b in zip(losses, ref_loss))
+        ok = ok and grad_rel < 2e-3 and frac_master < 2e-2 and frac_codes < 2e-2
+        ok = ok and max_master <= 2 * K * (1e-6 / 7) * 1.1
+        report["modes"][mode]["ok"] = bool(ok)
+        if mode == "eager":  # (c) sharded sampling == global draw
+            st2 = make_state(cfg, params_np, dev)
+            if world > 1:
+                parallel.attach(st2, sync="broadcast")
+            st2, m = TU.train_step(st2, shard(gbatches[0], False), JR.RngStream(5), sched, offset_noise_magnitude=0.1)
+            ls = float(m["loss"])
+            report["sampling"] = {"loss": ls, "loss_1rank": ref_loss_sampled,
+                                  "ok": bool(abs(ls - ref_loss_sampled) <= 2e-3 * abs(ref_loss_sampled))}
+            del st2
+        del st, step
+        torch.cuda.empty_cache()
+    report["ok"] = bool(all(v["ok"] for v in report["modes"].values()) and report["sampling"]["ok"])
+    if rank == 0:
+        print(json.dumps(report))
+        if args.out:
+            with open(args.out, "w") as f:
+                json.dump(report, f, indent=1)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    sys.exit(0 if report["ok"] else 1)
+
+
+if __name__ == "__main__":
+    main()
