@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — UNet train samples/sec at 512^2 (64x64x4 latents), SD-1.5 UNet, batch 8 per GPU (BASELINE.json configs[1]).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config sd15|sd21|tiny] [--batch B]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config sd15|sd21|tiny|lion] [--batch B]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
 One "step" = one pass of the hot path (add_noise -> UNet fwd -> MSE -> UNet bwd -> [bucketed NCCL all-reduce] ->
@@ -12,8 +12,13 @@ clip + 8-bit Lion + apply) over one synthetic batch. Prints ONE JSON line on ran
   roofline     tensor-pipe roofline of the step (algorithmic matmul FLOPs) + the HBM roofline of the Lion
                optimizer kernels timed alone ("kernels" sub-object)
   cpu_baseline the oracle (CPU restatement of the reference: torch-CPU fp32 UNet + NumPy Lion; JAX is not installable
-               here) timed on this box's host cores on a bounded sample of the same workload
---impl reference times that CPU restatement as the reference arm (the reference itself is JAX/TPU code and cannot run).
+               here) timed on this box's host cores on a bounded sample of the same workload: 1 of the step's samples
+               through the UNet + 1/B of the optimizer's elements per step — nothing is extrapolated
+--impl reference times that CPU restatement as the reference arm (the reference itself is JAX/TPU code and cannot run):
+               exactly --warmup + --steps bounded steps, same `config` object as our arm.
+--config lion  BASELINE.json configs[4]: the 8-bit Lion step alone over the full SD-1.5 parameter set (HBM roofline).
+--config sd21  BASELINE.json configs[3]: SD-2.x UNet, 96x96 latents, batch 4 per GPU, v-prediction.
+Refuses to run while SDB_* experiment variables are set (--allow-experiments stamps them into the JSON instead).
 """
 from __future__ import annotations
 
@@ -241,10 +246,8 @@ def run_ours(args):
             "metric": METRIC, "value": round(sps, 3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(step_ms, 3), "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": w["name"], "batch_per_gpu": B, "global_batch": B * world,
-                       "parallelism": f"dp{world}", "weights": "random-init (SURVEY 8(d) distributions)",
-                       "l2": "working set (1.7 GB bf16 weights + activations) >> 126 MB L2; 4 rotating batches",
-                       "cuda_graph": bool(args.graph), "loss_last": loss_last},
+            "config": common_config(args.config, B, world),
+            "run": {"cuda_graph": bool(args.graph), "loss_last": loss_last},
             "e2e": {"value": round(world * B * args.steps / e2e_s, 3), "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "loss_last": loss_host},
             "gpu_launches": int(launches),
@@ -252,25 +255,42 @@ def run_ours(args):
             "roofline": roofline_object(kernels, peaks, ach_tf, step_ms),
         }
         if not args.no_cpu:
-            out["cpu_baseline"] = cpu_baseline(args.config, budget_s=args.cpu_budget)
+            out["cpu_baseline"] = cpu_baseline(args.config, steps=2, warmup=0)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return out
 
 
+def ncu_traffic():
+    """dram read + write bytes per launch of the dominant kernel from the committed `ncu --set full` capture of THIS
+    build (profiles/ncu_traffic.json: {"build": sha1 of csrc/gemm_tc.cu, "traffic": bytes, "source": file}); None when
+    there is no capture or it belongs to another build of the kernel."""
+    import hashlib
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        src = os.path.join(ROOT, "stable_diffusion_training_b200", "csrc", "gemm_tc.cu")
+        if d.get("build") == hashlib.sha1(open(src, "rb").read()).hexdigest():
+            return int(d["traffic"]), d.get("source")
+    except Exception:
+        pass
+    return None, None
+
+
 def roofline_object(kernels, peaks, step_tf, step_ms):
     """`roofline` = the dominant kernel (the tcgen05 implicit-GEMM conv3x3, 320->320 @ 64x64, B=8: the GEMM family is
-    ~50 % of the step, profiles/r1i_ablation.md) timed live with CUDA events; `traffic` = dram bytes per launch from the
-    committed `ncu --set full` capture (profiles/r1n_ncu_full.md). The whole step and the other kernels ride along."""
+    ~50 % of the step, profiles/r3e_summary.md) timed live with CUDA events; `traffic` = dram bytes per launch from the
+    committed `ncu --set full` capture of this build (ncu_traffic), else null. The whole step and the other kernels
+    ride along."""
     k = kernels.get("conv3x3_fwd_320x320@64")
     step = {"bound": "tensor", "achieved": round(step_tf, 2), "peak": peaks["tf_sustained"], "unit": "TFLOP/s",
             "frac": round(step_tf / peaks["tf_sustained"], 4), "ms": round(step_ms, 3),
             "what": "whole train step: algorithmic matmul FLOPs/step (SURVEY 8(d)) / step time, sustained bf16 peak"}
     if k is None:
         return dict(step, traffic=None, of=peaks["source"], kernels=kernels)
+    traffic, traffic_src = ncu_traffic()
     return {"bound": "tensor", "achieved": k["achieved"], "peak": k["peak"], "unit": "TFLOP/s", "frac": k["frac"],
-            "traffic": 22849792, "kernel": "gemm_tc_kernel<FWD, 2 halves> conv3x3 320->320 @64x64 B=8",
+            "traffic": traffic, "traffic_source": traffic_src, "kernel": "gemm_tc_kernel<FWD, 2 halves> conv3x3 320->320 @64x64 B=8",
             "flops_per_launch": k["flops"], "ms_per_launch": k["ms"],
             "of": peaks["source"] + ", burst bf16 (kernel timed alone, L2 flushed between launches)",
             "step": step, "kernels": kernels}
@@ -352,20 +372,19 @@ def kernel_rooflines(state, peaks):
 
 
 # ---------------------------------------------------------------------------------------------------------------
-def cpu_baseline(config: str, budget_s: float = 30.0, steps: int = 1):
-    """The oracle timed as the CPU baseline: torch-CPU fp32 restatement of the reference UNet train step on ONE sample of
-    the workload (fwd + bwd + loss, all host threads) + NumPy 8-bit Lion on a 1/16 subset of the leaves scaled to
-    the full set. kind = "port" (the reference is JAX and cannot be imported on this box)."""
+_CPU_CACHE: dict = {}
+
+
+def _cpu_setup(config: str):
+    """Random-init parameters + one synthetic batch for the CPU arm (built once per process)."""
+    if config in _CPU_CACHE:
+        return _CPU_CACHE[config]
     import numpy as np
     import torch
-    from oracle import lion as OL
     from oracle import sched as OS
     from oracle import unet as OU
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
     cfg = {"sd15": OU.SD15, "sd21": OU.SD21, "tiny": OU.TINY}[config]
     w = WORKLOADS[config]
-    Bs = 1 if config != "tiny" else w["batch"]
     g = torch.Generator().manual_seed(0)
     params = {}
     for name, shape in OU.param_shapes(cfg).items():
@@ -376,55 +395,258 @@ def cpu_baseline(config: str, budget_s: float = 30.0, steps: int = 1):
         if name.endswith("scale"):
             params[name] += 1.0
     ac = OS.common_state("scaled_linear", 0.00085, 0.012)["alphas_cumprod"]
-    lat = torch.randn(Bs, 4, w["H"], w["H"], generator=g)
-    nz = torch.randn(Bs, 4, w["H"], w["H"], generator=g)
-    ts = torch.randint(0, 1000, (Bs,), generator=g)
-    ctx = torch.randn(Bs, w["L"], cfg.cross_attention_dim, generator=g)
+    B = w["batch"]
+    batch = (torch.randn(B, 4, w["H"], w["H"], generator=g), torch.randn(B, 4, w["H"], w["H"], generator=g),
+             torch.randint(0, 1000, (B,), generator=g), torch.randn(B, w["L"], cfg.cross_attention_dim, generator=g))
+    quant = {n: (n.endswith("kernel") and not any(e in n.split("/") for e in ("conv_in", "conv_out", "time_embedding",
+                                                                             "time_emb_proj"))
+                 and params[n].numel() % 16 == 0) for n in params}
+    _CPU_CACHE[config] = (cfg, params, ac, batch, quant)
+    return _CPU_CACHE[config]
+
+
+def cpu_step(config: str, n_samples: int, cores: int):
+    """ONE bounded sample of the workload on the host cores, nothing scaled afterwards: `n_samples` of the step's B
+    samples through the oracle's fp32 UNet (forward + loss + backward, torch-CPU, all threads), then the oracle's NumPy
+    8-bit Lion over the SAME fraction n_samples / B of every parameter leaf's elements (the optimizer runs once per
+    B-sample step, so n_samples samples carry n_samples / B of it; leaf chunks run on a thread pool — NumPy releases
+    the GIL). Returns (seconds, unet seconds, lion seconds)."""
+    import numpy as np
+    import torch
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import lion as OL
+    from oracle import unet as OU
+    cfg, params, ac, batch, quant = _cpu_setup(config)
+    w = WORKLOADS[config]
+    B = w["batch"]
     ptype = "v_prediction" if config == "sd21" else "epsilon"
-    times = []
-    for _ in range(steps):
-        t0 = time.perf_counter()
-        loss, grads, _ = OU.loss_and_grads(cfg, params, lat, nz, ts, ctx, ac, prediction_type=ptype, mode="fp32")
-        t_unet = time.perf_counter() - t0
-        names = sorted(params)
-        sub = names[::16]
-        frac = sum(params[n].numel() for n in sub) / sum(params[n].numel() for n in names)
-        t0 = time.perf_counter()
-        for n in sub:
-            gl = grads[n].numpy().reshape(-1)
-            q = n.endswith("kernel") and gl.size % 16 == 0
-            st = OL.init_state((gl.size,), q)
-            OL.lion_leaf_update(gl, params[n].numpy().reshape(-1), st, wd_flag=n.endswith("kernel"))
-        t_lion = (time.perf_counter() - t0) / max(frac, 1e-9)
-        times.append(t_unet + t_lion)
-        del grads
-    t = sorted(times)[len(times) // 2]
-    return {"value": round(Bs / t, 5), "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{Bs} sample(s) of the workload through the oracle (torch-CPU fp32 UNet fwd+bwd+loss {t_unet:.1f} s, "
-                      f"{cores} threads) + NumPy Lion-8bit on 1/16 of the leaves scaled to all ({t_lion:.1f} s); "
-                      f"JAX/Flax reference not installable here", "seconds_per_step": round(t, 2)}
+    lat, nz, ts, ctx = (t[:n_samples] for t in batch)
+    t0 = time.perf_counter()
+    loss, grads, _ = OU.loss_and_grads(cfg, params, lat, nz, ts, ctx, ac, prediction_type=ptype, mode="fp32")
+    t_unet = time.perf_counter() - t0
+    frac = n_samples / B
+
+    def leaf(n):
+        numel = params[n].numel()
+        m = max(16, int(numel * frac) // 16 * 16) if numel >= 16 else numel
+        m = min(m, numel)
+        gl = grads[n].numpy().reshape(-1)[:m]
+        pl = params[n].numpy().reshape(-1)[:m]
+        q = quant[n] and m % 16 == 0
+        OL.lion_leaf_update(gl, pl, OL.init_state((m,), q), wd_flag=n.endswith("kernel"))
+        return m
+
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=cores) as ex:
+        done = sum(ex.map(leaf, sorted(params, key=lambda n: -params[n].numel())))
+    t_lion = time.perf_counter() - t0
+    del grads
+    return t_unet + t_lion, t_unet, t_lion, done
+
+
+def cpu_baseline(config: str, steps: int = 2, warmup: int = 0, n_samples: int = 0):
+    """The oracle timed as the CPU baseline (kind = "port": the reference is JAX/Flax for TPU and cannot be imported
+    or installed on this box). value = samples/s = n_samples / seconds of a bounded step (see cpu_step)."""
+    import torch
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    w = WORKLOADS[config]
+    B = w["batch"]
+    ns = n_samples or (B if config == "tiny" else 1)
+    for _ in range(warmup):
+        cpu_step(config, ns, cores)
+    times = [cpu_step(config, ns, cores) for _ in range(max(1, steps))]
+    tot = sum(t[0] for t in times)
+    t_unet = sum(t[1] for t in times) / len(times)
+    t_lion = sum(t[2] for t in times) / len(times)
+    return {"value": round(ns * len(times) / tot, 5), "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"per step: {ns} of the step's {B} samples through the oracle's torch-CPU fp32 UNet fwd+loss+bwd "
+                      f"({t_unet:.2f} s, {cores} threads) + the oracle's NumPy Lion-8bit over {ns}/{B} of every leaf "
+                      f"({times[-1][3]} elements, {t_lion:.2f} s, {cores} threads); nothing extrapolated; the JAX/Flax "
+                      f"reference itself is not installable here",
+            "seconds_per_step": round(tot / len(times), 3), "steps_timed": len(times), "total_s": round(tot, 2)}
+
+
+def common_config(config: str, B: int, world: int):
+    """The `config` object — identical in both arms (ours / reference) by construction."""
+    w = WORKLOADS[config]
+    return {"workload": w["name"], "batch_per_gpu": B, "global_batch": B * world, "parallelism": f"dp{world}",
+            "weights": "random-init (SURVEY 8(d) distributions)",
+            "l2": "working set (1.7 GB bf16 weights + activations) >> 126 MB L2; 4 rotating batches"}
 
 
 def run_reference(args):
     """Reference arm: the reference's own train step is JAX/Flax on TPU and cannot be imported or installed on this box
     (no jax / flax / optax / diffusers wheels, no network); the arm therefore times the CPU restatement (oracle port) on
-    the host cores. Rank 0 only."""
+    the host cores — exactly `--warmup` + `--steps` bounded steps (cpu_step). Rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return None
+    if args.config == "lion":
+        return run_lion_reference(args)
     w = WORKLOADS[args.config]
     B = args.batch or w["batch"]
-    steps = max(1, min(args.steps, 3))
-    for _ in range(min(args.warmup, 1)):
-        cpu_baseline(args.config, steps=1)
-    cb = cpu_baseline(args.config, steps=steps)
+    cb = cpu_baseline(args.config, steps=args.steps, warmup=args.warmup)
     return {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
-            "steps": steps, "warmup": min(args.warmup, 1), "ms_per_step": round(1e3 * cb["seconds_per_step"], 1),
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * cb["seconds_per_step"], 1),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": w["name"], "batch_per_gpu": B, "global_batch": B * args.gpus,
-                       "note": "CPU restatement of the reference (oracle port); each step = a bounded 1-sample pass"},
+            "config": common_config(args.config, B, args.gpus),
             "cpu_baseline": cb, "gpu_launches": 0,
             "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# BASELINE.json configs[4]: the quantised-Lion optimizer step alone over the full SD-1.5 parameter set
+LION_METRIC = "lion8_optimizer_param_updates_per_sec"
+LION_WORKLOAD = ("8-bit Lion step alone (clip_by_global_norm + lion_8bit + apply) over the full SD-1.5 UNet leaf set: "
+                 "686 leaves, 256 quantised / 831 201 280 elements, 430 fp32-state / 28 319 684; replicated per GPU")
+
+
+def run_lion(args):
+    """One "step" = global-norm + clip + Lion-8bit + apply over the whole arena (3 + 2 launches), gradients resident
+    in HBM (4 rotating gradient arenas would not fit the point: the 3.4 GB arena alone is 27x the L2)."""
+    import torch
+    import torch.distributed as dist
+    from stable_diffusion_training_b200 import _lib
+    from stable_diffusion_training_b200 import lion_quant as LQ
+    from stable_diffusion_training_b200 import parallel
+    from stable_diffusion_training_b200 import training_utils as TU
+    from stable_diffusion_training_b200 import unet as PU
+    os.environ.setdefault("NCCL_DEBUG", "WARN")
+    rank, local, world = parallel.init_process_group_from_env("nccl")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    L = _lib.lib()
+    _lib.check(L.sdb_check_device(local), "sdb_check_device")
+    cfg = PU.SD15
+    params = LQ.unflatten_dict(fast_params(cfg, 0))
+    state = TU.TrainState.create(apply_fn=TU.UNetModel(cfg).apply, params=params, tx=TU.create_lion_optimizer(params),
+                                 device=dev)
+    del params
+    a = state.arena
+    g = torch.Generator(device=dev).manual_seed(2)
+    # SURVEY 8(d): g ~ N(0, (3.4e-5)^2) (about unit global norm); 10 warm-up steps so that codes are not all 3
+    a.grad.normal_(0, 3.4e-5, generator=g)
+    for _ in range(max(args.warmup, 10)):
+        state.apply_gradients(grads=None)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    n0 = L.sdb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        state.apply_gradients(grads=None)
+    e1.record()
+    barrier()
+    launches = L.sdb_launch_count() - n0
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    # e2e: a host gradient slab is copied in every step (pinned, 64 MB: the optimizer's real producer is the backward
+    # pass on the device, so the copy is bounded) and the global norm is read back
+    slab = torch.empty(16 << 20, dtype=torch.float32).pin_memory()
+    slab.normal_(0, 3.4e-5)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        a.grad[: slab.numel()].copy_(slab, non_blocking=True)
+        state.apply_gradients(grads=None)
+        gn = float(a.gnorm.item())
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_s = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    out = None
+    if rank == 0:
+        peaks = measured_peaks()
+        n_params = 859_520_964
+        step_ms = ms_total / args.steps
+        nq, nf = a.n_quant, a.n_total - a.n_quant
+        by = nq * 14.5 + nf * 20.0 + a.n_total * 4.0   # Lion (SURVEY 8(d)) + the separate global-norm read of g
+        ach = by / step_ms / 1e6
+        out = {"metric": LION_METRIC, "value": round(world * n_params * args.steps / (ms_total / 1e3), 1),
+               "unit": "params/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 10),
+               "ms_per_step": round(step_ms, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "f32 math, int8 state", "data": "synthetic",
+               "config": {"workload": LION_WORKLOAD, "parallelism": f"replicas x{world} (the reference replicates the "
+                          "optimizer state: PartitionSpec())", "l2": "3.4 GB gradient arena + 3.4 GB masters >> 126 MB L2"},
+               "e2e": {"value": round(world * n_params * args.steps / e2e_s, 1), "unit": "params/s",
+                       "h2d_bytes_per_step": slab.numel() * 4, "d2h_bytes_per_step": 4, "gnorm_last": gn},
+               "gpu_launches": int(launches), "clocks": clocks,
+               "roofline": {"bound": "hbm", "achieved": round(ach, 1), "peak": peaks["hbm"], "unit": "GB/s",
+                            "frac": round(ach / peaks["hbm"], 4), "traffic": None,
+                            "kernel": "sumsq_partial + lion8_kernel x2 + lion32_kernel x2 over the arena",
+                            "bytes_per_step": by, "of": peaks["source"]}}
+        if not args.no_cpu:
+            out["cpu_baseline"] = lion_cpu_baseline()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return out
+
+
+def lion_cpu_baseline(frac: float = 1.0 / 16):
+    """oracle/lion.py over 1/16 of every SD-1.5 leaf (thread pool), reported as params/s of that sample."""
+    import numpy as np
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import lion as OL
+    from oracle import unet as OU
+    cores = os.cpu_count() or 1
+    shapes = OU.param_shapes(OU.SD15)
+    rng = np.random.default_rng(2)
+    excl = ("conv_in", "conv_out", "time_embedding", "time_emb_proj")
+    work = []
+    for n, shp in shapes.items():
+        numel = int(np.prod(shp))
+        m = min(numel, max(16, int(numel * frac) // 16 * 16))
+        q = n.endswith("kernel") and not any(e in n.split("/") for e in excl) and m % 16 == 0
+        work.append((n, m, q))
+    data = {n: ((rng.standard_normal(m) * 3.4e-5).astype(np.float32), (rng.standard_normal(m) * 0.02).astype(np.float32))
+            for n, m, _ in work}
+
+    def leaf(item):
+        n, m, q = item
+        OL.lion_leaf_update(data[n][0], data[n][1], OL.init_state((m,), q), wd_flag=n.endswith("kernel"))
+        return m
+
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=cores) as ex:
+        done = sum(ex.map(leaf, sorted(work, key=lambda it: -it[1])))
+    dt = time.perf_counter() - t0
+    return {"value": round(done / dt, 1), "unit": "params/s", "cores": cores, "kind": "port",
+            "sample": f"oracle/lion.py (NumPy) over 1/16 of every SD-1.5 leaf = {done} elements in {dt:.2f} s, "
+                      f"{cores} threads", "seconds": round(dt, 3)}
+
+
+def run_lion_reference(args):
+    cbs = [lion_cpu_baseline() for _ in range(args.warmup + args.steps)][args.warmup:]
+    v = sum(c["value"] for c in cbs) / len(cbs)
+    cb = dict(cbs[-1], value=round(v, 1))
+    return {"impl": "reference", "metric": LION_METRIC, "value": cb["value"], "unit": "params/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(1e3 * sum(c["seconds"] for c in cbs) / len(cbs), 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": LION_WORKLOAD}, "cpu_baseline": cb, "gpu_launches": 0,
+            "e2e": {"value": cb["value"], "unit": "params/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+EXPERIMENT_ENV = ("SDB_SKIP", "SDB_GEMM_DBG", "SDB_BN", "SDB_MT", "SDB_SPLITK", "SDB_SPLITK_FORCE", "SDB_DELIVERY_CLKS",
+                  "SDB_SIDE_STREAM", "SDB_GN_LEGACY", "SDB_EXPERIMENTS", "SDB_LIB_PATH", "SDB_BUILD_TAG", "NVCC_EXTRA")
+
+
+def experiment_env():
+    return {k: v for k, v in os.environ.items() if k.startswith("SDB_") or k == "NVCC_EXTRA"}
 
 
 def main():
@@ -433,21 +655,33 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--config", default="sd15", choices=list(WORKLOADS))
+    ap.add_argument("--config", default="sd15", choices=list(WORKLOADS) + ["lion"])
+    ap.add_argument("--allow-experiments", action="store_true",
+                    help="run although SDB_* experiment variables are set (they are stamped into the JSON line)")
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--graph", type=int, default=1, help="replay the step from a CUDA graph (0: eager launches)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-kernels", action="store_true", help="skip the per-kernel roofline leg")
-    ap.add_argument("--cpu-budget", type=float, default=30.0)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    env = experiment_env()
+    bad = sorted(k for k in env if k in EXPERIMENT_ENV)
+    if bad and not args.allow_experiments:
+        sys.stderr.write(f"bench.py: experiment variables are set ({', '.join(bad)}): a benchmark number under them is "
+                         "meaningless. Unset them or pass --allow-experiments (they are then stamped into the JSON).\n")
+        sys.exit(2)
     # stdout carries exactly ONE JSON line: libraries that print banners on fd 1 (NCCL's version line) go to stderr
     sys.stdout.flush()
     real_stdout = os.dup(1)
     os.dup2(2, 1)
-    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if args.impl == "reference":
+        out = run_reference(args)
+    else:
+        out = run_lion(args) if args.config == "lion" else run_ours(args)
     sys.stdout.flush()
     if out is not None:
+        if env:
+            out["experiment_env"] = env
         os.write(real_stdout, (json.dumps(out) + "\n").encode())
 
 

@@ -14,8 +14,11 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
-BUILD_DIR = os.path.join(HERE, "_build")
-LIB_PATH = os.path.join(HERE, "libsdb200.so")
+# SDB_BUILD_TAG=<tag> (with NVCC_EXTRA=-D...) builds an experiment variant next to the product library
+# (libsdb200_<tag>.so, objects under _build_<tag>/); _lib loads it only with SDB_EXPERIMENTS=1 SDB_LIB_PATH=<path>.
+_TAG = os.environ.get("SDB_BUILD_TAG", "")
+BUILD_DIR = os.path.join(HERE, "_build" + ("_" + _TAG if _TAG else ""))
+LIB_PATH = os.path.join(HERE, "libsdb200" + ("_" + _TAG if _TAG else "") + ".so")
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -103,10 +103,16 @@ SIGNATURES = {
 _lib = None
 
 
+def experiments_enabled() -> bool:
+    return os.environ.get("SDB_EXPERIMENTS") == "1"
+
+
 def lib() -> C.CDLL:
     """Load libsdb200.so (built in-tree by _build.py). Raises if it is missing — there is no fallback path."""
-    global _lib
+    global _lib, LIB_PATH
     if _lib is None:
+        if experiments_enabled() and os.environ.get("SDB_LIB_PATH"):
+            LIB_PATH = os.environ["SDB_LIB_PATH"]  # an experiment build (SDB_BUILD_TAG); never set by the product
         if not os.path.exists(LIB_PATH):
             raise SdbError(
                 f"{LIB_PATH} not found: build it with `python -m stable_diffusion_training_b200._build` "
@@ -116,10 +122,11 @@ def lib() -> C.CDLL:
             fn = getattr(l, name)
             fn.restype = res
             fn.argtypes = args
-        # SDB_SKIP=sym1,sym2 (timing experiments only, tools/ablate.sh): the named entry points return 0 without
-        # launching, so the marginal cost of an operator class inside a CUDA-graph replay can be measured. Results
-        # are then meaningless; nothing in the product or the tests sets it.
-        skip = [x for x in os.environ.get("SDB_SKIP", "").split(",") if x]
+        # SDB_EXPERIMENTS=1 SDB_SKIP=sym1,sym2 (timing experiments only, tools/ablate.sh): the named entry points
+        # return 0 without launching, so the marginal cost of an operator class inside a CUDA-graph replay can be
+        # measured. Results are then meaningless; nothing in the product or the tests sets it, bench.py refuses to
+        # run under it, and without the explicit SDB_EXPERIMENTS=1 opt-in the variable is ignored.
+        skip = [x for x in os.environ.get("SDB_SKIP", "").split(",") if x] if experiments_enabled() else []
         for name in skip:
             if name in SIGNATURES:
                 setattr(l, name, (lambda *a, **k: 0))

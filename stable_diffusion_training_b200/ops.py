@@ -183,7 +183,8 @@ def _pick_splitk(N: int, pix, b_mn: bool, nkb: int, mt0: int, bn0: int):
     return best
 
 
-_SKIP_GEMM = set(x for x in os.environ.get("SDB_SKIP", "").split(",") if x.startswith("gemm_"))
+_SKIP_GEMM = set(x for x in os.environ.get("SDB_SKIP", "").split(",") if x.startswith("gemm_")) \
+    if _lib.experiments_enabled() else set()
 
 
 def _launch(desc: GemmDesc, impl: str) -> None:

@@ -5,7 +5,7 @@ out=${1:-gpurun_out/ablate.txt}
 : > $out
 run() {
   name=$1; shift
-  ms=$(SDB_SKIP=$1 timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu --no-kernels 2>/dev/null | python -c "import json,sys; print(json.loads(sys.stdin.read())['ms_per_step'])")
+  ms=$(SDB_EXPERIMENTS=1 SDB_SKIP=$1 timeout 300 python bench.py --allow-experiments --steps 10 --warmup 3 --no-cpu --no-kernels 2>/dev/null | python -c "import json,sys; print(json.loads(sys.stdin.read())['ms_per_step'])")
   echo "$name $ms" >> $out
 }
 run base none
