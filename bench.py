@@ -641,7 +641,7 @@ def run_lion_reference(args):
             "e2e": {"value": cb["value"], "unit": "params/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
-EXPERIMENT_ENV = ("SDB_SKIP", "SDB_GEMM_DBG", "SDB_BN", "SDB_MT", "SDB_SPLITK", "SDB_SPLITK_FORCE", "SDB_DELIVERY_CLKS",
+EXPERIMENT_ENV = ("SDB_SKIP", "SDB_GEMM_DBG", "SDB_BN", "SDB_MT", "SDB_SPLITK", "SDB_SPLITK_FORCE", "SDB_SPLITK_RED", "SDB_DELIVERY_CLKS",
                   "SDB_SIDE_STREAM", "SDB_GN_LEGACY", "SDB_EXPERIMENTS", "SDB_LIB_PATH", "SDB_BUILD_TAG", "NVCC_EXTRA")
 
 

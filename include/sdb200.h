@@ -159,9 +159,12 @@ typedef struct {
   int N;                /* output columns */
   int K;                /* FWD: reduction length per tap (channels of A) */
   int block_n;          /* N tile width, multiple of 16, <= 256 */
-  int splits;           /* WGRAD: split of the pixel range. FWD: split-K (> 1: D is an fp32 [pixels, N] buffer, row
-                           stride ldd, that the call zeroes and accumulates partial sums into with red.global.add;
-                           bias / temb / residual / d_stride* must be unset; finish with sdb_splitk_finish) */
+  int splits;           /* WGRAD: split of the pixel range. FWD: split-K (> 1: D is fp32 scratch, row stride ldd;
+                           bias / temb / residual / d_stride* must be unset; finish with sdb_splitk_finish).
+                           splitk_slab > 0: K range s stores its partial sums into the slab D + s * splitk_slab
+                           (the effective number of ranges is ceil(KB / ceil(KB / splits)), KB = ntaps * ceil(K / 64))
+                           — deterministic; splitk_slab == 0: one [pixels, N] buffer that the call zeroes and
+                           accumulates into with red.global.add */
   void* d;
   long long ldd;
   long long d_strideW, d_strideH, d_strideN; /* FWD only: element strides of the output pixel grid; all 0 = dense
@@ -173,6 +176,7 @@ typedef struct {
   const void* residual;
   long long ldr;
   int m_halves;         /* sdb_gemm_tc: M tile = 128 * m_halves rows (1 or 2; 0 = 1). Two halves share every B stage */
+  long long splitk_slab; /* FWD split-K: elements between per-range slabs (see splits); 0 = atomic accumulation */
 } sdb_gemm_desc;
 
 int sdb_gemm_tc(const sdb_gemm_desc* desc, cudaStream_t stream);
@@ -253,9 +257,10 @@ int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStrea
  * (bias fp32 [N], temb bf16 [images, ldt], residual bf16 [rows, ldr]; each may be NULL). Replaces the fused epilogue of
  * sdb_gemm_tc for the low-resolution layers of the UNet (flax nn.Conv / nn.Dense bias add, the time-embedding add of
  * FlaxResnetBlock2D and the residual adds, diffusers 0.21.4 resnet_flax.py / attention_flax.py). */
-int sdb_splitk_finish(const float* acc, long long lda, const float* bias, const void* temb, long long ldt,
-                      long long rows_per_image, const void* residual, long long ldr, void* out, long long ldo,
-                      long long rows, int N, cudaStream_t stream);
+int sdb_splitk_finish(const float* acc, long long lda, int nslabs, long long slab_stride, const float* bias,
+                      const void* temb, long long ldt, long long rows_per_image, const void* residual, long long ldr,
+                      void* out, long long ldo, long long rows, int N, cudaStream_t stream);
+/* acc: nslabs fp32 [rows, lda] slabs slab_stride elements apart, summed in slab order (nslabs = 1: one buffer). */
 size_t sdb_colsum_workspace_bytes(long long rows, int cols);
 int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long rows_per_seg, int cols, float* out_total,
                     void* out_seg_bf16, void* workspace, size_t ws_bytes, cudaStream_t stream);

@@ -32,7 +32,7 @@ class GemmDesc(C.Structure):
         ("M", C.c_int), ("N", C.c_int), ("K", C.c_int), ("block_n", C.c_int), ("splits", C.c_int),
         ("d", C.c_void_p), ("ldd", C.c_longlong), ("d_strideW", C.c_longlong), ("d_strideH", C.c_longlong),
         ("d_strideN", C.c_longlong), ("bias", C.c_void_p), ("temb", C.c_void_p), ("ldt", C.c_longlong),
-        ("residual", C.c_void_p), ("ldr", C.c_longlong), ("m_halves", C.c_int),
+        ("residual", C.c_void_p), ("ldr", C.c_longlong), ("m_halves", C.c_int), ("splitk_slab", C.c_longlong),
     ]
 
 
@@ -92,7 +92,7 @@ SIGNATURES = {
     "sdb_upsample2x_bwd": (_I, [_P, _P, _I, _I, _I, _I, _P]),
     "sdb_copy2d_bf16": (_I, [_P, _LL, _P, _LL, _LL, _I, _I, _P]),
     "sdb_add_bf16": (_I, [_P, _P, _P, _LL, _P]),
-    "sdb_splitk_finish": (_I, [_P, _LL, _P, _P, _LL, _LL, _P, _LL, _P, _LL, _LL, _I, _P]),
+    "sdb_splitk_finish": (_I, [_P, _LL, _I, _LL, _P, _P, _LL, _LL, _P, _LL, _P, _LL, _LL, _I, _P]),
     "sdb_colsum_workspace_bytes": (_SZ, [_LL, _I]),
     "sdb_colsum_bf16": (_I, [_P, _LL, _I, _LL, _I, _P, _P, _P, _SZ, _P]),
     "sdb_silu_fwd": (_I, [_P, _P, _LL, _P]),

@@ -358,7 +358,8 @@ extern "C" int sdb_copy2d_bf16(const void* src, long long lds, void* dst, long l
 
 // out[r, c] = bf16(acc[r, c] + bias[c] + temb[r / rows_per_image, c] + residual[r, c]): the epilogue of a split-K forward
 // GEMM (sdb_gemm_tc with splits > 1 leaves fp32 partial sums in acc)
-__global__ void splitk_finish_kernel(const float* __restrict__ acc, long long lda, const float* __restrict__ bias,
+__global__ void splitk_finish_kernel(const float* __restrict__ acc, long long lda, int nslabs, long long slab_stride,
+                                     const float* __restrict__ bias,
                                      const __nv_bfloat16* __restrict__ temb, long long ldt, long long rows_per_image,
                                      const __nv_bfloat16* __restrict__ residual, long long ldr,
                                      __nv_bfloat16* __restrict__ out, long long ldo, long long rows, int nvec) {
@@ -370,6 +371,11 @@ __global__ void splitk_finish_kernel(const float* __restrict__ acc, long long ld
     const int c = (int)(i - r * nvec) * 8;
     const float4 a0 = sdb::ld_f4(acc + r * lda + c), a1 = sdb::ld_f4(acc + r * lda + c + 4);
     float f[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    for (int s = 1; s < nslabs; ++s) {  // fixed order: the result does not depend on the GEMM's schedule
+      const float* ps = acc + (long long)s * slab_stride + r * lda + c;
+      const float4 s0 = sdb::ld_f4(ps), s1 = sdb::ld_f4(ps + 4);
+      f[0] += s0.x; f[1] += s0.y; f[2] += s0.z; f[3] += s0.w; f[4] += s1.x; f[5] += s1.y; f[6] += s1.z; f[7] += s1.w;
+    }
     if (bias != nullptr) {
       const float4 b0 = sdb::ld_f4(bias + c), b1 = sdb::ld_f4(bias + c + 4);
       f[0] += b0.x; f[1] += b0.y; f[2] += b0.z; f[3] += b0.w; f[4] += b1.x; f[5] += b1.y; f[6] += b1.z; f[7] += b1.w;
@@ -390,17 +396,19 @@ __global__ void splitk_finish_kernel(const float* __restrict__ acc, long long ld
   }
 }
 
-extern "C" int sdb_splitk_finish(const float* acc, long long lda, const float* bias, const void* temb, long long ldt,
-                                 long long rows_per_image, const void* residual, long long ldr, void* out, long long ldo,
-                                 long long rows, int N, cudaStream_t stream) {
+extern "C" int sdb_splitk_finish(const float* acc, long long lda, int nslabs, long long slab_stride, const float* bias,
+                                 const void* temb, long long ldt, long long rows_per_image, const void* residual,
+                                 long long ldr, void* out, long long ldo, long long rows, int N, cudaStream_t stream) {
   SDB_CHECK_ARG(acc != nullptr && out != nullptr && rows > 0 && N > 0, "sdb_splitk_finish: bad arguments");
+  SDB_CHECK_ARG(nslabs >= 1 && (nslabs == 1 || (slab_stride >= rows * lda && slab_stride % 4 == 0)),
+                "sdb_splitk_finish: bad slab layout (nslabs %d, stride %lld)", nslabs, slab_stride);
   SDB_CHECK_ARG(rows * (N / 8) < (1ll << 31) && rows_per_image < (1ll << 31), "sdb_splitk_finish: too many elements");
   SDB_CHECK_ARG(N % 8 == 0 && lda % 4 == 0 && ldo % 8 == 0 && ldt % 8 == 0 && ldr % 8 == 0 && rows_per_image > 0,
                 "sdb_splitk_finish: N %% 8, lda %% 4, ldo/ldt/ldr %% 8 and rows_per_image > 0 required");
   SDB_CHECK_ARG((((uintptr_t)acc | (uintptr_t)out | (uintptr_t)bias | (uintptr_t)temb | (uintptr_t)residual) & 15) == 0,
                 "sdb_splitk_finish: 16-byte alignment required");
   splitk_finish_kernel<<<ew_grid(rows * (N / 8)), 256, 0, stream>>>(
-      acc, lda, bias, reinterpret_cast<const __nv_bfloat16*>(temb), ldt, rows_per_image,
+      acc, lda, nslabs, slab_stride, bias, reinterpret_cast<const __nv_bfloat16*>(temb), ldt, rows_per_image,
       reinterpret_cast<const __nv_bfloat16*>(residual), ldr, reinterpret_cast<__nv_bfloat16*>(out), ldo, rows, N / 8);
   SDB_CUDA_LAUNCH_CHECK("sdb_splitk_finish");
   return SDB_OK;

@@ -3,12 +3,12 @@
 // Replaces flax nn.Conv / nn.Dense (forward, dgrad, wgrad) inside FlaxUNet2DConditionModel [diffusers 0.21.4,
 // un-vendored; call site /root/reference/training_utils.py:678-684] — SURVEY §2.1 K1/K2.
 //
-// One persistent, warp-specialised kernel (one CTA per SM, 192 threads):
+// One persistent, warp-specialised kernel (one CTA per SM, 352 threads):
 //   warp 0      : TMA producer  — 4-D tiled tensor maps over NHWC activations; a 3x3 tap is a box shifted by
 //                 (dh, dw) whose out-of-bounds part TMA zero-fills (= the conv padding); weights are 2-D boxes.
-//   warp 1      : TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x N x 16, bf16 -> fp32).
-//   warps 2..5  : epilogue — tcgen05.ld of the accumulator (one row per thread), bias / time-embedding / residual
-//                 add, bf16 (or fp32 / red.add for wgrad) stores.
+//   warps 1, 6  : tcgen05.mma issuers, one per 128-row half of the tile (UMMA 128 x N x 16, bf16 -> fp32); warp 1 owns TMEM.
+//   warps 2..5, 7..10 : two epilogue sets — tcgen05.ld of the accumulator (one row per thread), bias / time-embedding /
+//                 residual add, bf16 (or fp32 / red.add for wgrad) stores.
 // Two 256-column TMEM accumulators let the epilogue of tile i overlap the main loop of tile i+1.
 //
 // Operand layouts (all SWIZZLE_128B, produced directly by TMA):
@@ -48,16 +48,12 @@ extern "C" int sdb_gemm_timeline(long long* host_out) {
 
 namespace {
 
-// -DSDB_GEMM_EPI2 (candidate, default off): a second set of four epilogue warps (7-10). MT == 2: set e drains half e, which
-// should halve the 5.4 K-cycle tile-boundary gap of profiles/r3g_gemm_timeline.md; MT == 1: the sets alternate 32-column
-// chunks. A first measurement (r2i, before the timeline existed) showed no gain: re-measure with tools/gemm_timeline.py.
-#ifdef SDB_GEMM_EPI2
-constexpr int kThreads = 352;
+// Two sets of four epilogue warps (2-5 and 7-10). MT == 2: set e drains half e, which halves the tile-boundary gap the
+// operand-ring timeline exposed (5.4 K of ~39 K cycles per 256-row tile, profiles/r3g_gemm_timeline.md); MT == 1: the sets
+// alternate 32-column chunks. Measured r4a: conv3x3 320->320 @64x64 fwd 62.5 -> 58.4 us, FF linear 320->2560 fwd
+// 80.9 -> 68.6 us, the step -0.6 ms (together with the lean producer -1.4 ms).
+constexpr int kThreads = 352;                // warp 0 TMA, warps 1 / 6 MMA issuers (half 0 / 1), warps 2-5 and 7-10 epilogue
 constexpr int kEpiSets = 2;
-#else
-constexpr int kThreads = 224;                // warp 0 TMA, warp 1 MMA issuer (half 0), warps 2-5 epilogue, warp 6 MMA issuer (half 1)
-constexpr int kEpiSets = 1;
-#endif
 constexpr int kBlockK = 64;                 // bf16 elements per K block (one 128-byte swizzle row)
 constexpr uint32_t kAStageBytes = 128 * 128;  // 16 KB: 128 rows x 128 B, or two 64-row MN-major boxes
 constexpr uint32_t kBoxBytes = 64 * 128;      // one 64-row box
@@ -74,6 +70,7 @@ struct alignas(64) TcParams {
   int M, N, K, BN;
   int tiles_m, tiles_n, total_tiles, kblocks;
   int splits, pb_per_split, total_pb;
+  long long slab;  // FWD split-K: > 0 = elements between the per-split fp32 slabs (plain stores, deterministic); 0 = red.add
   int stages, dbg, mt;
   int st32;  // every output row segment the epilogue writes is 32-byte aligned: 32-byte stores
   uint32_t a_stage_bytes;
@@ -92,6 +89,7 @@ struct Tile {
   int w0, h0, n0;          // FWD: pixel origin of the M tile
   int tap, m_off;          // WGRAD
   int kb_begin, num_k;     // K iterations
+  int split;               // FWD split-K: index of this tile's K range
 };
 
 __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
@@ -114,6 +112,7 @@ __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
     ti.m_off = 0;
     ti.kb_begin = split * p.pb_per_split;
     ti.num_k = min(p.total_pb, ti.kb_begin + p.pb_per_split) - ti.kb_begin;
+    ti.split = split;
   } else {
     int split = t % p.splits;
     int r = t / p.splits;
@@ -127,6 +126,7 @@ __device__ __forceinline__ Tile decode_tile(const TcParams& p, int t) {
     int kb_end = min(p.total_pb, ti.kb_begin + p.pb_per_split);
     ti.num_k = kb_end - ti.kb_begin;
     ti.w0 = ti.h0 = ti.n0 = 0;
+    ti.split = split;
   }
   ti.nw = min(p.BN, p.N - ti.n_off);
   ti.umma_n = (ti.nw + 15) & ~15;
@@ -185,11 +185,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       int gk = 0;  // K blocks of this CTA so far (timeline index)
       for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
         const Tile ti = decode_tile(p, t);
-#ifdef SDB_GEMM_FAST_PRODUCER
-        // Candidate for the next round (r3g timeline: one producer iteration costs 500-600 clk — the integer division,
-        // the tap-indexed parameter loads and the box arithmetic sit in front of every TMA — and that, not the MMAs
-        // (320 clk) or the fetch latency (440 clk), paces the 128-row GEMMs of the 16x16 / 8x8 levels). Everything that
-        // depends on the tap or the pixel block is carried incrementally; off by default until validated on a GPU.
+        // Everything that depends on the tap or the pixel block is carried incrementally: with an integer division, four
+        // tap-indexed parameter loads and the box arithmetic in front of every TMA one producer iteration cost 500-600
+        // clk and paced the 128-row GEMMs of the 16x16 / 8x8 levels (MMAs 320 clk, fetch latency 440 clk: r3g timeline).
+        // Measured r4a: conv3x3 1280->1280 @16x16 fwd 76.8 -> 68.6 us, dgrad 59.4 -> 54.3 us, the step -0.9 ms.
         int f_tap = 0, f_kb = 0, f_cw = 0, f_ch = 0, f_brow = 0, f_iw = 0, f_ih = 0, f_in = 0;
         const CUtensorMap* f_ma = &p.mapA[0];
         if (MODE == SDB_GEMM_FWD) {
@@ -254,54 +253,6 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             phase ^= 1u;
           }
         }
-#else
-        for (int it = 0; it < ti.num_k; ++it, ++gk) {
-          ptx::mbar_wait_sleep(&empty_bar[stage], phase ^ 1u);
-          SDB_GTL(0, gk, 0);
-          uint8_t* sa = smem + (size_t)stage * p.stage_bytes;
-          uint8_t* sb = sa + p.a_stage_bytes;
-          if (!ptx::elect_one()) {
-            // the other lanes only follow the loop
-          } else if (SDB_DBG(p, 1)) {  // experiment: no TMA traffic (SDB_GEMM_DBG=1)
-            ptx::mbar_expect_tx(&full_bar[stage], 0u);
-          } else if (MODE == SDB_GEMM_FWD) {
-            const int kk = ti.kb_begin + it;
-            const int tap = kk / p.kblocks;
-            const int kb = kk - tap * p.kblocks;
-            const uint32_t bbytes = p.b_mn ? (uint32_t)ti.nboxes * kBoxBytes : p.b_stage_bytes;
-            ptx::mbar_expect_tx(&full_bar[stage], p.a_stage_bytes + bbytes);
-            ptx::tma_load_4d(sa, &p.mapA[p.tap_src[tap]], &full_bar[stage], kb * kBlockK, ti.w0 + p.tap_dw[tap],
-                             ti.h0 + p.tap_dh[tap], ti.n0);
-            if (p.b_mn) {
-              for (int j = 0; j < ti.nboxes; ++j)
-                ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j,
-                                 p.tap_brow[tap] + kb * kBlockK, 0, 0);
-            } else {
-              ptx::tma_load_4d(sb, &p.mapB, &full_bar[stage], kb * kBlockK, p.tap_brow[tap] + ti.n_off, 0, 0);
-            }
-          } else {
-            const int pb = ti.kb_begin + it;
-            const int iw = pb % p.tw;
-            const int r = pb / p.tw;
-            const int ih = r % p.th;
-            const int in = r / p.th;
-            const int pw0 = iw * p.bw, ph0 = ih * p.bh, pn0 = in * p.bn;
-            ptx::mbar_expect_tx(&full_bar[stage], p.a_stage_bytes + (uint32_t)ti.nboxes * kBoxBytes);
-            const CUtensorMap* ma = &p.mapA[p.tap_src[ti.tap]];
-            for (int i = 0; i < 2 * MT; ++i)
-              ptx::tma_load_4d(sa + i * kBoxBytes, ma, &full_bar[stage], ti.m_off + 64 * i, pw0 + p.tap_dw[ti.tap],
-                               ph0 + p.tap_dh[ti.tap], pn0);
-            for (int j = 0; j < ti.nboxes; ++j)
-              ptx::tma_load_4d(sb + j * kBoxBytes, &p.mapB, &full_bar[stage], ti.n_off + 64 * j, pw0, ph0, pn0);
-          }
-          __syncwarp();
-          SDB_GTL(0, gk, 1);
-          if (++stage == p.stages) {
-            stage = 0;
-            phase ^= 1u;
-          }
-        }
-#endif
       }
     }
   } else if (warp == 1 || warp == 6) {
@@ -383,8 +334,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
         const float* bias = p.bias ? p.bias + ti.n_off : nullptr;
         const __nv_bfloat16* temb = p.temb ? p.temb + (long long)n * p.ldt + ti.n_off : nullptr;
         if (p.splits > 1) {
-          // split-K: fp32 partial sums into the (zeroed) [pixels, N] buffer; sdb_splitk_finish adds the rest
-          float* acc_out = reinterpret_cast<float*>(p.d) + grow * p.ldd + ti.n_off;
+          // split-K: fp32 partial sums; sdb_splitk_finish adds the rest. Slab mode (default): every K range stores
+          // into its own [pixels, N] slab and the finish pass folds the slabs in a fixed order — deterministic, no
+          // memset, no atomics. red mode: red.global.add into one zeroed buffer (order depends on the schedule).
+          float* acc_out = reinterpret_cast<float*>(p.d) + (long long)ti.split * p.slab + grow * p.ldd + ti.n_off;
           for (int c0 = c_first; c0 < ti.nw; c0 += c_step) {
             uint32_t v[32];
             ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
@@ -392,11 +345,16 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             if (valid) {
 #pragma unroll
               for (int j4 = 0; j4 < 32; j4 += 4) {
-                if (c0 + j4 < ti.nw)
-                  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(acc_out + c0 + j4),
-                               "f"(__uint_as_float(v[j4])), "f"(__uint_as_float(v[j4 + 1])),
-                               "f"(__uint_as_float(v[j4 + 2])), "f"(__uint_as_float(v[j4 + 3]))
-                               : "memory");
+                if (c0 + j4 < ti.nw) {
+                  if (p.slab > 0)
+                    sdb::st_f4(acc_out + c0 + j4, make_float4(__uint_as_float(v[j4]), __uint_as_float(v[j4 + 1]),
+                                                              __uint_as_float(v[j4 + 2]), __uint_as_float(v[j4 + 3])));
+                  else
+                    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(acc_out + c0 + j4),
+                                 "f"(__uint_as_float(v[j4])), "f"(__uint_as_float(v[j4 + 1])),
+                                 "f"(__uint_as_float(v[j4 + 2])), "f"(__uint_as_float(v[j4 + 3]))
+                                 : "memory");
+                }
               }
             }
           }
@@ -637,8 +595,14 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
       SDB_CHECK_ARG(d->bias == nullptr && d->temb == nullptr && d->residual == nullptr && d->d_strideW == 0 &&
                         d->d_strideH == 0 && d->d_strideN == 0 && d->N % 4 == 0 && d->ldd % 4 == 0,
                     "sdb_gemm_tc: split-K forward accumulates plain fp32 partial sums (no epilogue terms, dense output)");
-      const cudaError_t me = cudaMemsetAsync(d->d, 0, (size_t)p.W * p.H * p.NI * (size_t)d->ldd * sizeof(float), stream);
-      if (me != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: memset: %s", cudaGetErrorString(me));
+      if (d->splitk_slab > 0) {
+        SDB_CHECK_ARG(d->splitk_slab >= (long long)p.W * p.H * p.NI * d->ldd && d->splitk_slab % 4 == 0,
+                      "sdb_gemm_tc: splitk_slab (%lld) must cover pixels x ldd and be a multiple of 4", d->splitk_slab);
+        p.slab = d->splitk_slab;
+      } else {
+        const cudaError_t me = cudaMemsetAsync(d->d, 0, (size_t)p.W * p.H * p.NI * (size_t)d->ldd * sizeof(float), stream);
+        if (me != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: memset: %s", cudaGetErrorString(me));
+      }
     }
     if (p.b_mn) {
       rc = encode_view(&p.mapB, d->b, 64, 64, 1, 1, "B (weights [K,N])");

@@ -183,6 +183,9 @@ def _pick_splitk(N: int, pix, b_mn: bool, nkb: int, mt0: int, bn0: int):
     return best
 
 
+# experiment switch (SDB_EXPERIMENTS=1 SDB_SPLITK_RED=1): accumulate split-K partial sums with red.global.add into one
+# buffer (the round-1 path, schedule-dependent summation order) instead of per-range slabs folded in a fixed order
+_SPLITK_RED = _lib.experiments_enabled() and os.environ.get("SDB_SPLITK_RED") == "1"
 _SKIP_GEMM = set(x for x in os.environ.get("SDB_SKIP", "").split(",") if x.startswith("gemm_")) \
     if _lib.experiments_enabled() else set()
 
@@ -228,13 +231,18 @@ def gemm_fwd(a_views, taps, b: torch.Tensor, b_mn: bool, out: torch.Tensor, pix,
         d.m_halves = mt
         d.bw, d.bh, d.bn = _pixel_box(W, H, NI, 128 * mt)
         rows = W * H * NI
-        ws = workspace(out.device, rows * N * 4)
+        # the library's effective number of K ranges (include/sdb200.h: sdb_gemm_desc.splits)
+        nslabs = -(-nkb // -(-nkb // d.splits))
+        slabs = not _SPLITK_RED
+        ws = workspace(out.device, rows * N * 4 * (nslabs if slabs else 1))
         d.d = ws.data_ptr()
         d.ldd = N
+        d.splitk_slab = rows * N if slabs else 0
         _launch(d, impl)
         r2 = residual.view(-1, residual.shape[-1]) if residual is not None else None
         _lib.check(_lib.lib().sdb_splitk_finish(
-            ws.data_ptr(), N, _lib.ptr(bias), temb.data_ptr() if temb is not None else None,
+            ws.data_ptr(), N, nslabs if slabs else 1, rows * N, _lib.ptr(bias),
+            temb.data_ptr() if temb is not None else None,
             temb.stride(0) if temb is not None else 0, W * H, r2.data_ptr() if r2 is not None else None,
             r2.stride(0) if r2 is not None else 0, out2.data_ptr() + d_offset * out2.element_size(), out2.stride(0),
             rows, N, _lib.stream_ptr()), "sdb_splitk_finish")

@@ -185,8 +185,8 @@ def force_splitk(monkeypatch):
 @pytest.mark.parametrize("B,H,W,Cin,Cout", [(8, 16, 16, 320, 320), (8, 8, 8, 192, 640), (2, 16, 16, 64, 96),
                                             (3, 12, 20, 64, 200)])
 def test_conv3x3_splitk(cuda, force_splitk, spec, B, H, W, Cin, Cout):
-    """Split-K forward / dgrad (fp32 partial sums with red.global.add, then sdb_splitk_finish adds bias, time embedding
-    and residual) gives the same result as the fused-epilogue kernel: every K range, ragged last split, 256-row tiles."""
+    """Split-K forward / dgrad (fp32 partial sums per K range, then sdb_splitk_finish folds them and adds bias, time
+    embedding and residual) gives the same result as the fused-epilogue kernel: every K range, ragged last split, 256-row tiles."""
     force_splitk(spec)
     x = _rand((B, H, W, Cin), cuda, seed=1)
     w = _rand((3, 3, Cin, Cout), cuda, 1.0 / (9 * Cin) ** 0.5, seed=2)
@@ -204,6 +204,25 @@ def test_conv3x3_splitk(cuda, force_splitk, spec, B, H, W, Cin, Cout):
     dx = ops.conv3x3_dgrad(dy, w)
     torch.cuda.synchronize()
     _close(dx, xt.grad.permute(0, 2, 3, 1), atol=4e-2)
+
+
+@pytest.mark.parametrize("red", [False, True])
+def test_splitk_slab_mode_is_deterministic(cuda, force_splitk, monkeypatch, red):
+    """Default split-K (per-range slabs folded in a fixed order by sdb_splitk_finish) returns the same bits on every
+    run — XLA's result is deterministic too; the atomic mode (experiment switch) is checked for parity only."""
+    force_splitk("1,128,6")
+    monkeypatch.setattr(ops, "_SPLITK_RED", red)
+    B, H, W, Cin, Cout = 8, 8, 8, 1280, 1280
+    x = _rand((B, H, W, Cin), cuda, seed=1)
+    w = _rand((3, 3, Cin, Cout), cuda, 1.0 / (9 * Cin) ** 0.5, seed=2)
+    bias = torch.randn(Cout, device=cuda)
+    outs = [ops.conv3x3(x, w, bias=bias).clone() for _ in range(6)]
+    torch.cuda.synchronize()
+    ref = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(3, 2, 0, 1), bias, padding=1)
+    _close(outs[0], ref.permute(0, 2, 3, 1))
+    if not red:
+        for o in outs[1:]:
+            assert torch.equal(o, outs[0])
 
 
 @pytest.mark.parametrize("spec", ["1,128,2", "2,256,5"])

@@ -136,15 +136,17 @@ def test_sd21_real_widths_train_step_matches_oracle(cuda):
 
 def test_sd15_full_size_compiled_step_matches_eager(cuda):
     """compile_train_step (CUDA-graph replay) == eager train_step on the real SD-1.5 graph at B = 2: the second call
-    is the captured + replayed one. Compared: loss, every gradient leaf (fp32 sum-order tolerance: split weight
-    gradients accumulate with red.add) and the fraction of Lion codes / masters that differ."""
+    is the captured + replayed one. Forward and input gradients are deterministic (split-K folds its partial sums in a
+    fixed order), so the losses are bit-identical and the gradients differ only by the fp32 summation order of the
+    split weight-gradient GEMMs (red.add): ~1e-6 relative, which moves a Lion code only where the momentum sits on a
+    rounding threshold. A second eager run gives the run-to-run yardstick for the same quantities."""
     cfg = PU.SD15
     params_np = PU.init_params_numpy(cfg, 0)
     sched = TU.default_scheduler(cuda, "scaled_linear", "epsilon")
     batches = [{k: torch.from_numpy(v).to(cuda) for k, v in _batch(2, 64, 77, cfg.cross_attention_dim, seed=s).items()}
                for s in (11, 12)]
     res = {}
-    for mode in ("eager", "graph"):
+    for mode in ("eager", "eager2", "graph"):
         tree = LQ.unflatten_dict(params_np)
         state = TU.TrainState.create(apply_fn=TU.UNetModel(cfg).apply, params=tree, tx=TU.create_lion_optimizer(tree),
                                      device=cuda)
@@ -158,14 +160,18 @@ def test_sd15_full_size_compiled_step_matches_eager(cuda):
         res[mode] = (losses, state.arena.grad.detach().clone(), state.arena.master.detach().clone(),
                      state.arena.codes.detach().clone(), int(state.step))
         del state, step, tree
-    (le, ge, pe, ce, se), (lg, gg, pg, cg, sg) = res["eager"], res["graph"]
-    assert se == sg == 2
-    np.testing.assert_allclose(lg, le, rtol=1e-3)
-    rel = float((gg - ge).double().norm() / ge.double().norm())
-    frac_p = float((pe != pg).float().mean())
-    frac_c = float((ce != cg).float().mean())
-    print(f"\ncompiled vs eager @SD-1.5: losses {lg} vs {le}; grad rel diff {rel:.3e}; masters differing {frac_p:.3e}, "
-          f"codes differing {frac_c:.3e}")
-    assert rel < 1e-3
-    assert frac_p < 1e-2 and frac_c < 1e-2
-    assert float((pe - pg).abs().max()) <= 2 * 2 * (1e-6 / 7) * 1.1
+
+    def diff(a, b):
+        (la, ga, pa, ca, sa), (lb, gb, pb, cb, sb) = res[a], res[b]
+        assert sa == sb == 2
+        return dict(loss=[abs(x - y) / abs(y) for x, y in zip(la, lb)],
+                    grad=float((ga - gb).double().norm() / gb.double().norm()),
+                    masters=float((pa != pb).float().mean()), codes=float((ca != cb).float().mean()),
+                    max_master=float((pa - pb).abs().max()))
+
+    d_run, d_graph = diff("eager2", "eager"), diff("graph", "eager")
+    print(f"\nSD-1.5 B=2, 2 steps: eager vs eager {d_run}\n                     graph vs eager {d_graph}")
+    assert max(d_graph["loss"]) <= 1e-6          # deterministic forward
+    assert d_graph["grad"] <= max(10 * d_run["grad"], 1e-5)
+    assert d_graph["codes"] <= max(10 * d_run["codes"], 1e-3) and d_graph["masters"] <= max(10 * d_run["masters"], 1e-3)
+    assert d_graph["max_master"] <= 2 * 2 * (1e-6 / 7) * 1.1
