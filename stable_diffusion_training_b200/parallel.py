@@ -29,6 +29,71 @@ import torch.distributed as dist
 DEFAULT_BUCKET_BYTES = int(os.environ.get("SDB_DP_BUCKET_MB", "64")) << 20
 
 
+class NcclComm:
+    """A second NCCL communicator over the same ranks, driven directly through the C API (ctypes on the libnccl that
+    torch ships): ncclAllReduce is enqueued on OUR communication stream with no framework bookkeeping around it — no
+    work objects, no watchdog events — which is what makes the collectives capturable into the step's CUDA graph
+    (CompiledTrainStep then replays ONE graph per step instead of a chain of segments with eager collectives between
+    them). torch.distributed stays the plumbing: rendezvous, the unique-id broadcast, barriers."""
+
+    _F32, _SUM = 7, 0  # ncclFloat32, ncclSum (nccl.h)
+
+    def __init__(self, group=None):
+        import ctypes as C
+        lib = None
+        errs = []
+        cands = []
+        try:
+            import nvidia.nccl as _n
+            cands += [os.path.join(d, "lib", "libnccl.so.2") for d in list(_n.__path__)]
+        except Exception as e:  # pragma: no cover
+            errs.append(repr(e))
+        for cand in cands + ["libnccl.so.2"]:
+            try:
+                lib = C.CDLL(cand)
+                break
+            except OSError as e:
+                errs.append(str(e))
+        if lib is None:
+            raise RuntimeError(f"NcclComm: libnccl.so.2 not loadable ({errs})")
+
+        class UniqueId(C.Structure):
+            _fields_ = [("internal", C.c_byte * 128)]
+
+        self._C, self._lib = C, lib
+        lib.ncclGetErrorString.restype = C.c_char_p
+        lib.ncclGetErrorString.argtypes = [C.c_int]
+        lib.ncclGetUniqueId.argtypes = [C.POINTER(UniqueId)]
+        lib.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, UniqueId, C.c_int]
+        lib.ncclAllReduce.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        lib.ncclCommDestroy.argtypes = [C.c_void_p]
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        uid = UniqueId()
+        if self.rank == 0:
+            self._check(lib.ncclGetUniqueId(C.byref(uid)), "ncclGetUniqueId")
+        box = [bytes(uid.internal)]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        C.memmove(C.byref(uid), box[0], 128)
+        self.comm = C.c_void_p()
+        self._check(lib.ncclCommInitRank(C.byref(self.comm), self.world, uid, self.rank), "ncclCommInitRank")
+
+    def _check(self, rc: int, what: str) -> None:
+        if rc != 0:
+            raise RuntimeError(f"{what} failed: {self._lib.ncclGetErrorString(rc).decode()}")
+
+    def all_reduce_sum_f32(self, t: torch.Tensor, stream: "torch.cuda.Stream") -> None:
+        """In-place SUM all-reduce of an fp32 CUDA tensor, enqueued on `stream` (capturable)."""
+        assert t.dtype == torch.float32 and t.is_cuda and t.is_contiguous()
+        self._check(self._lib.ncclAllReduce(t.data_ptr(), t.data_ptr(), t.numel(), self._F32, self._SUM, self.comm,
+                                            stream.cuda_stream), "ncclAllReduce")
+
+    def destroy(self) -> None:
+        if self.comm:
+            self._lib.ncclCommDestroy(self.comm)
+            self.comm = None
+
+
 def build_buckets(ranges: Dict[str, Tuple[int, int]], bucket_elems: int) -> List[Tuple[int, int, List[str]]]:
     """Cut the flat arena into contiguous [start, end) buckets on leaf boundaries, in arena order; every bucket holds
     at least `bucket_elems` elements except possibly the last. Leaves larger than a bucket get their own."""
@@ -66,6 +131,10 @@ class GradReducer:
         self.bucket_of = {n: i for i, (_, _, names) in enumerate(self.buckets) for n in names}
         self.cuda = grad_flat.is_cuda
         self.comm_stream = torch.cuda.Stream(device=grad_flat.device) if self.cuda else None
+        # direct NCCL communicator (capturable collectives): CUDA tensors, more than one rank, unless SDB_DP_NCCL=torch
+        self.nccl: Optional[NcclComm] = None
+        if self.cuda and self.world_size > 1 and os.environ.get("SDB_DP_NCCL", "direct") != "torch":
+            self.nccl = NcclComm(group)
         self._pending: List[int] = []
         self._next = 0            # buckets are issued strictly in index order (identical on every rank)
         self._ready: List[bool] = []
@@ -128,10 +197,21 @@ class GradReducer:
             ev = torch.cuda.Event()
             ev.record(torch.cuda.current_stream(self.grad.device))
             self.comm_stream.wait_event(ev)
-            with torch.cuda.stream(self.comm_stream):
-                dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+            self._reduce_on_comm_stream(view)
         else:
             dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
+
+    def _reduce_on_comm_stream(self, t: torch.Tensor) -> None:
+        if self.nccl is not None:
+            self.nccl.all_reduce_sum_f32(t, self.comm_stream)
+        else:
+            with torch.cuda.stream(self.comm_stream):
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+
+    @property
+    def graph_capturable(self) -> bool:
+        """True when the collectives may be captured into the step's CUDA graph (direct NCCL communicator)."""
+        return self.nccl is not None
 
     def finish(self, loss: torch.Tensor) -> torch.Tensor:
         """Flush the remaining buckets, average the loss over ranks, join the communication stream."""
@@ -146,14 +226,18 @@ class GradReducer:
                 ev = torch.cuda.Event()
                 ev.record(torch.cuda.current_stream(self.grad.device))
                 self.comm_stream.wait_event(ev)
-                with torch.cuda.stream(self.comm_stream):
-                    dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
-                    loss.mul_(1.0 / self.world_size)
+                self._reduce_on_comm_stream(loss.view(1))
                 torch.cuda.current_stream(self.grad.device).wait_stream(self.comm_stream)
+                _scale_f32(loss, 1.0 / self.world_size)
             else:
                 dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=self.group)
                 loss.mul_(1.0 / self.world_size)
         return loss
+
+
+def _scale_f32(t: torch.Tensor, f: float) -> None:
+    """t *= f on the current stream. (0-d loss: one torch elementwise kernel; not on the compute path.)"""
+    t.mul_(f)
 
 
 def _replay_buckets(red: GradReducer, buckets: Sequence[int]) -> None:
@@ -163,10 +247,9 @@ def _replay_buckets(red: GradReducer, buckets: Sequence[int]) -> None:
     ev = torch.cuda.Event()
     ev.record(torch.cuda.current_stream(dev))
     red.comm_stream.wait_event(ev)
-    with torch.cuda.stream(red.comm_stream):
-        for b in buckets:
-            s, e, _ = red.buckets[b]
-            dist.all_reduce(red.grad[s:e], op=dist.ReduceOp.SUM, group=red.group)
+    for b in buckets:
+        s, e, _ = red.buckets[b]
+        red._reduce_on_comm_stream(red.grad[s:e])
 
 
 GradReducer.replay_segment_buckets = _replay_buckets
@@ -182,8 +265,8 @@ def _replay_finish(red: GradReducer, buckets: Sequence[int], loss: torch.Tensor)
     ev = torch.cuda.Event(enable_timing=debug)
     ev.record(torch.cuda.current_stream(dev))
     red.comm_stream.wait_event(ev)
+    red._reduce_on_comm_stream(loss.view(1))
     with torch.cuda.stream(red.comm_stream):
-        dist.all_reduce(loss, op=dist.ReduceOp.SUM, group=red.group)
         loss.mul_(1.0 / red.world_size)
         if debug:  # exposed communication: end of this rank's backward -> last all-reduce complete (printed one step late)
             prev = getattr(red, "_dbg_events", None)

@@ -23,6 +23,7 @@ views with the reference's tree structure and the (int8 codes, fp32 reciprocal-a
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass, field
 from typing import Any, Callable, Dict, List, Optional, Tuple
 
@@ -595,8 +596,9 @@ class CompiledTrainStep:
         return (state, e["metrics"], new_rng) if return_rng else (state, e["metrics"])
 
     def _capture(self, e) -> None:
-        """Capture the step as a chain of CUDA-graph segments sharing one memory pool. Without data parallelism that
-        is one segment. With it, the NCCL collectives stay OUT of the graphs: the reducer closes a segment whenever
+        """Capture the step as ONE CUDA graph (single GPU, or data parallel with the direct NCCL communicator), else as
+        a chain of CUDA-graph segments sharing one memory pool: with torch.distributed's collectives, NCCL stays OUT of
+        the graphs: the reducer closes a segment whenever
         enough gradient buckets are complete, and at replay time those buckets are all-reduced eagerly on the
         communication stream right after the segment is enqueued, overlapping the following segments."""
         import gc
@@ -615,7 +617,8 @@ class CompiledTrainStep:
 
         def begin():
             cur["g"] = torch.cuda.CUDAGraph()
-            cur["g"].capture_begin(pool=pool)
+            # thread_local: other threads (torch's NCCL watchdog polling events) must not invalidate the capture
+            cur["g"].capture_begin(pool=pool, capture_error_mode="thread_local")
 
         def cut(final: bool):
             cur["g"].capture_end()
@@ -623,8 +626,12 @@ class CompiledTrainStep:
             dp._deferred.clear()
             begin()
 
+        # With the direct NCCL communicator the collectives are captured like any kernel (forked onto the communication
+        # stream by events, joined before the optimizer): ONE graph per step. Otherwise (SDB_DP_NCCL=torch) the step is
+        # cut into segments and the collectives are issued eagerly between their replays.
+        one_graph = dp is None or dp.world_size == 1 or (dp.graph_capturable and os.environ.get("SDB_DP_SEGMENTS") != "1")
         with torch.cuda.stream(stream):
-            if dp is not None:
+            if dp is not None and not one_graph:
                 dp.capture = cut
             try:
                 begin()
