@@ -323,9 +323,9 @@ __global__ void __launch_bounds__(kFwdThreads, 1) attn_fwd_kernel(const __grid_c
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
           const int i = c * 8 + e;
-          if (emode == 0) pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used));
-          else if (emode == 1) pv[e] = (key0 + i < p.Skv) ? ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used)) : 0.f;
-          else pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, kb[i] - m_used));
+          if (emode == 0) pv[e] = ptx::ex2_mixed(fmaf(u2f(sv[i]), p.scale2, -m_used), i);
+          else if (emode == 1) pv[e] = (key0 + i < p.Skv) ? ptx::ex2_mixed(fmaf(u2f(sv[i]), p.scale2, -m_used), i) : 0.f;
+          else pv[e] = ptx::ex2_mixed(fmaf(u2f(sv[i]), p.scale2, kb[i] - m_used), i);
           l4[e & 3] += pv[e];
         }
         uint4 o;
@@ -611,9 +611,9 @@ __global__ void __launch_bounds__(kFwd2Threads, 1) attn_fwd2_kernel(const __grid
 #pragma unroll
           for (int e = 0; e < 2; ++e) {
             const int i = c * 16 + e2 * 2 + e;
-            if (emode == 0) pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used));
-            else if (emode == 1) pv[e] = (key0 + i < p.Skv) ? ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, -m_used)) : 0.f;
-            else pv[e] = ptx::ex2_approx(fmaf(u2f(sv[i]), p.scale2, kb[i] - m_used));
+            if (emode == 0) pv[e] = ptx::ex2_mixed(fmaf(u2f(sv[i]), p.scale2, -m_used), i);
+            else if (emode == 1) pv[e] = (key0 + i < p.Skv) ? ptx::ex2_mixed(fmaf(u2f(sv[i]), p.scale2, -m_used), i) : 0.f;
+            else pv[e] = ptx::ex2_mixed(fmaf(u2f(sv[i]), p.scale2, kb[i] - m_used), i);
             l4[(e2 * 2 + e) & 3] += pv[e];
           }
           o[e2] = sdb::pack_bf16x2(pv[0], pv[1]);
@@ -949,7 +949,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const int k = k4 * 4 + e;
-              const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, av[e] + rowA));  // bias - lse; -inf masks
+              const float pk = ptx::ex2_mixed(fmaf(u2f(sv[k]), p.scale2, av[e] + rowA), k);  // bias - lse; -inf masks
               pv[k] = pk;
               ds[k] = pk * (u2f(dv[k]) - bv[e]);
             }
@@ -957,7 +957,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) attn_bwd_kernel(const __grid_c
         } else {
 #pragma unroll
           for (int k = 0; k < 16; ++k) {
-            const float pk = ptx::ex2_approx(fmaf(u2f(sv[k]), p.scale2, rowA));
+            const float pk = ptx::ex2_mixed(fmaf(u2f(sv[k]), p.scale2, rowA), k);
             pv[k] = pk;
             ds[k] = pk * (u2f(dv[k]) - rowD);
           }

@@ -58,6 +58,34 @@ __device__ __forceinline__ float ex2_approx(float x) {
   return y;
 }
 
+// 2^x on the FMA / ALU pipes instead of the MUFU unit (the softmax warps of the attention kernels are bound by MUFU:
+// 16 ex2 per clock and SM against 128 FMAs): round-to-nearest split x = n + f with the 1.5 * 2^23 magic add
+// (f in [-0.5, 0.5]), a degree-3 minimax polynomial for 2^f (max relative error 7.5e-5, far inside the bf16 rounding of
+// the probabilities it feeds), and the exponent spliced in by an integer add: the low mantissa bits of the magic sum
+// hold n, so (bits << 23) is n << 23. 8 FMA/ALU instructions; arguments below -126 give ~0, +inf / nan are not expected.
+__device__ __forceinline__ float ex2_poly(float x) {
+  x = fmaxf(x, -126.0f);
+  const float t = x + 12582912.0f;
+  const float f = x - (t - 12582912.0f);
+  float p = fmaf(0.0551716573536396f, f, 0.2426111400127411f);
+  p = fmaf(p, f, 0.6932609677314758f);
+  p = fmaf(p, f, 0.9999280571937561f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(t) << 23));
+}
+// SDB_ATTN_POLY = N > 0: every N-th exponential of the attention kernels goes through ex2_poly (0, the default: all on
+// MUFU). Measured r4c (profiles/r4c_attn_poly.md): no variant is faster — the softmax warps are bound by their instruction
+// issue rate (68 % of the issue slots, XU pipe 31-53 %), and the polynomial costs 8 issue slots against 1.
+#ifndef SDB_ATTN_POLY
+#define SDB_ATTN_POLY 0
+#endif
+__device__ __forceinline__ float ex2_mixed(float x, int i) {
+#if SDB_ATTN_POLY > 0
+  return ((i % SDB_ATTN_POLY) == SDB_ATTN_POLY - 1) ? ex2_poly(x) : ex2_approx(x);
+#else
+  return ex2_approx(x);
+#endif
+}
+
 // ---------------- TMA ----------------
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
