@@ -186,7 +186,6 @@ def _pick_splitk(N: int, pix, b_mn: bool, nkb: int, mt0: int, bn0: int):
 # experiment switch (SDB_EXPERIMENTS=1 SDB_SPLITK_RED=1): accumulate split-K partial sums with red.global.add into one
 # buffer (the round-1 path, schedule-dependent summation order) instead of per-range slabs folded in a fixed order
 _SPLITK_RED = _lib.experiments_enabled() and os.environ.get("SDB_SPLITK_RED") == "1"
-_WGRAD_MT2 = _lib.experiments_enabled() and os.environ.get("SDB_WGRAD_MT2") == "1"  # experiment: 256-row wgrad tiles everywhere
 _SKIP_GEMM = set(x for x in os.environ.get("SDB_SKIP", "").split(",") if x.startswith("gemm_")) \
     if _lib.experiments_enabled() else set()
 
@@ -284,10 +283,10 @@ def gemm_wgrad(a_views, taps, b_view: View4, out: torch.Tensor, pix, M: int, N: 
     tiles_n = -(-N // 256)
     d.block_n = min(256, (-(-N // tiles_n) + 15) // 16 * 16)
     # two 128-row halves share each dY stage: measured to pay for the 3x3 convolutions of the large feature maps
-    # (many pixel blocks per tile), not for linears or the 16x16 / 8x8 levels
+    # (many pixel blocks per tile), not for linears or the 16x16 / 8x8 levels (r4d: 256-row tiles everywhere cost
+    # +1.3 ms per step)
     d.m_halves = 2 if (M > 128 and len(taps) > 1 and W * H * NI >= 8192 and os.environ.get("SDB_MT", "0") != "1") else 1
-    if _WGRAD_MT2 and M > 128:
-        d.m_halves = 2
+
     tiles = len(taps) * -(-M // (128 * d.m_halves)) * -(-N // d.block_n)
     total_pb = -(-W // d.bw) * -(-H // d.bh) * -(-NI // d.bn)
     splits = max(1, min(total_pb, (2 * NUM_SMS) // max(1, tiles)))

@@ -275,7 +275,11 @@ class Graph:
         return self._kb_cache[key]
 
     # -------- primitive layers --------
-    def linear(self, x: T, name: str, bias: bool = True, res: Optional[T] = None, geom=None) -> T:
+    def linear(self, x: T, name: str, bias: bool = True, res: Optional[T] = None, geom=None, side: bool = False) -> T:
+        """side=True: the WHOLE backward of this layer (input gradient included) runs on the parameter-gradient stream.
+        Used for the 22 time_emb_proj projections: their output gradients are per-image column sums that feed nothing
+        on the main chain until the time-embedding MLP at the very end of backward, so ~5 tiny dependent launches per
+        ResNet leave the critical path (the consumer joins the streams: Graph.silu(join_before_bwd=True))."""
         w = self.W[name + "/kernel"]
         w2 = w.view(-1, w.shape[-1])
         y = T(ops.linear(x.v, w2, bias=self.P[name + "/bias"] if bias else None,
@@ -289,8 +293,13 @@ class Graph:
                 if bias:
                     ops.colsum(dy, self.G[name + "/bias"])
                 ops.linear_wgrad(x.v, dy, out=gw.view(-1, gw.shape[-1]))
+                if side and x.rg:
+                    old = x.g
+                    x.g = ops.linear_dgrad(dy, w2, residual=old)
+                    if old is not None:
+                        self._keep.append(old)
             self._fork(param_grads, dy)
-            if x.rg:
+            if x.rg and not side:
                 x.g = ops.linear_dgrad(dy, w2, residual=x.g)
             if res is not None:
                 self._acc_safe(res, dy)
@@ -323,10 +332,13 @@ class Graph:
         def bwd():
             dy = y.g
             dy4 = dy.view(geom[0], geom[1], geom[2], cout)
-            if temb is not None:  # the per-image column sums feed the time-embedding gradient: main stream
+            if temb is not None:
+                # the per-image column sums are the gradient of the broadcast time-embedding add; `temb` (a
+                # time_emb_proj output) has this one consumer and its own backward runs on the side stream too
                 dt = torch.empty((B, cout), device=dy.device, dtype=BF16)
-                ops.colsum(dy, self.G[name + "/bias"], nseg=B, out_seg=dt)
-                self._acc_safe(temb, dt)
+                self._fork(lambda: ops.colsum(dy, self.G[name + "/bias"], nseg=B, out_seg=dt), dy, dt)
+                assert temb.g is None
+                temb.g = dt
 
             def param_grads():
                 if temb is None:
@@ -392,10 +404,12 @@ class Graph:
         self.tape.append((bwd, None))
         return y
 
-    def silu(self, x: T) -> T:
+    def silu(self, x: T, join_before_bwd: bool = False) -> T:
         y = T(ops.silu_fwd(x.v), x.geom)
 
         def bwd():
+            if join_before_bwd:
+                self.join()  # y.g was accumulated on the side stream (Graph.linear(side=True))
             self._acc_safe(x, ops.silu_bwd(x.v, y.g))
             y.g = None
         self.tape.append((bwd, None))
@@ -458,7 +472,7 @@ class Graph:
     # -------- composite blocks (diffusers 0.21.4 FlaxResnetBlock2D / FlaxTransformer2DModel) --------
     def resnet(self, x: T, temb_act: T, name: str) -> T:
         a = self.groupnorm(x, name + "/norm1", silu=True)
-        t = self.linear(temb_act, name + "/time_emb_proj")
+        t = self.linear(temb_act, name + "/time_emb_proj", side=True)
         h = self.conv3x3(a, name + "/conv1", temb=t)
         b = self.groupnorm(h, name + "/norm2", silu=True)
         sc = self.linear(x, name + "/conv_shortcut") if (name + "/conv_shortcut/kernel") in self.W else x
@@ -510,7 +524,7 @@ class UNet:
         emb = T(ops.timestep_embedding(timesteps, cfg.block_out_channels[0], cfg.flip_sin_to_cos,
                                        float(cfg.freq_shift)), None, rg=False)
         temb = g.linear(g.silu(g.linear(emb, "time_embedding/linear_1")), "time_embedding/linear_2")
-        temb_act = g.silu(temb)
+        temb_act = g.silu(temb, join_before_bwd=True)
         skips: List[T] = []
         for op in self.program:
             kind = op[0]
