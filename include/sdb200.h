@@ -71,6 +71,13 @@ int sdb_clip_by_global_norm_f32(const float* g, float* out, long long n, const f
                                 cudaStream_t stream);
 int sdb_add_f32(const float* a, const float* b, float* out, long long n, cudaStream_t stream);
 
+/* Reduction step of the peer-memory gradient all-reduce that replaces the all-reduce GSPMD inserts for the reference's
+ * data-parallel step (training_utils.py:835-840, 852-931): dst[i] = sum in rank order of the nranks contributions to
+ * this rank's slice; the own contribution is dst itself (position self_pos), staged_host is a HOST array of the
+ * nranks - 1 device pointers (ascending rank, self skipped) holding the slices pulled from the peers. nranks <= 9. */
+int sdb_sum_slices_f32(float* dst, const float* const* staged_host, int nranks, int self_pos, long long n,
+                       cudaStream_t stream);
+
 /* ---- schedulers (schedulers/scheduling_utils_flax.py:316-343; scheduling_ddpm_flax.py:196-297) ----
  * alphas_cumprod has num_timesteps entries; a timestep outside the table is wrapped once if negative and clamped,
  * as jnp's gather does (it never reads out of bounds). */

@@ -117,6 +117,71 @@ def build_buckets(ranges: Dict[str, Tuple[int, int]], bucket_elems: int) -> List
     return fixed
 
 
+class PeerAllReduce:
+    """Gradient all-reduce over NVLink / NVSwitch PEER MEMORY with no communication kernel on the SMs.
+
+    The gradient arena lives in symmetric memory (torch.distributed._symmetric_memory: every rank maps every other
+    rank's arena). A bucket [s, e) is cut into `world` slices; rank r owns slice r:
+        barrier                      every rank has finished writing the bucket
+        pull   (copy engines)        slice r of every peer's arena  ->  local staging buffers
+        reduce (sdb_sum_slices_f32)  arena[slice r] = sum over ranks in rank order          (our kernel, HBM-bound)
+        push   (copy engines)        arena[slice r]  ->  slice r of every peer's arena
+    and one barrier after the last bucket. Bytes on the wire per rank equal a ring all-reduce's (2 (N-1)/N of the
+    arena), but they are moved by the DMA engines: NCCL's all-reduce kernels hold 16-32 SMs for the whole transfer, and a
+    persistent one-CTA-per-SM GEMM launched meanwhile runs as two waves (the CTAs that find their SM taken start when
+    the first ones finish) — that, not the exposed tail, was the data-parallel overhead of round 1 (3-6 ms per step).
+    Only rank r ever computes slice r, so every rank ends up with identical bits (the replicated-state contract of
+    the reference: PartitionSpec() for parameters and optimizer state, training_utils.py:852-895)."""
+
+    def __init__(self, numel: int, device, group=None):
+        import torch.distributed._symmetric_memory as symm
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.world > 9:
+            raise RuntimeError("PeerAllReduce: at most 9 ranks (one NVSwitch domain)")
+        self.numel = numel
+        self.buf = symm.empty(numel, dtype=torch.float32, device=device)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, self.group)
+        self.peer = [self.buf if p == self.rank else self.hdl.get_buffer(p, (numel,), torch.float32, 0)
+                     for p in range(self.world)]
+        self.stage: Optional[torch.Tensor] = None
+        self._ptrs = None
+
+    def _slices(self, s: int, e: int):
+        n = e - s
+        per = -(-n // self.world)
+        per = -(-per // 4) * 4
+        return [(min(e, s + q * per), min(e, s + (q + 1) * per)) for q in range(self.world)]
+
+    def prepare(self, max_bucket_elems: int) -> None:
+        per = -(-(-(-max_bucket_elems // self.world)) // 4) * 4
+        self.stage = torch.empty((max(self.world - 1, 1), per), dtype=torch.float32, device=self.buf.device)
+
+    def all_reduce_range(self, s: int, e: int) -> None:
+        """SUM all-reduce of arena[s:e] on the CURRENT stream (s, e multiples of 4)."""
+        import ctypes as C
+        from . import _lib
+        W, r = self.world, self.rank
+        a, b = self._slices(s, e)[r]
+        n = b - a
+        self.hdl.barrier(channel=0, timeout_ms=30000)
+        order = [(r + k) % W for k in range(1, W)]           # start with the next rank: spreads the NVLink load
+        if n > 0:
+            for p in order:
+                self.stage[p if p < r else p - 1][:n].copy_(self.peer[p][a:b])
+            ptrs = (C.c_void_p * 8)(*[self.stage[i].data_ptr() for i in range(W - 1)] + [None] * (9 - W))
+            _lib.check(_lib.lib().sdb_sum_slices_f32(self.buf.data_ptr() + 4 * a, ptrs, W, r, n,
+                                                     _lib.stream_ptr(self.buf.device)), "sdb_sum_slices_f32")
+            for p in order:
+                self.peer[p][a:b].copy_(self.buf[a:b])
+
+    def finish(self) -> None:
+        """After the last bucket: every rank's pushes have landed everywhere."""
+        self.hdl.barrier(channel=0, timeout_ms=30000)
+
+
 class GradReducer:
     def __init__(self, grad_flat: torch.Tensor, ranges: Dict[str, Tuple[int, int]], *, group=None,
                  bucket_bytes: int = DEFAULT_BUCKET_BYTES, total_elems: Optional[int] = None):
@@ -135,6 +200,8 @@ class GradReducer:
         self.nccl: Optional[NcclComm] = None
         if self.cuda and self.world_size > 1 and os.environ.get("SDB_DP_NCCL", "direct") != "torch":
             self.nccl = NcclComm(group)
+        # peer-memory all-reduce (copy engines + our reduction kernel): attach() allocates the arena in symmetric memory
+        self.peer: Optional[PeerAllReduce] = None
         self._pending: List[int] = []
         self._next = 0            # buckets are issued strictly in index order (identical on every rank)
         self._ready: List[bool] = []
@@ -202,11 +269,27 @@ class GradReducer:
             dist.all_reduce(view, op=dist.ReduceOp.SUM, group=self.group)
 
     def _reduce_on_comm_stream(self, t: torch.Tensor) -> None:
+        if self.peer is not None and t.data_ptr() != 0 and self._in_arena(t):
+            s = (t.data_ptr() - self.grad.data_ptr()) // 4
+            with torch.cuda.stream(self.comm_stream):
+                self.peer.all_reduce_range(s, s + t.numel())
+            self._peer_dirty = True
+            return
         if self.nccl is not None:
             self.nccl.all_reduce_sum_f32(t, self.comm_stream)
         else:
             with torch.cuda.stream(self.comm_stream):
                 dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+
+    def _in_arena(self, t: torch.Tensor) -> bool:
+        a0 = self.grad.data_ptr()
+        return a0 <= t.data_ptr() < a0 + self.grad.numel() * 4
+
+    def _peer_finish(self) -> None:
+        if self.peer is not None and getattr(self, "_peer_dirty", False):
+            with torch.cuda.stream(self.comm_stream):
+                self.peer.finish()
+            self._peer_dirty = False
 
     @property
     def graph_capturable(self) -> bool:
@@ -226,6 +309,7 @@ class GradReducer:
                 ev = torch.cuda.Event()
                 ev.record(torch.cuda.current_stream(self.grad.device))
                 self.comm_stream.wait_event(ev)
+                self._peer_finish()
                 self._reduce_on_comm_stream(loss.view(1))
                 torch.cuda.current_stream(self.grad.device).wait_stream(self.comm_stream)
                 _scale_f32(loss, 1.0 / self.world_size)
@@ -265,6 +349,7 @@ def _replay_finish(red: GradReducer, buckets: Sequence[int], loss: torch.Tensor)
     ev = torch.cuda.Event(enable_timing=debug)
     ev.record(torch.cuda.current_stream(dev))
     red.comm_stream.wait_event(ev)
+    red._peer_finish()
     red._reduce_on_comm_stream(loss.view(1))
     with torch.cuda.stream(red.comm_stream):
         loss.mul_(1.0 / red.world_size)
@@ -317,6 +402,14 @@ def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, sync: st
         raise RuntimeError(f"parallel.attach: the state lives on {a.device}, the current device is "
                            f"cuda:{torch.cuda.current_device()} (call torch.cuda.set_device(local_rank) first)")
     _replicate_state(state, group, sync)
+    peer = None
+    mode = os.environ.get("SDB_DP_ALLREDUCE", "peer")
+    if a.device.type == "cuda" and dist.is_initialized() and dist.get_world_size(group) > 1 and mode == "peer":
+        # the gradient arena moves into symmetric memory (peers read / write it directly); every view is rebound
+        peer = PeerAllReduce(a.n_total, a.device, group)
+        a.grad = peer.buf
+        a.g.update({n: a._view(a.grad, n) for n in a.shapes})   # same dict object the UNet holds as G
+        state._grad_tree = None
     ranges = {}
     for n, shape in a.shapes.items():
         numel = 1
@@ -324,6 +417,9 @@ def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, sync: st
             numel *= int(d)
         ranges[n] = (a.offset[n], a.offset[n] + numel)
     state.dp = GradReducer(a.grad, ranges, group=group, bucket_bytes=bucket_bytes, total_elems=a.n_total)
+    if peer is not None:
+        state.dp.peer = peer
+        peer.prepare(max(e - s for s, e, _ in state.dp.buckets))
     return state.dp
 
 

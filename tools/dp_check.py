@@ -6,9 +6,12 @@
         [--config sd15|tiny] [--batch B] [--steps K] [--out profiles/rX_dp_check.json]
 
 Checks, on N ranks (N = WORLD_SIZE):
- (a) N ranks x B  ==  1 rank x N*B on the concatenated batch, same weights: loss per step, the gradient arena after
-     step 1 (fp32 sum-order tolerance: all-reduce + split weight gradients add in another order), Lion codes /
-     masters after K steps (fraction of differing elements — a sign flip of a near-zero momentum moves a weight by lr);
+ (a) N ranks x B  ==  1 rank on the same global batch, same weights. Strict form: the single rank runs the N shards as
+     micro-batches (the kernels, tile shapes and split-K choices the ranks use) and sums the gradients in fp32 — loss,
+     step-1 gradient arena, Lion codes / masters after K steps agree to fp32 summation order (a momentum sitting on a
+     rounding threshold may flip a code). Loose form: the single rank runs the CONCATENATED batch (what the reference's
+     unsharded program would do) — other tile shapes give other bf16 roundings, so agreement is bounded by the model's
+     bf16 noise (reported beside the bf16-emulation yardstick), and every master stays within K Lion steps;
  (b) masters, Lion codes, reciprocal-absmax scales, fp32 momentum and the gradient arena are BIT-IDENTICAL across ranks
      after every step, in eager mode and in segmented-CUDA-graph mode (CompiledTrainStep);
  (c) in-step sampling: with noise / timesteps drawn from train_rng, rank r draws rows [r*B, (r+1)*B) of the global
@@ -96,15 +99,45 @@ def main():
         return {k: torch.from_numpy(b[k]).to(dev) for k in keys}
 
     report = {"config": args.config, "world": world, "batch_per_rank": B, "steps": K, "modes": {}}
-    # ---- reference run: 1 rank x N*B (every rank does it redundantly: no communication involved) ----
+    from stable_diffusion_training_b200 import ops
+
+    def micro_batched_step(st, gb):
+        """ONE rank computing the N shards one after the other with the kernels (tile shapes, split-K choices) the N
+        ranks use, gradients summed in fp32: the all-reduce result up to fp32 summation order."""
+        total, loss_sum = None, 0.0
+        for r in range(world):
+            sb = {k: torch.from_numpy(v[r * B:(r + 1) * B]).to(dev) for k, v in gb.items()}
+            noisy = sched.call.add_noise(sched.params, sb["latents"], sb["noise"], sb["timesteps"])
+            x = ops.nchw_to_nhwc_bf16(noisy)
+            ctx = ops.cast_bf16(sb["encoder_hidden_states"].contiguous())
+            pred = st.net.forward(x, sb["timesteps"].to(torch.int32), ctx)
+            loss, dpred = TU.mse_loss_and_grad(pred.v, sb["noise"], None, 1.0 / world)
+            st.net.backward(pred, dpred, None)
+            total = st.arena.grad.clone() if total is None else total + st.arena.grad
+            loss_sum += float(loss) / world
+        st.arena.grad.copy_(total)
+        st.apply_gradients(grads=None)
+        return loss_sum
+
+    # ---- reference 1: one rank, the N shards as micro-batches (strict comparison) ----
     ref = make_state(cfg, params_np, dev)
     ref_loss, ref_grad1 = [], None
     for i in range(K):
-        ref, m = TU.train_step(ref, whole(gbatches[i]), None, sched)
-        ref_loss.append(float(m["loss"]))
+        ref_loss.append(micro_batched_step(ref, gbatches[i]))
         if i == 0:
             ref_grad1 = ref.arena.grad.clone()
     ref_master, ref_codes = ref.arena.master.clone(), ref.arena.codes.clone()
+    del ref
+    # ---- reference 2: one rank on the CONCATENATED batch (other tile shapes -> other fp32 summation orders -> other
+    # bf16 roundings: agreement is bounded by the bf16 noise of the model, not by fp32 rounding) ----
+    ref = make_state(cfg, params_np, dev)
+    cat_loss, cat_grad1 = [], None
+    for i in range(K):
+        ref, m = TU.train_step(ref, whole(gbatches[i]), None, sched)
+        cat_loss.append(float(m["loss"]))
+        if i == 0:
+            cat_grad1 = ref.arena.grad.clone()
+    cat_master = ref.arena.master.clone()
     ref2 = make_state(cfg, params_np, dev)
     ref2, m = TU.train_step(ref2, whole(gbatches[0], False), JR.RngStream(5), sched, offset_noise_magnitude=0.1)
     ref_loss_sampled = float(m["loss"])
@@ -117,7 +150,7 @@ def main():
             parallel.attach(st, sync="verify")
         step = TU.compile_train_step(st, sched) if mode == "graph" else \
             (lambda s, b, r: TU.train_step(s, b, r, sched))
-        losses, ident, grad_rel = [], [], None
+        losses, ident, grad_rel, grad_rel_cat = [], [], None, None
         reps = K + (1 if mode == "graph" else 0)  # graph mode: call 1 is the eager warm-up, captured from call 2 on
         for i in range(K):
             st, m = step(st, shard(gbatches[i]), None)
@@ -126,21 +159,28 @@ def main():
             ident.append(ranks_identical(st, world))
             if i == 0:
                 grad_rel = float((st.arena.grad - ref_grad1).double().norm() / ref_grad1.double().norm())
+                grad_rel_cat = float((st.arena.grad - cat_grad1).double().norm() / cat_grad1.double().norm())
         frac_master = float((st.arena.master != ref_master).float().mean())
         frac_codes = float((st.arena.codes != ref_codes).float().mean())
         max_master = float((st.arena.master - ref_master).abs().max())
         report["modes"][mode] = {
-            "loss": losses, "loss_1rank": ref_loss,
-            "grad_step1_rel_diff_vs_1rank": grad_rel,
+            "loss": losses, "loss_1rank": ref_loss, "loss_1rank_concatenated": cat_loss,
+            "grad_step1_rel_diff_vs_1rank": grad_rel, "grad_step1_rel_diff_vs_1rank_concatenated": grad_rel_cat,
+            "masters_max_abs_diff_vs_1rank_concatenated": float((st.arena.master - cat_master).abs().max()),
             "masters_differing_frac_vs_1rank": frac_master, "codes_differing_frac_vs_1rank": frac_codes,
             "masters_max_abs_diff_vs_1rank": max_master,
             "ranks_bit_identical_per_step": ident,
             "bytes_all_reduced": int(st.dp.bytes_reduced) if st.dp is not None else 0,
         }
         ok = all(all(d.values()) for d in ident)
-        ok = ok and all(abs(a - b) <= 2e-3 * abs(b) for a, b in zip(losses, ref_loss))
-        ok = ok and grad_rel < 2e-3 and frac_master < 2e-2 and frac_codes < 2e-2
+        # strict: against the micro-batched single rank (same kernels): fp32 summation order only
+        ok = ok and all(abs(a - b) <= 1e-5 * abs(b) for a, b in zip(losses, ref_loss))
+        ok = ok and grad_rel < 1e-5 and frac_master < 1e-3 and frac_codes < 1e-3
         ok = ok and max_master <= 2 * K * (1e-6 / 7) * 1.1
+        # loose: against the concatenated batch — within half the model's own bf16 noise (gradient yardstick 1.2e-2 of
+        # tests/test_train_step_full_gpu.py) and every master within K Lion steps
+        ok = ok and all(abs(a - b) <= 2e-3 * abs(b) for a, b in zip(losses, cat_loss)) and grad_rel_cat < 6e-3
+        ok = ok and float((st.arena.master - cat_master).abs().max()) <= 2 * K * (1e-6 / 7) * 1.1
         report["modes"][mode]["ok"] = bool(ok)
         if mode == "eager":  # (c) sharded sampling == global draw
             st2 = make_state(cfg, params_np, dev)
