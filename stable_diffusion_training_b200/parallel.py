@@ -94,20 +94,30 @@ class NcclComm:
             self.comm = None
 
 
-def build_buckets(ranges: Dict[str, Tuple[int, int]], bucket_elems: int) -> List[Tuple[int, int, List[str]]]:
+def build_buckets(ranges: Dict[str, Tuple[int, int]], bucket_elems: int, tail_bucket_elems: Optional[int] = None,
+                  tail_span_elems: int = 0) -> List[Tuple[int, int, List[str]]]:
     """Cut the flat arena into contiguous [start, end) buckets on leaf boundaries, in arena order; every bucket holds
-    at least `bucket_elems` elements except possibly the last. Leaves larger than a bucket get their own."""
+    at least `bucket_elems` elements except possibly the last. Leaves larger than a bucket get their own. The last
+    `tail_span_elems` elements of the arena (the gradients backward finishes last) are cut into smaller buckets of
+    `tail_bucket_elems`, so that little communication is left exposed between the end of backward and the optimizer
+    while the bulk moves in few large buckets (few cross-rank synchronisations)."""
     leaves = sorted(ranges.items(), key=lambda kv: kv[1][0])
     out: List[Tuple[int, int, List[str]]] = []
     cur: List[str] = []
     start = None
     end = 0
+    total_end = max((e for _, (_, e) in leaves), default=0)
     for name, (s, e) in leaves:
         if start is None:
             start = s
         cur.append(name)
         end = e
-        if end - start >= bucket_elems:
+        want = bucket_elems
+        if tail_bucket_elems and start >= total_end - tail_span_elems:
+            want = tail_bucket_elems
+        elif tail_bucket_elems and end > total_end - tail_span_elems:
+            want = 0  # close the last large bucket where the tail begins
+        if end - start >= want:
             out.append((start, end, cur))
             cur, start = [], None
     if cur:
@@ -147,7 +157,7 @@ class PeerAllReduce:
         self.peer = [self.buf if p == self.rank else self.hdl.get_buffer(p, (numel,), torch.float32, 0)
                      for p in range(self.world)]
         self.stage: Optional[torch.Tensor] = None
-        self._ptrs = None
+        self.direct = os.environ.get("SDB_DP_PEER_DIRECT", "0") == "1"
 
     def _slices(self, s: int, e: int):
         n = e - s
@@ -169,9 +179,15 @@ class PeerAllReduce:
         self.hdl.barrier(channel=0, timeout_ms=30000)
         order = [(r + k) % W for k in range(1, W)]           # start with the next rank: spreads the NVLink load
         if n > 0:
-            for p in order:
-                self.stage[p if p < r else p - 1][:n].copy_(self.peer[p][a:b])
-            ptrs = (C.c_void_p * 8)(*[self.stage[i].data_ptr() for i in range(W - 1)] + [None] * (9 - W))
+            if self.direct:
+                # the reduction kernel loads the peers' slices over NVLink itself (no staging copy: 2 x less local
+                # HBM traffic; the kernel's CTAs need no shared memory and co-reside with the GEMM CTAs)
+                srcs = [self.peer[p][a:b].data_ptr() for p in range(W) if p != r]
+            else:
+                for p in order:
+                    self.stage[p if p < r else p - 1][:n].copy_(self.peer[p][a:b])
+                srcs = [self.stage[i].data_ptr() for i in range(W - 1)]
+            ptrs = (C.c_void_p * 8)(*srcs + [None] * (9 - W))
             _lib.check(_lib.lib().sdb_sum_slices_f32(self.buf.data_ptr() + 4 * a, ptrs, W, r, n,
                                                      _lib.stream_ptr(self.buf.device)), "sdb_sum_slices_f32")
             for p in order:
@@ -184,12 +200,16 @@ class PeerAllReduce:
 
 class GradReducer:
     def __init__(self, grad_flat: torch.Tensor, ranges: Dict[str, Tuple[int, int]], *, group=None,
-                 bucket_bytes: int = DEFAULT_BUCKET_BYTES, total_elems: Optional[int] = None):
+                 bucket_bytes: int = DEFAULT_BUCKET_BYTES, total_elems: Optional[int] = None,
+                 tail_bucket_bytes: int = 0, tail_span_bytes: int = 0):
         self.grad = grad_flat
         self.group = group
         self.world_size = dist.get_world_size(group) if dist.is_initialized() else 1
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
-        self.buckets = build_buckets(ranges, max(1, bucket_bytes // grad_flat.element_size()))
+        es = grad_flat.element_size()
+        self.buckets = build_buckets(ranges, max(1, bucket_bytes // es),
+                                     tail_bucket_elems=max(1, tail_bucket_bytes // es) if tail_bucket_bytes else None,
+                                     tail_span_elems=tail_span_bytes // es)
         if total_elems is not None and self.buckets:  # trailing padding of the arena belongs to the last bucket
             s, e, names = self.buckets[-1]
             self.buckets[-1] = (s, max(e, total_elems), names)
@@ -416,7 +436,9 @@ def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, sync: st
         for d in shape:
             numel *= int(d)
         ranges[n] = (a.offset[n], a.offset[n] + numel)
-    state.dp = GradReducer(a.grad, ranges, group=group, bucket_bytes=bucket_bytes, total_elems=a.n_total)
+    tail_mb = int(os.environ.get("SDB_DP_TAIL_MB", "32"))
+    state.dp = GradReducer(a.grad, ranges, group=group, bucket_bytes=bucket_bytes, total_elems=a.n_total,
+                           tail_bucket_bytes=tail_mb << 20, tail_span_bytes=(2 * tail_mb) << 20)
     if peer is not None:
         state.dp.peer = peer
         peer.prepare(max(e - s for s, e, _ in state.dp.buckets))

@@ -103,3 +103,20 @@ def test_grad_reducer_world2_gloo():
     # the arena was reduced twice (two begin/finish rounds): g = 2 * (g0 + g1) ... second round sums the sums
     assert err0 == 0.0 and err1 == 0.0
     assert early0 == early1 and len(early0) >= 2       # with in-order leaves, buckets go out before finish()
+
+
+def test_peer_all_reduce_slices_tile_every_bucket():
+    """PeerAllReduce cuts a bucket into `world` slices (rank r reduces slice r): they tile the bucket, every boundary is
+    a multiple of 4 elements (128-bit accesses of sdb_sum_slices_f32) and no slice is longer than the staging rows."""
+    from stable_diffusion_training_b200.parallel import PeerAllReduce
+    for world in (2, 3, 4, 8):
+        obj = PeerAllReduce.__new__(PeerAllReduce)
+        obj.world = world
+        for (s, e) in ((0, 16), (16, 16 + 4 * 5), (1024, 1024 + 16 * 1000003), (64, 64 + 16), (0, 4)):
+            sl = obj._slices(s, e)
+            assert len(sl) == world and sl[0][0] == s and sl[-1][1] == e
+            for (a, b), (c, d) in zip(sl, sl[1:]):
+                assert b == c and a <= b
+            assert all(a % 4 == 0 and b % 4 == 0 for a, b in sl)
+            per = -(-(-(-(e - s) // world)) // 4) * 4
+            assert max(b - a for a, b in sl) <= per
