@@ -91,6 +91,13 @@ int sdb_ddpm_step(const float* model_output, const float* sample, const float* n
                   float sqrt_alpha_prod, float sqrt_beta_prod, float pred_original_coeff, float current_sample_coeff,
                   float sigma, int prediction_type, int clip_sample, cudaStream_t stream);
 
+/* FlaxDDIMScheduler.step (schedulers/scheduling_ddim_flax.py:199-284): prev = sqrt(a_prev) * x0 + direction_coeff * eps
+ * with (x0, eps) from the model output per prediction type; direction_coeff = sqrt(1 - a_prev - sigma_t^2). eta = 0
+ * (the reference's default and the only use, training_utils.py:997-1004) has no noise term. */
+int sdb_ddim_step(const float* model_output, const float* sample, float* prev_sample, long long n,
+                  float sqrt_alpha_prod, float sqrt_beta_prod, float sqrt_alpha_prod_prev, float direction_coeff,
+                  int prediction_type, cudaStream_t stream);
+
 /* ---- loss (training_utils.py:704-709, min-SNR weight 546-568) ----
  * pred: UNet output NHWC bf16 [B,HW,C]; target: NCHW fp32 [B,C,HW]; sample_weight: nullable fp32 [B].
  * loss[0] = mean(w_b (target-pred)^2); dpred (nullable) = d loss / d pred * loss_grad_scale, NHWC bf16. */

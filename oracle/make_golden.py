@@ -174,6 +174,36 @@ def sched_cases():
     return save
 
 
+def ddim_cases():
+    """The UNMODIFIED /root/reference/schedulers/scheduling_ddim_flax.py under the shim: the placeholder scheduler the
+    reference saves (training_utils.py:997-1004: scaled_linear 0.00085-0.012, set_alpha_to_one False, steps_offset 1,
+    v_prediction) and the other prediction types, 50 inference steps."""
+    sys.path.insert(0, REF)
+    try:
+        ddim = importlib.import_module("schedulers.scheduling_ddim_flax")
+    finally:
+        sys.path.remove(REF)
+    jnp = sys.modules["jax.numpy"]
+    rng = np.random.default_rng(13)
+    mo = rng.standard_normal((2, 4, 8, 8)).astype(np.float32)
+    smp = rng.standard_normal((2, 4, 8, 8)).astype(np.float32)
+    save = {"model_output": mo, "sample": smp}
+    for ptype in ("epsilon", "sample", "v_prediction"):
+        for one in (True, False):
+            s = ddim.FlaxDDIMScheduler(beta_start=0.00085, beta_end=0.012, beta_schedule="scaled_linear",
+                                       num_train_timesteps=1000, set_alpha_to_one=one, steps_offset=1,
+                                       prediction_type=ptype)
+            st = s.set_timesteps(s.create_state(), 50)
+            save[f"timesteps/{int(one)}"] = np.asarray(st.timesteps)
+            save[f"final/{int(one)}"] = np.asarray(st.final_alpha_cumprod)
+            for ti in (981, 501, 21, 1):
+                for eta in (0.0, 0.5):
+                    out = s.step(st, jnp.asarray(mo), ti, jnp.asarray(smp), eta=eta)
+                    save[f"step/{ptype}/{int(one)}/{ti}/{eta}"] = np.asarray(out.prev_sample)
+                save[f"var/{int(one)}/{ti}"] = np.asarray(s._get_variance(st, ti, ti - 20))
+    return save
+
+
 def main():
     if not os.path.isdir(REF):
         raise SystemExit("make_golden needs /root/reference (build container only)")
@@ -184,7 +214,9 @@ def main():
     np.savez_compressed(os.path.join(OUT, "lion_ref.npz"), **lion)
     sched = sched_cases()
     np.savez_compressed(os.path.join(OUT, "sched_ref.npz"), **sched)
-    print(f"wrote {len(lion)} lion arrays, {len(sched)} scheduler arrays to {OUT}")
+    ddim = ddim_cases()
+    np.savez_compressed(os.path.join(OUT, "ddim_ref.npz"), **ddim)
+    print(f"wrote {len(lion)} lion arrays, {len(sched)} scheduler arrays, {len(ddim)} DDIM arrays to {OUT}")
 
 
 if __name__ == "__main__":

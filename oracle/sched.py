@@ -170,6 +170,44 @@ def ddpm_step(state, model_output, t: int, sample, noise=None, prediction_type="
     return prev.astype(F32)
 
 
+def ddim_variance(state, t: int, prev_t: int, final_alpha_cumprod=F32(1.0)):
+    """scheduling_ddim_flax.py:186-197 (_get_variance), fp32."""
+    ac = state["alphas_cumprod"]
+    ap = ac[t]
+    ap_prev = ac[prev_t] if prev_t >= 0 else F32(final_alpha_cumprod)
+    bp, bp_prev = F32(F32(1) - ap), F32(F32(1) - ap_prev)
+    return F32(F32(bp_prev / bp) * F32(F32(1) - F32(ap / ap_prev)))
+
+
+def ddim_step(state, model_output, t: int, sample, num_inference_steps: int, prediction_type="epsilon", eta=0.0,
+              num_train_timesteps=1000, final_alpha_cumprod=F32(1.0)):
+    """scheduling_ddim_flax.py:199-284: x0 / epsilon from the model output, sigma_t(eta), direction, x_{t-1}. fp32,
+    one rounded op per reference op (x ** 0.5 == correctly rounded sqrt)."""
+    ac = state["alphas_cumprod"]
+    prev_t = t - num_train_timesteps // num_inference_steps
+    ap = ac[t]
+    ap_prev = ac[prev_t] if prev_t >= 0 else F32(final_alpha_cumprod)
+    bp = F32(F32(1) - ap)
+    sa, sb = np.sqrt(ap).astype(F32), np.sqrt(bp).astype(F32)
+    mo, x = model_output.astype(F32), sample.astype(F32)
+    if prediction_type == "epsilon":
+        x0 = ((x - sb * mo) / sa).astype(F32)
+        eps = mo
+    elif prediction_type == "sample":
+        x0 = mo
+        eps = ((x - sa * x0) / sb).astype(F32)
+    elif prediction_type == "v_prediction":
+        x0 = (sa * x - sb * mo).astype(F32)
+        eps = (sa * mo + sb * x).astype(F32)
+    else:
+        raise ValueError(f"prediction_type given as {prediction_type} must be one of `epsilon`, `sample`, or"
+                         " `v_prediction`")
+    var = ddim_variance(state, t, prev_t, final_alpha_cumprod)
+    std = F32(F32(eta) * np.sqrt(var).astype(F32))
+    cdir = np.sqrt(F32(F32(F32(1) - ap_prev) - F32(std * std))).astype(F32)
+    return (np.sqrt(ap_prev).astype(F32) * x0 + cdir * eps).astype(F32)
+
+
 def min_snr_weight(alphas_cumprod, timesteps, gamma: float, v_prediction: bool):
     """training_utils.py:546-568: snr = ac/(1-ac); w = min(snr, gamma)/snr (eps) or /(snr+1) (v)."""
     ac = alphas_cumprod[np.asarray(timesteps)]

@@ -61,6 +61,7 @@ SIGNATURES = {
     "sdb_add_noise": (_I, [_P, _P, _P, _P, _I, _P, _I, _LL, _P]),
     "sdb_get_velocity": (_I, [_P, _P, _P, _P, _I, _P, _I, _LL, _P]),
     "sdb_ddpm_step": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _F, _I, _I, _P]),
+    "sdb_ddim_step": (_I, [_P, _P, _P, _LL, _F, _F, _F, _F, _I, _P]),
     "sdb_mse_workspace_bytes": (_SZ, []),
     "sdb_min_snr_weight": (_I, [_P, _I, _P, _I, _F, _I, _P, _P]),
     "sdb_threefry_bits": (_I, [_U32, _U32, _P, _LL, _LL, _LL, _P]),

@@ -201,6 +201,44 @@ extern "C" int sdb_ddpm_step(const float* model_output, const float* sample, con
   return SDB_OK;
 }
 
+// FlaxDDIMScheduler.step (schedulers/scheduling_ddim_flax.py:199-284), elementwise part; the scalars (alpha / beta products,
+// eta-scaled standard deviation, direction coefficient) are computed by the host in fp32 in the reference's order.
+namespace {
+__global__ void __launch_bounds__(256)
+ddim_step_kernel(const float* __restrict__ model_out, const float* __restrict__ sample, float* __restrict__ prev,
+                 long long n, float sa, float sb, float sa_prev, float cdir, int pred_type) {
+  sdb::pdl_trigger();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float mo = model_out[i], x = sample[i];
+    float x0, eps;
+    if (pred_type == 0) {
+      x0 = __fdiv_rn(__fsub_rn(x, __fmul_rn(sb, mo)), sa);
+      eps = mo;
+    } else if (pred_type == 1) {
+      x0 = mo;
+      eps = __fdiv_rn(__fsub_rn(x, __fmul_rn(sa, x0)), sb);
+    } else {
+      x0 = __fsub_rn(__fmul_rn(sa, x), __fmul_rn(sb, mo));
+      eps = __fadd_rn(__fmul_rn(sa, mo), __fmul_rn(sb, x));
+    }
+    prev[i] = __fadd_rn(__fmul_rn(sa_prev, x0), __fmul_rn(cdir, eps));
+  }
+}
+}  // namespace
+
+extern "C" int sdb_ddim_step(const float* model_output, const float* sample, float* prev_sample, long long n,
+                             float sqrt_alpha_prod, float sqrt_beta_prod, float sqrt_alpha_prod_prev,
+                             float direction_coeff, int prediction_type, cudaStream_t stream) {
+  SDB_CHECK_ARG(prediction_type >= 0 && prediction_type <= 2, "sdb_ddim_step: prediction_type must be 0/1/2");
+  SDB_CHECK_ARG(n > 0, "sdb_ddim_step: n must be positive");
+  ddim_step_kernel<<<grid_cap(n, 256, 8), 256, 0, stream>>>(model_output, sample, prev_sample, n, sqrt_alpha_prod,
+                                                           sqrt_beta_prod, sqrt_alpha_prod_prev, direction_coeff,
+                                                           prediction_type);
+  SDB_CUDA_LAUNCH_CHECK("sdb_ddim_step");
+  return SDB_OK;
+}
+
 extern "C" size_t sdb_mse_workspace_bytes(void) { return sizeof(double) * kMseBlocks; }
 
 extern "C" int sdb_mse_fwd_bwd(const void* pred_nhwc_bf16, const float* target_nchw, const float* sample_weight,

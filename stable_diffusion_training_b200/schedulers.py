@@ -271,3 +271,119 @@ class FlaxDDPMScheduler:
 
     def __len__(self):
         return self.config.num_train_timesteps
+
+
+# ---------------------------------------------------------------------------------------------------------------
+@dataclass(frozen=True)
+class DDIMSchedulerState:
+    """schedulers/scheduling_ddim_flax.py:36-57."""
+    common: CommonSchedulerState
+    final_alpha_cumprod: torch.Tensor
+    init_noise_sigma: torch.Tensor
+    timesteps: torch.Tensor
+    num_inference_steps: Optional[int] = None
+
+    @classmethod
+    def create(cls, common, final_alpha_cumprod, init_noise_sigma, timesteps):
+        return cls(common=common, final_alpha_cumprod=final_alpha_cumprod, init_noise_sigma=init_noise_sigma,
+                   timesteps=timesteps)
+
+    def replace(self, **kw):
+        return dataclasses.replace(self, **kw)
+
+
+@dataclass
+class FlaxDDIMSchedulerOutput(FlaxSchedulerOutput):
+    state: DDIMSchedulerState
+
+
+class FlaxDDIMScheduler:
+    """schedulers/scheduling_ddim_flax.py:66-305 — the scheduler the reference writes into saved pipelines
+    (training_utils.py:997-1004) and the one its validation sampling uses. Same constructor, state and methods; the
+    elementwise part of step() is sdb_ddim_step, the scalars are fp32 host arithmetic in the reference's order."""
+
+    has_state = True
+
+    def __init__(self, num_train_timesteps: int = 1000, beta_start: float = 0.0001, beta_end: float = 0.02,
+                 beta_schedule: str = "linear", trained_betas=None, set_alpha_to_one: bool = True,
+                 steps_offset: int = 0, prediction_type: str = "epsilon", dtype=torch.float32, device="cuda"):
+        if dtype not in (torch.float32, "float32"):
+            raise NotImplementedError("FlaxDDIMScheduler: only dtype float32 (the reference default) is built")
+        self.dtype = torch.float32
+        self.device = torch.device(device)
+        self.config = SimpleNamespace(num_train_timesteps=num_train_timesteps, beta_start=beta_start, beta_end=beta_end,
+                                      beta_schedule=beta_schedule, trained_betas=trained_betas,
+                                      set_alpha_to_one=set_alpha_to_one, steps_offset=steps_offset,
+                                      prediction_type=prediction_type)
+        self._host = None
+
+    def create_state(self, common: Optional[CommonSchedulerState] = None) -> DDIMSchedulerState:
+        if common is None:
+            common = CommonSchedulerState.create(self)
+        final = torch.tensor(1.0, dtype=self.dtype, device=self.device) if self.config.set_alpha_to_one \
+            else common.alphas_cumprod[0]
+        init_noise_sigma = torch.tensor(1.0, dtype=self.dtype, device=self.device)
+        timesteps = torch.arange(0, self.config.num_train_timesteps, device=self.device).flip(0)
+        return DDIMSchedulerState.create(common=common, final_alpha_cumprod=final, init_noise_sigma=init_noise_sigma,
+                                         timesteps=timesteps)
+
+    def scale_model_input(self, state, sample, timestep: Optional[int] = None):
+        return sample
+
+    def set_timesteps(self, state: DDIMSchedulerState, num_inference_steps: int, shape: Tuple = ()):
+        step_ratio = self.config.num_train_timesteps // num_inference_steps
+        timesteps = (torch.arange(0, num_inference_steps, device=self.device) * step_ratio).flip(0) \
+            + self.config.steps_offset
+        return state.replace(num_inference_steps=num_inference_steps, timesteps=timesteps)
+
+    def _tables(self, state):
+        if self._host is None or self._host[0] is not state:
+            self._host = (state, state.common.alphas_cumprod.cpu().numpy(),
+                          _F(state.final_alpha_cumprod.cpu().numpy()))
+        return self._host[1], self._host[2]
+
+    def _alpha_pair(self, state, timestep: int, prev_timestep: int):
+        ac, final = self._tables(state)
+        n = ac.shape[0]
+        idx = lambda t: min(max(t + n if t < 0 else t, 0), n - 1)  # jnp gather: wrap a negative index once, clamp
+        return ac[idx(timestep)], (ac[idx(prev_timestep)] if prev_timestep >= 0 else final)
+
+    def _get_variance(self, state, timestep: int, prev_timestep: int):
+        a_t, a_prev = self._alpha_pair(state, int(timestep), int(prev_timestep))
+        beta_t, beta_prev = _F(_F(1) - a_t), _F(_F(1) - a_prev)
+        return _F(_F(beta_prev / beta_t) * _F(_F(1) - _F(a_t / a_prev)))
+
+    def step(self, state: DDIMSchedulerState, model_output, timestep: int, sample, eta: float = 0.0,
+             return_dict: bool = True):
+        if state.num_inference_steps is None:
+            raise ValueError("Number of inference steps is 'None', you need to run 'set_timesteps' after creating "
+                             "the scheduler")
+        ptype = self.config.prediction_type
+        if ptype not in ("epsilon", "sample", "v_prediction"):
+            raise ValueError(f"prediction_type given as {ptype} must be one of `epsilon`, `sample`, or `v_prediction`")
+        t = int(timestep)
+        prev_t = t - self.config.num_train_timesteps // state.num_inference_steps
+        a_t, a_prev = self._alpha_pair(state, t, prev_t)
+        beta_t = _F(_F(1) - a_t)
+        variance = self._get_variance(state, t, prev_t)
+        std = _F(_F(eta) * _F(np.sqrt(variance)))
+        cdir = _F(np.sqrt(_F(_F(_F(1) - a_prev) - _F(std * std))))
+        model_output = _as_f32(model_output, self.device, "FlaxDDIMScheduler.step")
+        sample = _as_f32(sample, self.device, "FlaxDDIMScheduler.step")
+        prev = torch.empty_like(sample)
+        _lib.check(_lib.lib().sdb_ddim_step(model_output.data_ptr(), sample.data_ptr(), prev.data_ptr(), sample.numel(),
+                                            float(np.sqrt(a_t)), float(np.sqrt(beta_t)), float(np.sqrt(a_prev)),
+                                            float(cdir), ("epsilon", "sample", "v_prediction").index(ptype),
+                                            _lib.stream_ptr(self.device)), "sdb_ddim_step")
+        if not return_dict:
+            return (prev, state)
+        return FlaxDDIMSchedulerOutput(prev_sample=prev, state=state)
+
+    def add_noise(self, state: DDIMSchedulerState, original_samples, noise, timesteps):
+        return add_noise_common(state.common, original_samples, noise, timesteps)
+
+    def get_velocity(self, state: DDIMSchedulerState, sample, noise, timesteps):
+        return get_velocity_common(state.common, sample, noise, timesteps)
+
+    def __len__(self):
+        return self.config.num_train_timesteps

@@ -118,3 +118,29 @@ def test_ddpm_step(cuda, ptype, vt):
         out = s.step(st, mo, t, smp, key=vn)
         assert np.array_equal(_bits(_np(out.prev_sample)), _bits(z[f"step/{ptype}/{vt}/{t}"])), (ptype, vt, t)
         assert np.array_equal(_bits(np.float32(s._get_variance(st, t))), _bits(z[f"var/{vt}/{t}"]))
+
+
+@pytest.mark.parametrize("ptype", ["epsilon", "sample", "v_prediction"])
+@pytest.mark.parametrize("one", [True, False])
+def test_ddim_scheduler_matches_reference_run(cuda, ptype, one):
+    """FlaxDDIMScheduler (sdb_ddim_step) == tests/golden/ddim_ref.npz, the output of the unmodified
+    schedulers/scheduling_ddim_flax.py: create_state / set_timesteps / _get_variance / step, bit for bit."""
+    from stable_diffusion_training_b200.schedulers import FlaxDDIMScheduler
+    z = np.load(os.path.join(G, "ddim_ref.npz"))
+    s = FlaxDDIMScheduler(beta_start=0.00085, beta_end=0.012, beta_schedule="scaled_linear", num_train_timesteps=1000,
+                          set_alpha_to_one=one, steps_offset=1, prediction_type=ptype, device=cuda)
+    st0 = s.create_state()
+    mo, smp = torch.from_numpy(z["model_output"]).to(cuda), torch.from_numpy(z["sample"]).to(cuda)
+    with pytest.raises(ValueError):
+        s.step(st0, mo, 981, smp)
+    st = s.set_timesteps(st0, 50)
+    assert np.array_equal(_np(st.timesteps), z[f"timesteps/{int(one)}"])
+    assert np.array_equal(_bits(_np(st.final_alpha_cumprod)), _bits(z[f"final/{int(one)}"]))
+    assert len(s) == 1000 and s.scale_model_input(st, smp) is smp
+    for ti in (981, 501, 21, 1):
+        assert np.array_equal(_bits(s._get_variance(st, ti, ti - 20)), _bits(z[f"var/{int(one)}/{ti}"]))
+        for eta in (0.0, 0.5):
+            out = s.step(st, mo, ti, smp, eta=eta)
+            assert np.array_equal(_bits(_np(out.prev_sample)), _bits(z[f"step/{ptype}/{int(one)}/{ti}/{eta}"])), (ti, eta)
+    prev, st2 = s.step(st, mo, 501, smp, return_dict=False)
+    assert st2 is st and prev.shape == smp.shape

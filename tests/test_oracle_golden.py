@@ -130,3 +130,23 @@ def test_ddpm_step(sched, ptype, vt):
 def test_set_timesteps(sched):
     assert np.array_equal(sched["set_timesteps_50"], (np.arange(50) * 20)[::-1])
     assert int(sched["len"]) == 1000
+
+
+@pytest.mark.parametrize("ptype", ["epsilon", "sample", "v_prediction"])
+@pytest.mark.parametrize("one", [True, False])
+def test_ddim_step_bit_exact(ptype, one):
+    """oracle/sched.py:ddim_step == the UNMODIFIED schedulers/scheduling_ddim_flax.py:199-284 run under the shim
+    (tests/golden/ddim_ref.npz), bit for bit: 3 prediction types, set_alpha_to_one on / off, eta 0 and 0.5, first / middle /
+    last steps of a 50-step schedule with steps_offset 1."""
+    z = np.load(os.path.join(G, "ddim_ref.npz"))
+    st = OS.common_state("scaled_linear", 0.00085, 0.012)
+    final = np.float32(1.0) if one else st["alphas_cumprod"][0]
+    assert z[f"final/{int(one)}"] == final
+    assert np.array_equal(z[f"timesteps/{int(one)}"], (np.arange(50) * 20)[::-1] + 1)
+    for ti in (981, 501, 21, 1):
+        assert _bits(OS.ddim_variance(st, ti, ti - 20, final)) == _bits(z[f"var/{int(one)}/{ti}"])
+        for eta in (0.0, 0.5):
+            got = OS.ddim_step(st, z["model_output"], ti, z["sample"], 50, prediction_type=ptype, eta=eta,
+                               final_alpha_cumprod=final)
+            want = z[f"step/{ptype}/{int(one)}/{ti}/{eta}"]
+            assert np.array_equal(_bits(got), _bits(want)), (ptype, one, ti, eta)
