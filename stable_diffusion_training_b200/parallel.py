@@ -26,7 +26,7 @@ from typing import Dict, List, Optional, Sequence, Tuple
 import torch
 import torch.distributed as dist
 
-DEFAULT_BUCKET_BYTES = int(os.environ.get("SDB_DP_BUCKET_MB", "64")) << 20
+DEFAULT_BUCKET_BYTES = int(os.environ.get("SDB_DP_BUCKET_MB", "256")) << 20  # r4h: 8 GPUs 43.4 ms (256 MB) vs 45.8 (64 MB)
 
 
 class NcclComm:
