@@ -253,6 +253,32 @@ int sdb_attn_bwd(const void* q, long long ldq, const void* k, long long ldk, con
                  long long lddq, void* dk, long long lddk, void* dv, long long lddv, int B, int H, int Sq, int Skv, int d,
                  float scale, void* workspace, size_t ws_bytes, cudaStream_t stream);
 
+/* ---- text encoder (FlaxCLIPTextModel [transformers, third-party], loaded at training_utils.py:215-217, called at
+ * 635-640; context assembly 641-674). GEMMs / LayerNorm / bias gradients reuse the entry points above. ----
+ * Embeddings: out[r, :] = bf16(token[ids[r], :] + position[r % seq_len, :]) over bf16 tables; the backward zeroes
+ * dtoken (vocab x hidden fp32) itself, adds the rows with fp32 atomics and writes dposition (fixed-order sums). */
+int sdb_embed_fwd(const int* input_ids, const void* token_embedding_bf16, const void* position_embedding_bf16,
+                  void* out_bf16, int rows, int seq_len, int hidden, int vocab, cudaStream_t stream);
+int sdb_embed_bwd(const int* input_ids, const void* dout_bf16, float* dtoken_embedding, float* dposition_embedding,
+                  int rows, int seq_len, int hidden, int vocab, cudaStream_t stream);
+/* Attention over short sequences (S <= 128, d <= 128, d % 8 == 0), optional causal mask (FlaxCLIPAttention): q / k / v /
+ * o are [N * S, ld] bf16 matrices with the H heads side by side in the columns; lse fp32 [N][H][S] (natural log). */
+int sdb_attn_small_fwd(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv, void* o,
+                       long long ldo, float* lse, int N, int H, int S, int d, float scale, int causal,
+                       cudaStream_t stream);
+int sdb_attn_small_bwd(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv,
+                       const void* o, long long ldo, const void* dO, long long lddo, const float* lse, void* dq,
+                       long long lddq, void* dk, long long lddk, void* dv, long long lddv, int N, int H, int S, int d,
+                       float scale, int causal, cudaStream_t stream);
+/* ACT2FN[hidden_act] of FlaxCLIPMLP: kind 0 = quick_gelu (z * sigmoid(1.702 z)), 1 = gelu (erf). bf16 in / out. */
+int sdb_act_fwd(const void* x, void* y, long long n, int kind, cudaStream_t stream);
+int sdb_act_bwd(const void* x, const void* dy, void* dx, long long n, int kind, cudaStream_t stream);
+/* Context assembly (training_utils.py:641-674) as a row gather: scatter_out_rows == 0: out[r, :] = src[row_index[r], :]
+ * for r < rows; scatter_out_rows > 0 (the adjoint): out is a [scatter_out_rows, cols] matrix that the call zeroes, then
+ * out[row_index[r], :] = src[r, :] (every index used at most once). */
+int sdb_gather_rows_bf16(const void* src, const int* row_index, void* out, long long rows, int cols,
+                         long long scatter_out_rows, cudaStream_t stream);
+
 /* ---- data movement / small elementwise pieces of the UNet graph (FlaxUpsample2D nearest resize, skip-connection
  * concatenate, FlaxTimesteps sinusoid, silu(temb), NCHW->NHWC entry transpose [upstream diffusers 0.21.4]) ---- */
 int sdb_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream);

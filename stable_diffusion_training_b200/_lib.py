@@ -86,6 +86,14 @@ SIGNATURES = {
     "sdb_attn_bwd_workspace_bytes": (_SZ, [_I, _I, _I]),
     "sdb_attn_bwd": (_I, [_P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _P, _P, _LL, _P, _LL, _P, _LL, _I, _I, _I,
                           _I, _I, _F, _P, _SZ, _P]),
+    "sdb_embed_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "sdb_embed_bwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "sdb_attn_small_fwd": (_I, [_P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _I, _I, _I, _I, _F, _I, _P]),
+    "sdb_attn_small_bwd": (_I, [_P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _LL, _P, _P, _LL, _P, _LL, _P, _LL, _I, _I, _I,
+                                _I, _F, _I, _P]),
+    "sdb_act_fwd": (_I, [_P, _P, _LL, _I, _P]),
+    "sdb_act_bwd": (_I, [_P, _P, _P, _LL, _I, _P]),
+    "sdb_gather_rows_bf16": (_I, [_P, _P, _P, _LL, _I, _LL, _P]),
     "sdb_cast_f32_bf16": (_I, [_P, _P, _LL, _P]),
     "sdb_nchw_f32_to_nhwc_bf16": (_I, [_P, _P, _I, _I, _I, _P]),
     "sdb_nhwc_bf16_to_nchw_f32": (_I, [_P, _P, _I, _I, _I, _P]),

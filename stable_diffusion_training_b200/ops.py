@@ -671,3 +671,77 @@ def timestep_embedding(t, dim: int, flip_sin_to_cos: bool = True, freq_shift: fl
     _lib.check(_L().sdb_timestep_embedding(t.data_ptr(), out.data_ptr(), t.shape[0], dim, int(flip_sin_to_cos),
                                            freq_shift, _lib.stream_ptr()), "sdb_timestep_embedding")
     return out
+
+
+# ---- text encoder (csrc/clip.cu) -----------------------------------------------------------------------------------
+def embed_fwd(input_ids, tok_w, pos_w):
+    """input_ids int32 [N, S]; tok_w bf16 [vocab, D]; pos_w bf16 [>= S, D] -> bf16 [N * S, D]."""
+    N, S = input_ids.shape
+    D = tok_w.shape[1]
+    out = torch.empty((N * S, D), device=tok_w.device, dtype=BF16)
+    _lib.check(_L().sdb_embed_fwd(input_ids.data_ptr(), tok_w.data_ptr(), pos_w.data_ptr(), out.data_ptr(), N * S, S, D,
+                                  tok_w.shape[0], _lib.stream_ptr()), "sdb_embed_fwd")
+    return out
+
+
+def embed_bwd(input_ids, dout, dtok, dpos):
+    N, S = input_ids.shape
+    D = dout.shape[1]
+    _lib.check(_L().sdb_embed_bwd(input_ids.data_ptr(), dout.data_ptr(), dtok.data_ptr(), dpos.data_ptr(), N * S, S, D,
+                                  dtok.shape[0], _lib.stream_ptr()), "sdb_embed_bwd")
+
+
+def attention_small_fwd(q, k, v, N: int, heads: int, scale: float, causal: bool):
+    """q / k / v bf16 [N * S, C] (column slices allowed) -> (o [N * S, C], lse [N, heads, S])."""
+    C_ = q.shape[1]
+    S = q.shape[0] // N
+    o = torch.empty((N * S, C_), device=q.device, dtype=BF16)
+    lse = torch.empty((N, heads, S), device=q.device, dtype=torch.float32)
+    _lib.check(_L().sdb_attn_small_fwd(q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+                                       o.data_ptr(), o.stride(0), lse.data_ptr(), N, heads, S, C_ // heads, scale,
+                                       int(causal), _lib.stream_ptr()), "sdb_attn_small_fwd")
+    return o, lse
+
+
+def attention_small_bwd(q, k, v, o, dO, lse, N: int, heads: int, scale: float, causal: bool):
+    C_ = q.shape[1]
+    S = q.shape[0] // N
+    dq, dk, dv = (torch.empty((N * S, C_), device=q.device, dtype=BF16) for _ in range(3))
+    _lib.check(_L().sdb_attn_small_bwd(q.data_ptr(), q.stride(0), k.data_ptr(), k.stride(0), v.data_ptr(), v.stride(0),
+                                       o.data_ptr(), o.stride(0), dO.data_ptr(), dO.stride(0), lse.data_ptr(),
+                                       dq.data_ptr(), dq.stride(0), dk.data_ptr(), dk.stride(0), dv.data_ptr(),
+                                       dv.stride(0), N, heads, S, C_ // heads, scale, int(causal), _lib.stream_ptr()),
+               "sdb_attn_small_bwd")
+    return dq, dk, dv
+
+
+ACT_KINDS = {"quick_gelu": 0, "gelu": 1}
+
+
+def act_fwd(x, kind: str):
+    y = torch.empty_like(x)
+    _lib.check(_L().sdb_act_fwd(x.data_ptr(), y.data_ptr(), x.numel(), ACT_KINDS[kind], _lib.stream_ptr()), "sdb_act_fwd")
+    return y
+
+
+def act_bwd(x, dy, kind: str):
+    dx = torch.empty_like(x)
+    _lib.check(_L().sdb_act_bwd(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), x.numel(), ACT_KINDS[kind],
+                                _lib.stream_ptr()), "sdb_act_bwd")
+    return dx
+
+
+def gather_rows(src2d, row_index, rows_out: int):
+    """out[r, :] = src[row_index[r], :] (bf16, contiguous)."""
+    out = torch.empty((rows_out, src2d.shape[1]), device=src2d.device, dtype=BF16)
+    _lib.check(_L().sdb_gather_rows_bf16(src2d.data_ptr(), row_index.data_ptr(), out.data_ptr(), rows_out,
+                                         src2d.shape[1], 0, _lib.stream_ptr()), "sdb_gather_rows_bf16")
+    return out
+
+
+def scatter_rows(dout2d, row_index, rows_src: int):
+    """Adjoint of gather_rows: dsrc zero except dsrc[row_index[r], :] = dout[r, :] (the call zeroes dsrc itself)."""
+    dsrc = torch.empty((rows_src, dout2d.shape[1]), device=dout2d.device, dtype=BF16)
+    _lib.check(_L().sdb_gather_rows_bf16(dout2d.data_ptr(), row_index.data_ptr(), dsrc.data_ptr(), dout2d.shape[0],
+                                         dout2d.shape[1], rows_src, _lib.stream_ptr()), "sdb_gather_rows_bf16")
+    return dsrc

@@ -324,6 +324,14 @@ class GradReducer:
         if self.capture is not None:
             self.capture(True)  # the replayer reduces the remaining buckets and the loss, then joins the streams
             return loss
+        if loss is None:  # a second model's gradients (the text encoder): buckets only
+            if self.world_size > 1 and self.cuda:
+                ev = torch.cuda.Event()
+                ev.record(torch.cuda.current_stream(self.grad.device))
+                self.comm_stream.wait_event(ev)
+                self._peer_finish()
+                torch.cuda.current_stream(self.grad.device).wait_stream(self.comm_stream)
+            return None
         if self.world_size > 1:
             if self.cuda:
                 ev = torch.cuda.Event()

@@ -35,7 +35,8 @@ from . import jax_random as JR
 from . import lion_quant as LQ
 from .lion_quant import create_mask, flatten_dict, unflatten_dict
 from .schedulers import FlaxDDPMScheduler
-from .unet import SD15, UNet, UNetConfig, init_params_numpy, layer_program, param_shapes
+from . import clip as CL
+from .unet import SD15, T, UNet, UNetConfig, init_params_numpy, layer_program, param_shapes
 
 
 @dataclass
@@ -269,24 +270,27 @@ class TrainState:
     def create(cls, *, apply_fn, params: dict, tx: LQ.GradientTransformation, device="cuda",
                reference_attention_quirk: bool = True) -> "TrainState":
         model = getattr(apply_fn, "__self__", None)
-        if not isinstance(model, UNetModel):
-            raise TypeError("TrainState.create: apply_fn must be UNetModel(...).apply")
+        is_text = isinstance(model, CL.CLIPTextModel)
+        if not isinstance(model, UNetModel) and not is_text:
+            raise TypeError("TrainState.create: apply_fn must be UNetModel(...).apply or CLIPTextModel(...).__call__")
         cfg = model.config
         flat = flatten_dict(params)
-        shapes = param_shapes(cfg)
+        shapes = CL.param_shapes(cfg) if is_text else param_shapes(cfg)
         if set(flat) != set(shapes):
             missing = sorted(set(shapes) - set(flat))[:3]
             extra = sorted(set(flat) - set(shapes))[:3]
-            raise ValueError(f"params do not match the UNet config (missing {missing}, unexpected {extra})")
+            raise ValueError(f"params do not match the model config (missing {missing}, unexpected {extra})")
         hyper = _parse_chain(tx.hyper)
         ones = {n: True for n in shapes}
         quant = flatten_dict(LQ._expand_mask(hyper["excluded_layer_mask"], params)) if hyper["quantize"] else \
             {n: False for n in shapes}
         decay = flatten_dict(LQ._expand_mask(hyper["mask"], params)) if hyper["mask"] is not None else ones
-        arena = ParamArena(shapes, quant, decay, backward_param_order(cfg), device, hyper["block_size"])
+        order = CL.backward_param_order(cfg) if is_text else backward_param_order(cfg)
+        arena = ParamArena(shapes, quant, decay, order, device, hyper["block_size"])
         arena.load(flat)
         tree = unflatten_dict(arena.p)
-        net = UNet(cfg, arena.p, arena.w, arena.g, reference_attention_quirk)
+        net = CL.ClipText(cfg, arena.p, arena.w, arena.g) if is_text else \
+            UNet(cfg, arena.p, arena.w, arena.g, reference_attention_quirk)
         dev = arena.device
         lion_state = LQ.ScaleBy8bitLionState(count=torch.zeros([], dtype=torch.int32, device=dev),
                                              mu_quant=arena.mu_quant_tree(),
@@ -394,7 +398,18 @@ def _check_rng(rng, return_rng: bool, what: str) -> None:
                          "(training_utils.py:530, 755-762) or pass a jax_random.RngStream")
 
 
+_CTX_INDEX: Dict[tuple, torch.Tensor] = {}
+
+
+def _context_index(device, batch: int, chunks: int, strip: bool) -> torch.Tensor:
+    key = (str(device), batch, chunks, strip)
+    if key not in _CTX_INDEX:
+        _CTX_INDEX[key] = torch.from_numpy(CL.context_row_index(batch, chunks, strip).reshape(-1).copy()).to(device)
+    return _CTX_INDEX[key]
+
+
 def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
+               text_encoder_state: Optional[TrainState] = None, strip_bos_eos_token: bool = True,
                unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
                min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0, ema_rate: float = 0.0,
                return_rng: bool = False):
@@ -403,6 +418,10 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
     inputs of any width are promoted to fp32 like jnp would). Whatever the batch does not supply is drawn from `rng`
     exactly as the reference draws it (split(train_rng, 3) / split(sample_rng, 4), jax.random.normal / randint; offset
     and perturbation noise apply to drawn noise only, as in the reference).
+    With `text_encoder_state` (a TrainState over clip.CLIPTextModel, training_utils.py:389-425) the batch carries
+    "input_ids" int [B * chunks, 77] instead of "encoder_hidden_states": the text encoder runs inside the step, its
+    hidden states are assembled into the context as the reference does (641-674, `strip_bos_eos_token`), the UNet's
+    context gradient flows back through it and both optimizers step (732-733); that state is donated too.
     Returns (state, {"loss": 0-d device tensor}) and, with return_rng=True, new_train_rng as third element. `state`
     and `unet_ema_params` (state.create_ema(); updated when ema_rate != 0, training_utils.py:735-739) are donated.
     Raises ValueError for an unknown prediction type (training_utils.py:697-701)."""
@@ -449,9 +468,25 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
         weight = min_snr_weight(sstate.common.alphas_cumprod, timesteps, float(min_snr_gamma_magnitude),
                                 ptype == "v_prediction")
     x = ops.nchw_to_nhwc_bf16(noisy)
-    ctx = batch["encoder_hidden_states"]
-    if ctx.dtype != torch.bfloat16:
-        ctx = ops.cast_bf16(ctx.to(torch.float32).contiguous())
+    tnet = None
+    if text_encoder_state is not None:
+        if not isinstance(text_encoder_state.net, CL.ClipText):
+            raise TypeError("train_step: text_encoder_state must be a TrainState over clip.CLIPTextModel")
+        ids = batch["input_ids"]
+        if ids.device != dev:
+            raise ValueError(f"train_step: batch['input_ids'] is on {ids.device}, the state on {dev}")
+        ids = ids.to(torch.int32).contiguous().view(-1, ids.shape[-1])
+        if ids.shape[0] % B != 0 or ids.shape[1] != 77:
+            raise ValueError(f"train_step: input_ids {tuple(ids.shape)} must be [B * chunks, 77] with B = {B}")
+        tnet = text_encoder_state.net
+        hidden = tnet.forward(ids)                                            # training_utils.py:635-640
+        idx = _context_index(dev, B, ids.shape[0] // B, bool(strip_bos_eos_token))
+        ctx_t = tnet.graph.gather_rows(hidden, idx)                            # training_utils.py:641-674
+        ctx = (ctx_t, B)
+    else:
+        ctx = batch["encoder_hidden_states"]
+        if ctx.dtype != torch.bfloat16:
+            ctx = ops.cast_bf16(ctx.to(torch.float32).contiguous())
 
     net = state.net
     on_grad = state.dp.on_param_grad if state.dp is not None else None
@@ -463,6 +498,15 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
     net.backward(pred, dpred, on_grad)
     if state.dp is not None:
         loss = state.dp.finish(loss)
+    if tnet is not None:  # the text encoder's backward starts from the context gradient the UNet left in ctx_t.g
+        tdp = text_encoder_state.dp
+        if tdp is not None:
+            tdp.begin(tnet.graph)
+            tdp.before_issue = tnet.graph.join
+        tnet.backward(tdp.on_param_grad if tdp is not None else None)
+        if tdp is not None:
+            tdp.finish(None)
+        text_encoder_state.apply_gradients(grads=None)
     fused_ema = bool(ema_rate) and unet_ema_params is not None and unet_ema_params is state.ema_params
     state.apply_gradients(grads=None, ema_rate=float(ema_rate) if fused_ema else 0.0)
     if ema_rate and unet_ema_params is not None and not fused_ema:
@@ -521,9 +565,16 @@ class CompiledTrainStep:
     futures: the host blocks only when it reads it)."""
 
     def __init__(self, state: TrainState, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
+                 text_encoder_state: Optional[TrainState] = None, strip_bos_eos_token: bool = True,
                  unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
                  min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0,
                  ema_rate: float = 0.0):
+        self.text_state = text_encoder_state
+        self.strip = bool(strip_bos_eos_token)
+        if text_encoder_state is not None:
+            tlr = text_encoder_state.hyper["learning_rate"]
+            if callable(tlr) and tlr(0) != tlr(1_000_000):
+                raise NotImplementedError("CompiledTrainStep: only a constant learning-rate schedule can be baked in")
         lr = state.hyper["learning_rate"]
         if callable(lr) and lr(0) != lr(1_000_000):
             # the learning rate is a kernel argument baked into the graph; the reference only ever uses
@@ -542,7 +593,8 @@ class CompiledTrainStep:
         self.launches_per_replay = 0
 
     def _flags(self) -> dict:
-        return dict(unet_ema_params=self.ema_params, ema_rate=self.ema_rate, min_snr_gamma_magnitude=self.min_snr)
+        return dict(unet_ema_params=self.ema_params, ema_rate=self.ema_rate, min_snr_gamma_magnitude=self.min_snr,
+                    text_encoder_state=self.text_state, strip_bos_eos_token=self.strip)
 
     def _eager(self, batch, rng, return_rng):
         return train_step(self.state, batch, rng, self.sched, offset_noise_magnitude=self.offset,
@@ -552,7 +604,8 @@ class CompiledTrainStep:
         """Copy / draw the step's inputs into the graph's static buffers (outside the graph). Returns new_train_rng."""
         buf = e["buf"]
         buf["latents"].copy_(batch["latents"], non_blocking=True)
-        buf["encoder_hidden_states"].copy_(batch["encoder_hidden_states"], non_blocking=True)
+        cond = "input_ids" if self.text_state is not None else "encoder_hidden_states"
+        buf[cond].copy_(batch[cond], non_blocking=True)
         have_n, have_t = batch.get("noise") is not None, batch.get("timesteps") is not None
         if have_n:
             buf["noise"].copy_(batch["noise"], non_blocking=True)
@@ -574,7 +627,8 @@ class CompiledTrainStep:
     def __call__(self, state: TrainState, batch: dict, rng=None, return_rng: bool = False):
         if state is not self.state:
             raise ValueError("CompiledTrainStep: called with a different TrainState than it was compiled for")
-        key = (tuple(batch["latents"].shape), tuple(batch["encoder_hidden_states"].shape))
+        cond = "input_ids" if self.text_state is not None else "encoder_hidden_states"
+        key = (tuple(batch["latents"].shape), tuple(batch[cond].shape))
         e = self._entries.get(key)
         if e is None:
             self._entries[key] = {"graph": None}
@@ -584,8 +638,8 @@ class CompiledTrainStep:
             e["buf"] = {"latents": torch.empty(key[0], dtype=torch.float32, device=dev),
                         "noise": torch.empty(key[0], dtype=torch.float32, device=dev),
                         "timesteps": torch.empty((key[0][0],), dtype=torch.int32, device=dev),
-                        "encoder_hidden_states": torch.empty(key[1], dtype=batch["encoder_hidden_states"].dtype,
-                                                             device=dev)}
+                        cond: torch.empty(key[1], dtype=torch.int32 if cond == "input_ids" else batch[cond].dtype,
+                                          device=dev)}
             new_rng = self._fill(e, batch, rng, return_rng)
             ops.freeze_workspaces()  # the graphs bake the scratch pointers: growth would leave them dangling
             self._capture(e)
@@ -630,6 +684,9 @@ class CompiledTrainStep:
         # stream by events, joined before the optimizer): ONE graph per step. Otherwise (SDB_DP_NCCL=torch) the step is
         # cut into segments and the collectives are issued eagerly between their replays.
         one_graph = dp is None or dp.world_size == 1 or (dp.graph_capturable and os.environ.get("SDB_DP_SEGMENTS") != "1")
+        if self.text_state is not None and not one_graph:
+            raise NotImplementedError("CompiledTrainStep: a trained text encoder under data parallelism needs the "
+                                      "capturable collectives (peer-memory or direct NCCL), not graph segments")
         with torch.cuda.stream(stream):
             if dp is not None and not one_graph:
                 dp.capture = cut

@@ -520,7 +520,11 @@ class UNet:
         self.graph = g
         B, H, W, Cin = sample_nhwc.shape
         x = T(sample_nhwc.view(-1, Cin), (B, H, W), rg=False)
-        ctx = T(context.view(-1, context.shape[-1]), None, rg=False)
+        if isinstance(context, tuple):   # (T [B * L, D] produced by a trained text encoder, B): its gradient is wanted
+            ctx = context[0]
+            assert ctx.v.dim() == 2 and ctx.v.shape[0] % context[1] == 0
+        else:
+            ctx = T(context.view(-1, context.shape[-1]), None, rg=False)
         emb = T(ops.timestep_embedding(timesteps, cfg.block_out_channels[0], cfg.flip_sin_to_cos,
                                        float(cfg.freq_shift)), None, rg=False)
         temb = g.linear(g.silu(g.linear(emb, "time_embedding/linear_1")), "time_embedding/linear_2")
