@@ -261,7 +261,8 @@ int sdb_embed_fwd(const int* input_ids, const void* token_embedding_bf16, const 
                   void* out_bf16, int rows, int seq_len, int hidden, int vocab, cudaStream_t stream);
 int sdb_embed_bwd(const int* input_ids, const void* dout_bf16, float* dtoken_embedding, float* dposition_embedding,
                   int rows, int seq_len, int hidden, int vocab, cudaStream_t stream);
-/* Attention over short sequences (S <= 128, d <= 128, d % 8 == 0), optional causal mask (FlaxCLIPAttention): q / k / v /
+/* Attention over short sequences (S <= 128, d <= 128, d % 8 == 0; the backward keeps q, k, v, dO, P and dS of one head in
+ * shared memory: (4 S (d + 1) + 2 S (S + 1)) * 4 B <= 227 KB, e.g. S = 77 with d = 64), optional causal mask (FlaxCLIPAttention): q / k / v /
  * o are [N * S, ld] bf16 matrices with the H heads side by side in the columns; lse fp32 [N][H][S] (natural log). */
 int sdb_attn_small_fwd(const void* q, long long ldq, const void* k, long long ldk, const void* v, long long ldv, void* o,
                        long long ldo, float* lse, int N, int H, int S, int d, float scale, int causal,
