@@ -280,6 +280,18 @@ int sdb_act_bwd(const void* x, const void* dy, void* dx, long long n, int kind, 
 int sdb_gather_rows_bf16(const void* src, const int* row_index, void* out, long long rows, int cols,
                          long long scatter_out_rows, cudaStream_t stream);
 
+/* ---- frozen VAE encode (diffusers-0.21.4 FlaxAutoencoderKL.encode [third-party], training_utils.py:574-586): convs /
+ * GroupNorm reuse the entry points above; these are the extra pieces. */
+int sdb_nchw_f32_to_nhwc_bf16_pad(const float* src, void* dst, int B, int C, int Cpad, int HW, cudaStream_t stream);
+/* out[r, :cols] = softmax(scale * x[r, :cols]) (bf16 rows, row stride ld, fp32 statistics): the encoder mid block's
+ * single-head attention over H*W tokens with head dim 512 runs as GEMM -> this -> GEMM. */
+int sdb_softmax_rows_bf16(const void* x, void* out, long long rows, int cols, long long ld, float scale,
+                          cudaStream_t stream);
+/* FlaxDiagonalGaussianDistribution.sample + the 0.18215 scaling: latents NCHW fp32 = (mean + exp(0.5 clip(logvar, -30,
+ * 20)) * eps) * scaling; moments NHWC bf16 [B, HW, 2 L] = (mean | logvar), eps fp32 NHWC [B, HW, L] (NULL: the mode). */
+int sdb_vae_sample(const void* moments_nhwc_bf16, const float* eps_nhwc, float* latents_nchw, int B, int latent_channels,
+                   int HW, float scaling, cudaStream_t stream);
+
 /* ---- data movement / small elementwise pieces of the UNet graph (FlaxUpsample2D nearest resize, skip-connection
  * concatenate, FlaxTimesteps sinusoid, silu(temb), NCHW->NHWC entry transpose [upstream diffusers 0.21.4]) ---- */
 int sdb_cast_f32_bf16(const float* src, void* dst, long long n, cudaStream_t stream);

@@ -94,6 +94,9 @@ SIGNATURES = {
     "sdb_act_fwd": (_I, [_P, _P, _LL, _I, _P]),
     "sdb_act_bwd": (_I, [_P, _P, _P, _LL, _I, _P]),
     "sdb_gather_rows_bf16": (_I, [_P, _P, _P, _LL, _I, _LL, _P]),
+    "sdb_nchw_f32_to_nhwc_bf16_pad": (_I, [_P, _P, _I, _I, _I, _I, _P]),
+    "sdb_softmax_rows_bf16": (_I, [_P, _P, _LL, _I, _LL, _F, _P]),
+    "sdb_vae_sample": (_I, [_P, _P, _P, _I, _I, _I, _F, _P]),
     "sdb_cast_f32_bf16": (_I, [_P, _P, _LL, _P]),
     "sdb_nchw_f32_to_nhwc_bf16": (_I, [_P, _P, _I, _I, _I, _P]),
     "sdb_nhwc_bf16_to_nchw_f32": (_I, [_P, _P, _I, _I, _I, _P]),

@@ -343,3 +343,97 @@ extern "C" int sdb_gather_rows_bf16(const void* src, const int* row_index, void*
   SDB_CUDA_LAUNCH_CHECK("sdb_gather_rows_bf16");
   return SDB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Frozen VAE encoder pieces (diffusers-0.21.4 FlaxAutoencoderKL.encode [third-party, un-vendored], called at
+// /root/reference/training_utils.py:574-586): pixel layout change with channel padding, the single-head 512-wide
+// attention of the encoder's mid block as GEMM -> row softmax -> GEMM, and the latent sample.
+namespace {
+
+// src NCHW fp32 [B, C, HW] -> dst NHWC bf16 [B, HW, Cpad] (channels C..Cpad-1 zero: conv_in runs on 4-channel pixels)
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_pad_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int B, int C, int Cpad, int HW) {
+  sdb::pdl_trigger();
+  const long long total = (long long)B * Cpad * HW;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % Cpad);
+    const long long bp = i / Cpad;
+    const int p = (int)(bp % HW);
+    const int b = (int)(bp / HW);
+    dst[i] = __float2bfloat16_rn(c < C ? src[((long long)b * C + c) * HW + p] : 0.0f);
+  }
+}
+
+// out[r, :] = softmax(scale * x[r, :]) over bf16 rows; one CTA per row, fp32 statistics
+__global__ void __launch_bounds__(256)
+softmax_rows_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ out, int cols, long long ld,
+                    float scale) {
+  sdb::pdl_trigger();
+  const __nv_bfloat16* xr = x + (long long)blockIdx.x * ld;
+  __nv_bfloat16* orow = out + (long long)blockIdx.x * ld;
+  __shared__ float red[8];
+  float mx = -INFINITY;
+  for (int c = threadIdx.x; c < cols; c += 256) mx = fmaxf(mx, bf(xr + c) * scale);
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  mx = red[0];
+  for (int i = 1; i < 8; ++i) mx = fmaxf(mx, red[i]);
+  __syncthreads();
+  float sum = 0.f;
+  for (int c = threadIdx.x; c < cols; c += 256) sum += __expf(bf(xr + c) * scale - mx);
+  sum = sdb::warp_sum(sum);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sum;
+  __syncthreads();
+  sum = 0.f;
+  for (int i = 0; i < 8; ++i) sum += red[i];
+  const float inv = 1.0f / sum;
+  for (int c = threadIdx.x; c < cols; c += 256) orow[c] = __float2bfloat16_rn(__expf(bf(xr + c) * scale - mx) * inv);
+}
+
+// latents NCHW fp32 [B, L, HW] = (mean + exp(0.5 * clip(logvar, -30, 20)) * eps) * scaling; moments NHWC bf16 [B, HW, 2L]
+// (mean | logvar), eps fp32 in NHWC order [B, HW, L] (FlaxDiagonalGaussianDistribution.sample draws in the NHWC shape)
+__global__ void __launch_bounds__(256)
+vae_sample_kernel(const __nv_bfloat16* __restrict__ moments, const float* __restrict__ eps, float* __restrict__ latents,
+                  int B, int L, int HW, float scaling) {
+  sdb::pdl_trigger();
+  const long long total = (long long)B * L * HW;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int p = (int)(i % HW);
+    const long long bc = i / HW;
+    const int c = (int)(bc % L);
+    const int b = (int)(bc / L);
+    const long long row = (long long)b * HW + p;
+    const float mean = bf(moments + row * 2 * L + c);
+    const float logvar = fminf(fmaxf(bf(moments + row * 2 * L + L + c), -30.0f), 20.0f);
+    const float e = eps ? eps[row * L + c] : 0.0f;
+    latents[i] = (mean + __expf(0.5f * logvar) * e) * scaling;
+  }
+}
+
+}  // namespace
+
+extern "C" int sdb_nchw_f32_to_nhwc_bf16_pad(const float* src, void* dst, int B, int C, int Cpad, int HW,
+                                             cudaStream_t stream) {
+  SDB_CHECK_ARG(B > 0 && C > 0 && Cpad >= C && HW > 0, "sdb_nchw_f32_to_nhwc_bf16_pad: bad shape");
+  nchw_to_nhwc_pad_kernel<<<grid_for((long long)B * Cpad * HW), 256, 0, stream>>>(src, (__nv_bfloat16*)dst, B, C, Cpad, HW);
+  SDB_CUDA_LAUNCH_CHECK("sdb_nchw_f32_to_nhwc_bf16_pad");
+  return SDB_OK;
+}
+
+extern "C" int sdb_softmax_rows_bf16(const void* x, void* out, long long rows, int cols, long long ld, float scale,
+                                     cudaStream_t stream) {
+  SDB_CHECK_ARG(rows > 0 && rows < (1ll << 31) && cols > 0 && ld >= cols, "sdb_softmax_rows_bf16: bad shape");
+  softmax_rows_kernel<<<(unsigned)rows, 256, 0, stream>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, cols, ld, scale);
+  SDB_CUDA_LAUNCH_CHECK("sdb_softmax_rows_bf16");
+  return SDB_OK;
+}
+
+extern "C" int sdb_vae_sample(const void* moments_nhwc_bf16, const float* eps_nhwc, float* latents_nchw, int B,
+                              int latent_channels, int HW, float scaling, cudaStream_t stream) {
+  SDB_CHECK_ARG(B > 0 && latent_channels > 0 && HW > 0, "sdb_vae_sample: bad shape");
+  vae_sample_kernel<<<grid_for((long long)B * latent_channels * HW), 256, 0, stream>>>(
+      (const __nv_bfloat16*)moments_nhwc_bf16, eps_nhwc, latents_nchw, B, latent_channels, HW, scaling);
+  SDB_CUDA_LAUNCH_CHECK("sdb_vae_sample");
+  return SDB_OK;
+}

@@ -408,7 +408,22 @@ def _context_index(device, batch: int, chunks: int, strip: bool) -> torch.Tensor
     return _CTX_INDEX[key]
 
 
+def encode_pixels(state: TrainState, frozen_vae_state: FrozenModel, pixel_values: torch.Tensor, rng, return_rng: bool,
+                  what: str) -> torch.Tensor:
+    """training_utils.py:574-586: frozen VAE encode, `latent_dist.sample(sample_rng)`, NCHW, * 0.18215. The sample key is
+    the step's `sample_rng` (split(train_rng, 3)[1]) — the same key the noise keys are split from, as in the reference."""
+    _check_rng(rng, return_rng, what)
+    dev = state.arena.device
+    enc = frozen_vae_state.call.encoder(frozen_vae_state.params, dev)
+    B, _, H, W = pixel_values.shape
+    mom = enc.encode(pixel_values)
+    Bg, b0 = _dp_rows(state, B)
+    down = 2 ** (len(enc.cfg.block_out_channels) - 1)
+    return enc.sample(mom, (H // down, W // down), key=JR.train_step_keys(rng)["sample"], batch_global=Bg, batch_begin=b0)
+
+
 def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
+               frozen_vae_state: Optional[FrozenModel] = None,
                text_encoder_state: Optional[TrainState] = None, strip_bos_eos_token: bool = True,
                unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
                min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0, ema_rate: float = 0.0,
@@ -418,6 +433,9 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
     inputs of any width are promoted to fp32 like jnp would). Whatever the batch does not supply is drawn from `rng`
     exactly as the reference draws it (split(train_rng, 3) / split(sample_rng, 4), jax.random.normal / randint; offset
     and perturbation noise apply to drawn noise only, as in the reference).
+    With `frozen_vae_state` (FrozenModel(call=vae.AutoencoderKL, params=tree), training_utils.py:218-222) and
+    "pixel_values" fp32 [B, 3, H, W] in the batch instead of "latents", the frozen VAE encodes the pixels and the latents
+    are sampled from its posterior with the step's `sample_rng`, scaled by 0.18215 (574-586).
     With `text_encoder_state` (a TrainState over clip.CLIPTextModel, training_utils.py:389-425) the batch carries
     "input_ids" int [B * chunks, 77] instead of "encoder_hidden_states": the text encoder runs inside the step, its
     hidden states are assembled into the context as the reference does (641-674, `strip_bos_eos_token`), the UNet's
@@ -436,7 +454,12 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
     if torch.cuda.current_device() != dev.index:
         raise RuntimeError(f"train_step: the state lives on {dev} but the current CUDA device is "
                            f"cuda:{torch.cuda.current_device()} (call torch.cuda.set_device first)")
-    lat = batch["latents"]
+    used_rng = False
+    if "latents" not in batch and frozen_vae_state is not None and "pixel_values" in batch:
+        lat = encode_pixels(state, frozen_vae_state, batch["pixel_values"], rng, return_rng, "train_step")
+        used_rng = True
+    else:
+        lat = batch["latents"]
     if lat.device != dev:
         raise ValueError(f"train_step: batch['latents'] is on {lat.device}, the state on {dev}")
     if lat.dtype != torch.float32 or not lat.is_contiguous():
@@ -453,7 +476,7 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
             perturbation_noise_magnitude=perturbation_noise_magnitude)
         noise = n_ if noise is None else noise
         timesteps = t_ if timesteps is None else timesteps
-    elif return_rng and rng is not None:
+    elif (return_rng or used_rng) and rng is not None:
         new_rng = JR.train_step_keys(rng)["new_train"]  # the key still advances (training_utils.py:530)
         if isinstance(rng, JR.RngStream):
             rng.key = new_rng
@@ -565,10 +588,12 @@ class CompiledTrainStep:
     futures: the host blocks only when it reads it)."""
 
     def __init__(self, state: TrainState, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
+                 frozen_vae_state: Optional[FrozenModel] = None,
                  text_encoder_state: Optional[TrainState] = None, strip_bos_eos_token: bool = True,
                  unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
                  min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0,
                  ema_rate: float = 0.0):
+        self.vae = frozen_vae_state   # the frozen encode runs eagerly in front of the graph (its latents are an input)
         self.text_state = text_encoder_state
         self.strip = bool(strip_bos_eos_token)
         if text_encoder_state is not None:
@@ -595,6 +620,12 @@ class CompiledTrainStep:
     def _flags(self) -> dict:
         return dict(unet_ema_params=self.ema_params, ema_rate=self.ema_rate, min_snr_gamma_magnitude=self.min_snr,
                     text_encoder_state=self.text_state, strip_bos_eos_token=self.strip)
+
+    def _with_latents(self, batch, rng, return_rng):
+        if "latents" in batch or self.vae is None or "pixel_values" not in batch:
+            return batch
+        lat = encode_pixels(self.state, self.vae, batch["pixel_values"], rng, return_rng, "CompiledTrainStep")
+        return dict({k: v for k, v in batch.items() if k != "pixel_values"}, latents=lat)
 
     def _eager(self, batch, rng, return_rng):
         return train_step(self.state, batch, rng, self.sched, offset_noise_magnitude=self.offset,
@@ -627,6 +658,7 @@ class CompiledTrainStep:
     def __call__(self, state: TrainState, batch: dict, rng=None, return_rng: bool = False):
         if state is not self.state:
             raise ValueError("CompiledTrainStep: called with a different TrainState than it was compiled for")
+        batch = self._with_latents(batch, rng, return_rng)
         cond = "input_ids" if self.text_state is not None else "encoder_hidden_states"
         key = (tuple(batch["latents"].shape), tuple(batch[cond].shape))
         e = self._entries.get(key)
