@@ -38,8 +38,10 @@ def test_softmax_rows_and_sample_kernels(cuda):
     mom[0, 1, L:] = -50.0  # and to -30
     eps = torch.randn(B, HW, L)
     lat = torch.empty(B, L, HW, device=cuda)
-    _lib.check(l.sdb_vae_sample(mom.to(cuda).data_ptr(), eps.to(cuda).data_ptr(), lat.data_ptr(), B, L, HW, 0.18215,
+    mom_d, eps_d = mom.to(cuda), eps.to(cuda)
+    _lib.check(l.sdb_vae_sample(mom_d.data_ptr(), eps_d.data_ptr(), lat.data_ptr(), B, L, HW, 0.18215,
                                 _lib.stream_ptr()), "vae_sample")
+    torch.cuda.synchronize()
     want = OV.sample_latents(OV.SD_VAE, mom.float().view(B, 1, HW, 2 * L), eps.view(B, 1, HW, L)).reshape(B, L, HW)
     assert _rel(lat.cpu().numpy(), want.numpy()) < 1e-5
 
