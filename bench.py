@@ -43,7 +43,12 @@ WORKLOADS = {
     "sd15": dict(name="SD-1.5 UNet (860M) train_step, 64x64x4 latents, ctx 77x768, eps-pred, Lion-8bit", H=64, L=77, batch=8),
     "sd21": dict(name="SD-2.x UNet train_step, 96x96x4 latents, ctx 77x1024, v-pred, Lion-8bit", H=96, L=77, batch=4),
     "tiny": dict(name="tiny UNet (32/64) train_step, 32x32x4 latents, ctx 77x32", H=32, L=77, batch=2),
+    # the reference's COMPLETE step (training_utils.py:504-762): frozen VAE encode of 512x512 pixels, CLIP-L text encoder
+    # trained inside the step on the repo's default 3 x 75 + 2 token context (227 tokens), SD-1.5 UNet, two Lion updates
+    "sd15_full": dict(name="SD-1.5 complete step: VAE encode 512x512 px + CLIP-L train (227-token context) + UNet train, "
+                           "eps-pred, Lion-8bit x2", H=64, L=227, batch=8),
 }
+TRAIN_FLOP_PER_SAMPLE["sd15_full"] = 2.4479e12  # UNet only (ctx 227); VAE / CLIP FLOPs are not counted
 
 
 def measured_peaks():
@@ -114,6 +119,11 @@ def host_batches(cfg_name, cfg, B, n, seed, pin):
     rng = np.random.default_rng(seed)
     out = []
     for _ in range(n):
+        if cfg_name == "sd15_full":
+            b = {"pixel_values": torch.from_numpy(rng.uniform(-1, 1, (B, 3, 8 * w["H"], 8 * w["H"])).astype(np.float32)),
+                 "input_ids": torch.from_numpy(rng.integers(0, 49408, (B * 3, 77)).astype(np.int32))}
+            out.append({k: v.pin_memory() for k, v in b.items()} if pin else b)
+            continue
         b = {"latents": torch.from_numpy(rng.standard_normal((B, 4, w["H"], w["H"]), dtype=np.float32)),
              "noise": torch.from_numpy(rng.standard_normal((B, 4, w["H"], w["H"]), dtype=np.float32)),
              "timesteps": torch.from_numpy(rng.integers(0, 1000, B).astype(np.int32)),
@@ -167,7 +177,8 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     L = _lib.lib()
     _lib.check(L.sdb_check_device(local), "sdb_check_device")
-    cfg = {"sd15": PU.SD15, "sd21": PU.SD21, "tiny": PU.TINY}[args.config]
+    full = args.config == "sd15_full"
+    cfg = {"sd15": PU.SD15, "sd21": PU.SD21, "tiny": PU.TINY, "sd15_full": PU.SD15}[args.config]
     w = WORKLOADS[args.config]
     B = args.batch or w["batch"]
     ptype = "v_prediction" if args.config == "sd21" else "epsilon"
@@ -179,8 +190,25 @@ def run_ours(args):
     if world > 1:
         parallel.attach(state)
     sched = TU.default_scheduler(dev, "scaled_linear", ptype)
-    step_fn = TU.compile_train_step(state, sched) if args.graph else \
-        (lambda s, b, r: TU.train_step(s, b, r, frozen_noise_scheduler_state=sched))
+    extra = {}
+    if full:
+        from stable_diffusion_training_b200 import clip as CL
+        from stable_diffusion_training_b200 import jax_random as JR
+        from stable_diffusion_training_b200 import vae as PV
+        tparams = LQ.unflatten_dict({k: torch.from_numpy(v) for k, v in CL.init_params_numpy(CL.SD15_CLIP, 1).items()})
+        tstate = TU.TrainState.create(apply_fn=CL.CLIPTextModel(CL.SD15_CLIP).__call__, params=tparams,
+                                      tx=TU.create_lion_optimizer(tparams), device=dev)
+        vtree = LQ.unflatten_dict(PV.init_params_numpy(PV.SD_VAE, 2))
+        if world > 1:
+            parallel.attach(tstate)
+        extra = dict(frozen_vae_state=TU.FrozenModel(call=PV.AutoencoderKL(PV.SD_VAE), params=vtree),
+                     text_encoder_state=tstate)
+        train_rng = JR.RngStream(1234)
+    step_fn = TU.compile_train_step(state, sched, **extra) if args.graph else \
+        (lambda s, b, r: TU.train_step(s, b, r, frozen_noise_scheduler_state=sched, **extra))
+    if full:  # the step draws VAE sample noise, diffusion noise and timesteps itself from train_rng
+        inner = step_fn
+        step_fn = lambda s, b, r: inner(s, b, train_rng)
 
     nb = 4
     hb = host_batches(args.config, cfg, B, nb, 1 + rank, pin=True)
@@ -254,7 +282,7 @@ def run_ours(args):
             "clocks": clocks,
             "roofline": roofline_object(kernels, peaks, ach_tf, step_ms),
         }
-        if not args.no_cpu:
+        if not args.no_cpu and not full:  # the CPU restatement of the complete step is not timed (UNet arm only)
             out["cpu_baseline"] = cpu_baseline(args.config, steps=2, warmup=0)
     if world > 1:
         dist.barrier()
