@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SDB200_ABI_VERSION 4
+#define SDB200_ABI_VERSION 5
 
 #ifndef __CUDA_RUNTIME_H__
 typedef struct CUstream_st* cudaStream_t;
@@ -291,6 +291,21 @@ int sdb_softmax_rows_bf16(const void* x, void* out, long long rows, int cols, lo
  * 20)) * eps) * scaling; moments NHWC bf16 [B, HW, 2 L] = (mean | logvar), eps fp32 NHWC [B, HW, L] (NULL: the mode). */
 int sdb_vae_sample(const void* moments_nhwc_bf16, const float* eps_nhwc, float* latents_nchw, int B, int latent_channels,
                    int HW, float scaling, cudaStream_t stream);
+
+/* ---- validation sampler (models/pipeline_flax_stable_diffusion.py:160-254): the elementwise steps between the UNet
+ * forward, sdb_ddim_step and the VAE decode. The decoder itself reuses the conv / GroupNorm / GEMM entry points. */
+/* out NHWC bf16 [repeat * B, HW, C] = bf16(latents NCHW fp32 [B, C, HW] * scale), the batch written `repeat` times:
+ * `jnp.concatenate([latents] * 2)` + the UNet's entry transpose (211-224; repeat 2, scale 1), and `1 / scaling_factor *
+ * latents` + FlaxAutoencoderKL.decode's transpose (246-249; repeat 1). */
+int sdb_latents_to_nhwc_bf16(const float* latents_nchw, float scale, int repeat, void* out_nhwc_bf16, int B, int C, int HW,
+                             cudaStream_t stream);
+/* classifier-free guidance (226-227): pred NHWC bf16 [2B, HW, C] (uncond rows first) -> NCHW fp32 [B, C, HW] =
+ * uncond + guidance_scale * bf16(text - uncond). */
+int sdb_cfg_combine(const void* pred_nhwc_bf16, float guidance_scale, float* out_nchw, int B, int C, int HW,
+                    cudaStream_t stream);
+/* (image / 2 + 0.5).clip(0, 1).transpose(0, 2, 3, 1) (250) on the decoder's NHWC bf16 [npix, Cpad] output -> NHWC fp32
+ * [npix, C] (bf16 arithmetic, as the reference's bf16 VAE computes it). */
+int sdb_image_postprocess(const void* x_nhwc_bf16, float* out_nhwc, long long npix, int Cpad, int C, cudaStream_t stream);
 
 /* ---- data movement / small elementwise pieces of the UNet graph (FlaxUpsample2D nearest resize, skip-connection
  * concatenate, FlaxTimesteps sinusoid, silu(temb), NCHW->NHWC entry transpose [upstream diffusers 0.21.4]) ---- */

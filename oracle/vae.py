@@ -11,8 +11,13 @@ eps 1e-6, swish, conv3x3, 1x1 conv_shortcut when the width changes) and FlaxDown
 stride-2 VALID conv), FlaxUNetMidBlock2D (resnet, FlaxAttentionBlock: one head, scale C^-1/4 on q and k, softmax over
 all H*W tokens, proj_attn, residual; resnet), conv_norm_out + swish + conv_out), quant_conv 1x1,
 FlaxDiagonalGaussianDistribution (logvar clipped to [-30, 20]). It is hardened by an independent torch.nn NCHW
-restatement (tests/test_oracle_vae.py). Only the encoder half and quant_conv are on the path (the decoder is never run
-in training).
+restatement (tests/test_oracle_vae.py). Only the encoder half and quant_conv are on the TRAINING path.
+
+The DECODE half (post_quant_conv 1x1, FlaxDecoder: conv_in, mid block, FlaxUpDecoderBlock2D x 4 over the reversed
+widths with layers_per_block + 1 resnets each and FlaxUpsample2D (nearest 2x, conv3x3) on all but the last,
+conv_norm_out + swish + conv_out) is the last stage of the validation sampler
+(/root/reference/models/pipeline_flax_stable_diffusion.py:246-251): `decoder_param_shapes`,
+`init_decoder_params`, `decode`.
 """
 from __future__ import annotations
 
@@ -189,3 +194,99 @@ def sample_latents(cfg: VAEConfig, moments_nhwc, eps_nhwc):
     mean, logvar = moments_nhwc[..., :L], moments_nhwc[..., L:].clamp(-30.0, 20.0)
     lat = mean + torch.exp(0.5 * logvar) * eps_nhwc.to(mean.dtype)
     return lat.permute(0, 3, 1, 2) * cfg.scaling_factor
+
+
+# ---- decode half (validation sampling only) ------------------------------------------------------------------
+def decoder_param_shapes(cfg: VAEConfig) -> Dict[str, tuple]:
+    s: Dict[str, tuple] = {}
+
+    def conv(n, cin, cout, k=3):
+        s[n + "/kernel"] = (k, k, cin, cout)
+        s[n + "/bias"] = (cout,)
+
+    def dense(n, cin, cout):
+        s[n + "/kernel"] = (cin, cout)
+        s[n + "/bias"] = (cout,)
+
+    def norm(n, c):
+        s[n + "/scale"] = (c,)
+        s[n + "/bias"] = (c,)
+
+    def resnet(n, cin, cout):
+        norm(n + "/norm1", cin)
+        conv(n + "/conv1", cin, cout)
+        norm(n + "/norm2", cout)
+        conv(n + "/conv2", cout, cout)
+        if cin != cout:
+            conv(n + "/conv_shortcut", cin, cout, 1)
+
+    rev = tuple(reversed(cfg.block_out_channels))
+    conv("post_quant_conv", cfg.latent_channels, cfg.latent_channels, 1)
+    conv("decoder/conv_in", cfg.latent_channels, rev[0])
+    ch = rev[0]
+    resnet("decoder/mid_block/resnets_0", ch, ch)
+    a = "decoder/mid_block/attentions_0"
+    norm(a + "/group_norm", ch)
+    for d in ("query", "key", "value", "proj_attn"):
+        dense(f"{a}/{d}", ch, ch)
+    resnet("decoder/mid_block/resnets_1", ch, ch)
+    for i, c in enumerate(rev):
+        for j in range(cfg.layers_per_block + 1):
+            resnet(f"decoder/up_blocks_{i}/resnets_{j}", ch, c)
+            ch = c
+        if i != len(rev) - 1:
+            conv(f"decoder/up_blocks_{i}/upsamplers_0/conv", ch, ch)
+    norm("decoder/conv_norm_out", ch)
+    conv("decoder/conv_out", ch, cfg.in_channels)
+    return dict(sorted(s.items()))
+
+
+def _init(shapes, seed):
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    out = {}
+    for name, shape in shapes.items():
+        leaf = name.rsplit("/", 1)[1]
+        parent = name.rsplit("/", 2)[-2]
+        if leaf == "kernel":
+            fan_in = int(np.prod(shape[:-1]))
+            a = rng.standard_normal(shape, dtype=np.float32) * np.float32(1.0 / math.sqrt(fan_in))
+        elif leaf == "scale":
+            a = np.float32(1) + rng.standard_normal(shape, dtype=np.float32) * np.float32(0.1)
+        elif "norm" in parent:
+            a = rng.standard_normal(shape, dtype=np.float32) * np.float32(0.1)
+        else:
+            a = rng.standard_normal(shape, dtype=np.float32) * np.float32(0.02)
+        out[name] = torch.from_numpy(a.astype(np.float32))
+    return out
+
+
+def init_decoder_params(cfg: VAEConfig, seed: int = 0) -> Dict[str, torch.Tensor]:
+    """Decoder + post_quant_conv leaves, drawn from their own stream so the encoder's synthetic weights do not move."""
+    return _init(decoder_param_shapes(cfg), seed + 7919)
+
+
+def _upsample(c, x, name):
+    """FlaxUpsample2D: jax.image.resize(method="nearest") to (2H, 2W), then conv3x3."""
+    x = x.repeat_interleave(2, dim=1).repeat_interleave(2, dim=2)
+    return _conv(c, x, name + "/conv")
+
+
+def decode(cfg: VAEConfig, params: Dict[str, torch.Tensor], latents_nchw, mode="fp32"):
+    """FlaxAutoencoderKL.decode(latents NCHW).sample -> NCHW [B, in_channels, 8h, 8w]."""
+    c = _Ctx(params, mode)
+    g = cfg.norm_num_groups
+    rev = tuple(reversed(cfg.block_out_channels))
+    x = latents_nchw.to(c.dtype).permute(0, 2, 3, 1)
+    x = _conv(c, x, "post_quant_conv")
+    x = _conv(c, x, "decoder/conv_in")
+    x = _resnet(c, x, "decoder/mid_block/resnets_0", g)
+    x = _attention(c, x, "decoder/mid_block/attentions_0", g)
+    x = _resnet(c, x, "decoder/mid_block/resnets_1", g)
+    for i in range(len(rev)):
+        for j in range(cfg.layers_per_block + 1):
+            x = _resnet(c, x, f"decoder/up_blocks_{i}/resnets_{j}", g)
+        if i != len(rev) - 1:
+            x = _upsample(c, x, f"decoder/up_blocks_{i}/upsamplers_0")
+    x = _conv(c, F.silu(_group_norm(c, x, "decoder/conv_norm_out", g)), "decoder/conv_out")
+    return x.permute(0, 3, 1, 2)

@@ -97,6 +97,9 @@ SIGNATURES = {
     "sdb_nchw_f32_to_nhwc_bf16_pad": (_I, [_P, _P, _I, _I, _I, _I, _P]),
     "sdb_softmax_rows_bf16": (_I, [_P, _P, _LL, _I, _LL, _F, _P]),
     "sdb_vae_sample": (_I, [_P, _P, _P, _I, _I, _I, _F, _P]),
+    "sdb_latents_to_nhwc_bf16": (_I, [_P, _F, _I, _P, _I, _I, _I, _P]),
+    "sdb_cfg_combine": (_I, [_P, _F, _P, _I, _I, _I, _P]),
+    "sdb_image_postprocess": (_I, [_P, _P, _LL, _I, _I, _P]),
     "sdb_cast_f32_bf16": (_I, [_P, _P, _LL, _P]),
     "sdb_nchw_f32_to_nhwc_bf16": (_I, [_P, _P, _I, _I, _I, _P]),
     "sdb_nhwc_bf16_to_nchw_f32": (_I, [_P, _P, _I, _I, _I, _P]),

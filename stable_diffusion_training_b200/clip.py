@@ -165,9 +165,9 @@ class ClipText:
         self.P, self.W, self.G = P, W, G
         self.graph: Optional[TextGraph] = None
 
-    def forward(self, input_ids: torch.Tensor) -> T:
+    def forward(self, input_ids: torch.Tensor, forward_only: bool = False) -> T:
         cfg = self.cfg
-        g = TextGraph(self.P, self.W, self.G, False)
+        g = TextGraph(self.P, self.W, self.G, False, forward_only)
         self.graph = g
         N, S = input_ids.shape
         if S > cfg.max_position_embeddings:
@@ -211,7 +211,7 @@ class CLIPTextModel:
         if st is None or (params is not None and params is not st.params):
             raise ValueError("CLIPTextModel.__call__: pass params=state.params of the TrainState created with this model")
         ids = input_ids.to(torch.int32).contiguous()
-        out = st.net.forward(ids)
+        out = st.net.forward(ids, forward_only=True)
         st.net.graph = None
         N, S = ids.shape
         return (out.v.view(N, S, -1).float(),)

@@ -232,7 +232,7 @@ class UNetModel:
         B, Cc, H, W = sample.shape
         x = ops.nchw_to_nhwc_bf16(sample.to(torch.float32).contiguous())
         ctx = ops.cast_bf16(encoder_hidden_states.to(torch.float32).contiguous())
-        pred = st.net.forward(x, timesteps.to(torch.int32), ctx)
+        pred = st.net.forward(x, timesteps.to(torch.int32), ctx, forward_only=True)
         st.net.graph = None
         Co = pred.v.shape[-1]
         out = torch.empty((B, Co, H, W), dtype=torch.float32, device=pred.v.device)

@@ -195,13 +195,21 @@ class T:
         self.geom = geom  # (B, H, W) for image-shaped activations
 
 
+class _NoTape(list):
+    """Tape of a forward-only pass: the backward closures (and the activations they hold) are dropped at once."""
+
+    def append(self, item) -> None:
+        pass
+
+
 class Graph:
     """One forward/backward pass over device buffers. P: fp32 masters, W: bf16 shadows, G: fp32 gradients
-    (dicts path -> tensor views into the arenas)."""
+    (dicts path -> tensor views into the arenas). forward_only: nothing is kept for a backward pass (the sampler),
+    so every activation is freed as soon as its consumers have been enqueued."""
 
-    def __init__(self, P, W, G, reference_attention_quirk: bool = True):
+    def __init__(self, P, W, G, reference_attention_quirk: bool = True, forward_only: bool = False):
         self.P, self.W, self.G = P, W, G
-        self.tape = []
+        self.tape = _NoTape() if forward_only else []
         self.quirk = reference_attention_quirk
         self._kb_cache = {}
         # Parameter gradients (wgrad GEMMs, bias column sums) feed nothing but the optimizer, so backward enqueues them
@@ -512,10 +520,11 @@ class UNet:
         self.graph: Optional[Graph] = None
         self._kb_cache = {}
 
-    def forward(self, sample_nhwc: torch.Tensor, timesteps: torch.Tensor, context: torch.Tensor) -> T:
+    def forward(self, sample_nhwc: torch.Tensor, timesteps: torch.Tensor, context: torch.Tensor,
+                forward_only: bool = False) -> T:
         """sample_nhwc [B,H,W,Cin] bf16; timesteps int32 [B]; context [B,L,D] bf16."""
         cfg = self.cfg
-        g = Graph(self.P, self.W, self.G, self.quirk)
+        g = Graph(self.P, self.W, self.G, self.quirk, forward_only)
         g._kb_cache = self._kb_cache
         self.graph = g
         B, H, W, Cin = sample_nhwc.shape

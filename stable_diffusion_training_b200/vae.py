@@ -1,4 +1,5 @@
-"""Frozen VAE encode on the sm_100a kernels (host side, forward only) — SURVEY.md 8(f)-3.
+"""Frozen VAE encode and decode (8(f)-4, validation sampler) on the sm_100a kernels — host side,
+forward only.
 
 Mirrors diffusers==0.21.4 FlaxAutoencoderKL.encode as the reference calls it at the top of its step
 (/root/reference/training_utils.py:574-586: `frozen_vae_state.call.apply({"params": ...}, sample=batch["pixel_values"],
@@ -11,6 +12,12 @@ the stride-2 downsample uses the parity-view trick with FlaxDownsample2D's ((0,1
 single-head attention (head dim 512 > the flash kernels' 192) runs per image as GEMM -> row softmax -> GEMM; conv_in
 (3 channels) runs on pixels padded to 8 channels. Parameter names and layouts are Flax's (`encoder/conv_in/kernel`
 HWIO, ...): trees interchange with the reference.
+
+Decode mirrors FlaxAutoencoderKL.decode as the reference's sampler calls it
+(/root/reference/models/pipeline_flax_stable_diffusion.py:246-251: `1 / scaling_factor * latents`, `vae.apply(...,
+method=vae.decode).sample`, `(image / 2 + 0.5).clip(0, 1).transpose(0, 2, 3, 1)`): post_quant_conv, conv_in (4 ->
+512, the UNet's 4-channel CUDA-core kernel), mid block, four up blocks (nearest 2x + conv3x3), conv_out (128 -> 3,
+weights padded to 4 output channels) and the image post-processing fused into the read-out kernel.
 """
 from __future__ import annotations
 
@@ -89,9 +96,13 @@ def param_shapes(cfg: VAEConfig) -> Dict[str, tuple]:
 
 def init_params_numpy(cfg: VAEConfig, seed: int = 0) -> Dict[str, np.ndarray]:
     """Synthetic random-init weights (same generator and order as oracle/vae.py:init_params)."""
+    return _init_numpy(param_shapes(cfg), seed)
+
+
+def _init_numpy(shapes: Dict[str, tuple], seed: int) -> Dict[str, np.ndarray]:
     rng = np.random.default_rng(seed)
     out = {}
-    for name, shape in param_shapes(cfg).items():
+    for name, shape in shapes.items():
         leaf = name.rsplit("/", 1)[1]
         parent = name.rsplit("/", 2)[-2]
         if leaf == "kernel":
@@ -113,17 +124,63 @@ def _down_taps(cin: int):
     return [(par[kh][0] * 2 + par[kw][0], par[kh][1], par[kw][1], (kh * 3 + kw) * cin) for kh in range(3) for kw in range(3)]
 
 
-class VAEEncoder:
-    """encode(pixel_values NCHW fp32 [B, 3, H, W]) -> moments NHWC bf16 [B, H/8 * W/8, 2 * latent]."""
+def decoder_param_shapes(cfg: VAEConfig) -> Dict[str, tuple]:
+    """Decoder + post_quant_conv leaves of the FlaxAutoencoderKL tree (validation sampling only)."""
+    s: Dict[str, tuple] = {}
 
-    def __init__(self, cfg: VAEConfig, params: dict, device):
+    def conv(n, cin, cout, k=3):
+        s[n + "/kernel"] = (k, k, cin, cout)
+        s[n + "/bias"] = (cout,)
+
+    def norm(n, c):
+        s[n + "/scale"] = (c,)
+        s[n + "/bias"] = (c,)
+
+    def resnet(n, cin, cout):
+        norm(n + "/norm1", cin)
+        conv(n + "/conv1", cin, cout)
+        norm(n + "/norm2", cout)
+        conv(n + "/conv2", cout, cout)
+        if cin != cout:
+            conv(n + "/conv_shortcut", cin, cout, 1)
+
+    rev = tuple(reversed(cfg.block_out_channels))
+    conv("post_quant_conv", cfg.latent_channels, cfg.latent_channels, 1)
+    conv("decoder/conv_in", cfg.latent_channels, rev[0])
+    ch = rev[0]
+    resnet("decoder/mid_block/resnets_0", ch, ch)
+    a = "decoder/mid_block/attentions_0"
+    norm(a + "/group_norm", ch)
+    for d in ("query", "key", "value", "proj_attn"):
+        s[f"{a}/{d}/kernel"] = (ch, ch)
+        s[f"{a}/{d}/bias"] = (ch,)
+    resnet("decoder/mid_block/resnets_1", ch, ch)
+    for i, c in enumerate(rev):
+        for j in range(cfg.layers_per_block + 1):
+            resnet(f"decoder/up_blocks_{i}/resnets_{j}", ch, c)
+            ch = c
+        if i != len(rev) - 1:
+            conv(f"decoder/up_blocks_{i}/upsamplers_0/conv", ch, ch)
+    norm("decoder/conv_norm_out", ch)
+    conv("decoder/conv_out", ch, cfg.in_channels)
+    return dict(sorted(s.items()))
+
+
+def init_decoder_params_numpy(cfg: VAEConfig, seed: int = 0) -> Dict[str, np.ndarray]:
+    """Synthetic decoder weights (same generator and order as oracle/vae.py:init_decoder_params)."""
+    return _init_numpy(decoder_param_shapes(cfg), seed + 7919)
+
+
+class _VAEExec:
+    """Loads the leaves named by `shapes` (fp32 copies P, bf16 GEMM operands W) and holds the layers both halves use."""
+
+    def __init__(self, cfg: VAEConfig, params: dict, device, shapes: Dict[str, tuple], what: str):
         self.cfg = cfg
         self.device = torch.device(device)
         flat = flatten_dict(params)
-        shapes = param_shapes(cfg)
         missing = sorted(set(shapes) - set(flat))
         if missing:
-            raise ValueError(f"VAE params lack encoder leaves (e.g. {missing[:3]})")
+            raise ValueError(f"VAE params lack {what} leaves (e.g. {missing[:3]})")
         self.P: Dict[str, torch.Tensor] = {}   # fp32 (biases, norm parameters)
         self.W: Dict[str, torch.Tensor] = {}   # bf16 GEMM operands
         for n, shp in shapes.items():
@@ -135,15 +192,6 @@ class VAEEncoder:
             self.P[n] = t
             if n.endswith("/kernel"):
                 self.W[n] = ops.cast_bf16(t)
-        # conv_in on the tensor cores: pixels padded to 8 channels (TMA needs 16-byte pixel rows), the padded input
-        # channels have zero weights; a K block of 64 is mostly TMA zero fill, which is still 7x faster than the CUDA-core
-        # 4-channel kernel at 512x512 (r4m: 2.27 ms for B = 8)
-        k = self.P["encoder/conv_in/kernel"]
-        if cfg.in_channels > 8:
-            raise NotImplementedError("conv_in with more than 8 input channels")
-        kp = torch.zeros((3, 3, 8, k.shape[3]), dtype=torch.float32, device=self.device)
-        kp[:, :, :cfg.in_channels] = k
-        self._conv_in_w = ops.cast_bf16(kp)
 
     # ---- layers (forward only) ----
     def _gn(self, x, B, name, silu):
@@ -195,6 +243,22 @@ class VAEEncoder:
             ops.linear(scores, vb, out=o[b * S:(b + 1) * S])
         return self._linear(o, name + "/proj_attn", residual=x4.view(B * S, C)).view(B, H, W, C)
 
+
+class VAEEncoder(_VAEExec):
+    """encode(pixel_values NCHW fp32 [B, 3, H, W]) -> moments NHWC bf16 [B, H/8 * W/8, 2 * latent]."""
+
+    def __init__(self, cfg: VAEConfig, params: dict, device):
+        super().__init__(cfg, params, device, param_shapes(cfg), "encoder")
+        # conv_in on the tensor cores: pixels padded to 8 channels (TMA needs 16-byte pixel rows), the padded input
+        # channels have zero weights; a K block of 64 is mostly TMA zero fill, which is still 7x faster than the CUDA-core
+        # 4-channel kernel at 512x512 (r4m: 2.27 ms for B = 8)
+        k = self.P["encoder/conv_in/kernel"]
+        if cfg.in_channels > 8:
+            raise NotImplementedError("conv_in with more than 8 input channels")
+        kp = torch.zeros((3, 3, 8, k.shape[3]), dtype=torch.float32, device=self.device)
+        kp[:, :, :cfg.in_channels] = k
+        self._conv_in_w = ops.cast_bf16(kp)
+
     def encode(self, pixel_values: torch.Tensor) -> torch.Tensor:
         cfg = self.cfg
         if pixel_values.device != self.device:
@@ -238,16 +302,92 @@ class VAEEncoder:
         return lat
 
 
+class VAEDecoder(_VAEExec):
+    """decode_nhwc(latents NCHW fp32 [B, L, h, w], scale) -> NHWC bf16 [B, 8h, 8w, 4] (channel 3 is padding);
+    decode() / decode_image() read it out as the reference's `.sample` (NCHW) or as post-processed pixels."""
+
+    def __init__(self, cfg: VAEConfig, params: dict, device):
+        super().__init__(cfg, params, device, decoder_param_shapes(cfg), "decoder")
+        if cfg.latent_channels != 4 or cfg.in_channels > 4:
+            raise NotImplementedError("VAEDecoder: 4 latent channels and at most 4 image channels")
+        # conv_out (C -> 3) on the 4-output-channel CUDA-core kernel of the UNet's conv_out: zero fourth output channel
+        k = self.P["decoder/conv_out/kernel"]
+        kp = torch.zeros((3, 3, k.shape[2], 4), dtype=torch.float32, device=self.device)
+        kp[..., :cfg.in_channels] = k
+        self._conv_out_w = ops.cast_bf16(kp)
+        bp = torch.zeros(4, dtype=torch.float32, device=self.device)
+        bp[:cfg.in_channels] = self.P["decoder/conv_out/bias"]
+        self._conv_out_b = bp
+
+    def _upsample(self, x4, name):
+        return self._conv(ops.upsample2x_fwd(x4), name + "/conv")
+
+    def decode_nhwc(self, latents: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+        cfg = self.cfg
+        if latents.device != self.device:
+            raise ValueError(f"VAEDecoder.decode: latents are on {latents.device}, the VAE on {self.device}")
+        if latents.dim() != 4 or latents.shape[1] != cfg.latent_channels:
+            raise ValueError(f"VAEDecoder.decode: expected NCHW latents [B, {cfg.latent_channels}, h, w]")
+        B, L, h, w = latents.shape
+        lat = latents.to(torch.float32).contiguous()
+        x = torch.empty((B, h, w, L), device=self.device, dtype=BF16)
+        _lib.check(_lib.lib().sdb_latents_to_nhwc_bf16(lat.data_ptr(), float(np.float32(scale)), 1, x.data_ptr(), B, L,
+                                                       h * w, _lib.stream_ptr(self.device)), "sdb_latents_to_nhwc_bf16")
+        x = self._linear(x.view(-1, L), "post_quant_conv").view(B, h, w, L)
+        x = ops.conv3x3_c4in(x, self.W["decoder/conv_in/kernel"], bias=self.P["decoder/conv_in/bias"])
+        x = self._resnet(x, "decoder/mid_block/resnets_0")
+        x = self._attention(x, "decoder/mid_block/attentions_0")
+        x = self._resnet(x, "decoder/mid_block/resnets_1")
+        n = len(cfg.block_out_channels)
+        for i in range(n):
+            for j in range(cfg.layers_per_block + 1):
+                x = self._resnet(x, f"decoder/up_blocks_{i}/resnets_{j}")
+            if i != n - 1:
+                x = self._upsample(x, f"decoder/up_blocks_{i}/upsamplers_0")
+        Bq, Hq, Wq, C = x.shape
+        x = self._gn(x, B, "decoder/conv_norm_out", True).view(Bq, Hq, Wq, C)
+        return ops.conv3x3_c4out(x, self._conv_out_w, bias=self._conv_out_b)
+
+    def decode(self, latents: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+        """FlaxAutoencoderKL.decode(latents * scale).sample: NCHW fp32 [B, in_channels, 8h, 8w] (bf16-valued)."""
+        y = self.decode_nhwc(latents, scale)
+        B, H, W, _ = y.shape
+        out = torch.empty((B, 4, H, W), dtype=torch.float32, device=self.device)
+        _lib.check(_lib.lib().sdb_nhwc_bf16_to_nchw_f32(y.data_ptr(), out.data_ptr(), B, 4, H * W,
+                                                        _lib.stream_ptr(self.device)), "sdb_nhwc_bf16_to_nchw_f32")
+        return out[:, :self.cfg.in_channels]
+
+    def decode_image(self, latents: torch.Tensor, scale: float = 1.0) -> torch.Tensor:
+        """(decode(latents * scale) / 2 + 0.5).clip(0, 1).transpose(0, 2, 3, 1): NHWC fp32 [B, 8h, 8w, in_channels]."""
+        y = self.decode_nhwc(latents, scale)
+        B, H, W, _ = y.shape
+        C = self.cfg.in_channels
+        out = torch.empty((B, H, W, C), dtype=torch.float32, device=self.device)
+        _lib.check(_lib.lib().sdb_image_postprocess(y.data_ptr(), out.data_ptr(), B * H * W, 4, C,
+                                                    _lib.stream_ptr(self.device)), "sdb_image_postprocess")
+        return out
+
+
 class AutoencoderKL:
     """Stand-in for the FlaxAutoencoderKL module object (`FrozenModel(call=vae, params=vae_params)` in the reference):
-    `.config`, `.encoder(params, device)` builds / caches the executor for a parameter tree."""
+    `.config`, `.encoder(params, device)` / `.decoder(params, device)` build / cache the executors for a parameter tree."""
 
     def __init__(self, config: VAEConfig = SD_VAE):
         self.config = config
         self._enc = None
+        self._dec = None
 
-    def init_weights(self, seed: int = 0) -> dict:
-        return unflatten_dict(init_params_numpy(self.config, seed))
+    def init_weights(self, seed: int = 0, decoder: bool = False) -> dict:
+        """Synthetic tree: the encoder half (what training needs); decoder=True adds the decode half."""
+        flat = init_params_numpy(self.config, seed)
+        if decoder:
+            flat.update(init_decoder_params_numpy(self.config, seed))
+        return unflatten_dict(flat)
+
+    def decoder(self, params: dict, device) -> VAEDecoder:
+        if self._dec is None or self._dec[0] is not params or self._dec[1].device != torch.device(device):
+            self._dec = (params, VAEDecoder(self.config, params, device))
+        return self._dec[1]
 
     def encoder(self, params: dict, device) -> VAEEncoder:
         if self._enc is None or self._enc[0] is not params or self._enc[1].device != torch.device(device):
