@@ -425,9 +425,9 @@ def encode_pixels(state: TrainState, frozen_vae_state: FrozenModel, pixel_values
 def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
                frozen_vae_state: Optional[FrozenModel] = None,
                text_encoder_state: Optional[TrainState] = None, strip_bos_eos_token: bool = True,
-               unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
-               min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0, ema_rate: float = 0.0,
-               return_rng: bool = False):
+               unet_ema_params: Optional[dict] = None, text_encoder_ema_params: Optional[dict] = None,
+               offset_noise_magnitude: float = 0.0, min_snr_gamma_magnitude: float = 0.0,
+               perturbation_noise_magnitude: float = 0.0, ema_rate: float = 0.0, return_rng: bool = False):
     """One denoising train step (training_utils.py:504-762, UNet part). batch: {"latents" [B,4,H,W],
     "encoder_hidden_states" [B,L,D], optional "noise" [B,4,H,W], "timesteps" int [B]} (device tensors; floating
     inputs of any width are promoted to fp32 like jnp would). Whatever the batch does not supply is drawn from `rng`
@@ -441,7 +441,8 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
     hidden states are assembled into the context as the reference does (641-674, `strip_bos_eos_token`), the UNet's
     context gradient flows back through it and both optimizers step (732-733); that state is donated too.
     Returns (state, {"loss": 0-d device tensor}) and, with return_rng=True, new_train_rng as third element. `state`
-    and `unet_ema_params` (state.create_ema(); updated when ema_rate != 0, training_utils.py:735-739) are donated.
+    and `unet_ema_params` (state.create_ema(); updated when ema_rate != 0, training_utils.py:735-739) are donated;
+    `text_encoder_ema_params` (text_encoder_state.create_ema(), training_utils.py:740-746) likewise.
     Raises ValueError for an unknown prediction type (training_utils.py:697-701)."""
     if frozen_noise_scheduler_state is None:
         frozen_noise_scheduler_state = default_scheduler(state.arena.device)
@@ -529,7 +530,11 @@ def train_step(state: TrainState, batch: dict, rng=None, frozen_noise_scheduler_
         tnet.backward(tdp.on_param_grad if tdp is not None else None)
         if tdp is not None:
             tdp.finish(None)
-        text_encoder_state.apply_gradients(grads=None)
+        t_ema = bool(ema_rate) and text_encoder_ema_params is not None
+        t_fused = t_ema and text_encoder_ema_params is text_encoder_state.ema_params
+        text_encoder_state.apply_gradients(grads=None, ema_rate=float(ema_rate) if t_fused else 0.0)
+        if t_ema and not t_fused:
+            LQ.compute_model_ema(text_encoder_ema_params, text_encoder_state.params, float(ema_rate))
     fused_ema = bool(ema_rate) and unet_ema_params is not None and unet_ema_params is state.ema_params
     state.apply_gradients(grads=None, ema_rate=float(ema_rate) if fused_ema else 0.0)
     if ema_rate and unet_ema_params is not None and not fused_ema:
@@ -590,9 +595,9 @@ class CompiledTrainStep:
     def __init__(self, state: TrainState, frozen_noise_scheduler_state: Optional[FrozenModel] = None, *,
                  frozen_vae_state: Optional[FrozenModel] = None,
                  text_encoder_state: Optional[TrainState] = None, strip_bos_eos_token: bool = True,
-                 unet_ema_params: Optional[dict] = None, offset_noise_magnitude: float = 0.0,
-                 min_snr_gamma_magnitude: float = 0.0, perturbation_noise_magnitude: float = 0.0,
-                 ema_rate: float = 0.0):
+                 unet_ema_params: Optional[dict] = None, text_encoder_ema_params: Optional[dict] = None,
+                 offset_noise_magnitude: float = 0.0, min_snr_gamma_magnitude: float = 0.0,
+                 perturbation_noise_magnitude: float = 0.0, ema_rate: float = 0.0):
         self.vae = frozen_vae_state   # the frozen encode runs eagerly in front of the graph (its latents are an input)
         self.text_state = text_encoder_state
         self.strip = bool(strip_bos_eos_token)
@@ -607,6 +612,11 @@ class CompiledTrainStep:
             raise NotImplementedError("CompiledTrainStep: only a constant learning-rate schedule can be baked in")
         if ema_rate and unet_ema_params is not None and unet_ema_params is not state.ema_params:
             raise ValueError("CompiledTrainStep: unet_ema_params must be the tree returned by state.create_ema()")
+        if ema_rate and text_encoder_ema_params is not None and (
+                text_encoder_state is None or text_encoder_ema_params is not text_encoder_state.ema_params):
+            raise ValueError("CompiledTrainStep: text_encoder_ema_params must be the tree returned by "
+                             "text_encoder_state.create_ema()")
+        self.text_ema_params = text_encoder_ema_params
         self.state = state
         self.sched = frozen_noise_scheduler_state or default_scheduler(state.arena.device)
         self.offset = float(offset_noise_magnitude)
@@ -618,7 +628,8 @@ class CompiledTrainStep:
         self.launches_per_replay = 0
 
     def _flags(self) -> dict:
-        return dict(unet_ema_params=self.ema_params, ema_rate=self.ema_rate, min_snr_gamma_magnitude=self.min_snr,
+        return dict(unet_ema_params=self.ema_params, text_encoder_ema_params=self.text_ema_params,
+                    ema_rate=self.ema_rate, min_snr_gamma_magnitude=self.min_snr,
                     text_encoder_state=self.text_state, strip_bos_eos_token=self.strip)
 
     def _with_latents(self, batch, rng, return_rng):

@@ -220,3 +220,40 @@ def test_joint_compiled_step_matches_eager(cuda):
     assert se == sg == 3
     np.testing.assert_allclose(lg, le, rtol=1e-5)
     assert float((ue != ug).float().mean()) < 1e-2 and float((te != tg).float().mean()) < 1e-2
+
+
+@pytest.mark.parametrize("mode", ["eager", "graph", "foreign"])
+def test_text_encoder_ema_follows_the_reference_rule(cuda, mode):
+    """training_utils.py:740-746: new_text_encoder_ema = rate * ema + (1 - rate) * new_params, every step; fused into
+    the text encoder's optimizer launches (eager / graph) or leaf by leaf for a tree that is not the arena's own."""
+    from oracle import lion as OL
+    ucfg, tcfg = PU.TINY, CL.TINY_CLIP
+    rate = 0.9
+    utree = LQ.unflatten_dict(PU.init_params_numpy(ucfg, 0))
+    ustate = TU.TrainState.create(apply_fn=TU.UNetModel(ucfg).apply, params=utree, tx=TU.create_lion_optimizer(utree),
+                                  device=cuda)
+    tp_np, _, tstate = _text_state(cuda, tcfg)
+    sched = TU.default_scheduler(cuda, "scaled_linear", "epsilon")
+    if mode == "foreign":
+        ema_tree = LQ.unflatten_dict({k: torch.from_numpy(v.copy()).to(cuda) for k, v in tp_np.items()})
+    else:
+        ema_tree = tstate.create_ema()
+    flags = dict(text_encoder_state=tstate, text_encoder_ema_params=ema_tree, ema_rate=rate)
+    step = TU.compile_train_step(ustate, sched, **flags) if mode == "graph" else \
+        (lambda s, b, r: TU.train_step(s, b, r, sched, **flags))
+    want = {k: v.copy() for k, v in tp_np.items()}
+    for s in (1, 2, 3):
+        b = {k: torch.from_numpy(v).to(cuda) for k, v in _joint_batch(2, 2, 16, tcfg.vocab_size, s).items()}
+        ustate, _ = step(ustate, b, None)
+        torch.cuda.synchronize()
+        new = {k: v.cpu().numpy() for k, v in LQ.flatten_dict(tstate.params).items()}
+        want = {k: OL.ema_update(want[k], new[k], rate) for k in want}
+    got = {k: v.cpu().numpy() for k, v in LQ.flatten_dict(ema_tree).items()}
+    moved = 0
+    for k in want:
+        assert np.array_equal(got[k].view(np.uint32), want[k].view(np.uint32)), k
+        moved += int(np.any(got[k] != tp_np[k]))
+    assert moved > len(want) // 2
+    if mode == "graph":
+        with pytest.raises(ValueError, match="text_encoder_ema_params"):
+            TU.compile_train_step(ustate, sched, text_encoder_state=tstate, text_encoder_ema_params={"x": 1}, ema_rate=rate)
