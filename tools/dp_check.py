@@ -15,7 +15,10 @@ Checks, on N ranks (N = WORLD_SIZE):
  (b) masters, Lion codes, reciprocal-absmax scales, fp32 momentum and the gradient arena are BIT-IDENTICAL across ranks
      after every step, in eager mode and in segmented-CUDA-graph mode (CompiledTrainStep);
  (c) in-step sampling: with noise / timesteps drawn from train_rng, rank r draws rows [r*B, (r+1)*B) of the global
-     draw (the N-rank losses equal the 1-rank loss on the concatenated batch).
+     draw (the N-rank losses equal the 1-rank loss on the concatenated batch);
+ (d) (--config tiny) the JOINT step — text encoder trained inside the step (training_utils.py:635-674, 733), both
+     TrainStates attached: losses / masters of both models against one rank on the concatenated batch, both arenas
+     bit-identical across ranks after every step, eager and CUDA graph.
 Rank 0 prints one JSON object and (with --out) writes it.
 """
 from __future__ import annotations
@@ -65,6 +68,69 @@ def make_state(cfg, params_np, dev):
     tree = LQ.unflatten_dict({k: torch.from_numpy(v) for k, v in params_np.items()})
     return TU.TrainState.create(apply_fn=TU.UNetModel(cfg).apply, params=tree, tx=TU.create_lion_optimizer(tree),
                                 device=dev)
+
+
+def joint_check(ucfg, uparams_np, sched, dev, rank, world, B, K, chunks=2):
+    from stable_diffusion_training_b200 import clip as CL
+    tcfg = CL.TINY_CLIP
+    tparams_np = CL.init_params_numpy(tcfg, 1)
+    G = B * world
+    H = 16
+    rng = np.random.default_rng(78)
+    gb = [{"latents": rng.standard_normal((G, 4, H, H), dtype=np.float32),
+           "noise": rng.standard_normal((G, 4, H, H), dtype=np.float32),
+           "timesteps": rng.integers(0, 1000, G).astype(np.int32),
+           "input_ids": rng.integers(0, tcfg.vocab_size, (G * chunks, 77)).astype(np.int32)} for _ in range(K)]
+
+    def states():
+        ust = make_state(ucfg, uparams_np, dev)
+        ttree = LQ.unflatten_dict({k: torch.from_numpy(v) for k, v in tparams_np.items()})
+        tst = TU.TrainState.create(apply_fn=CL.CLIPTextModel(tcfg).__call__, params=ttree,
+                                   tx=TU.create_lion_optimizer(ttree), device=dev)
+        return ust, tst
+
+    def part(b, lo, hi):
+        out = {k: torch.from_numpy(v[lo:hi]).to(dev) for k, v in b.items() if k != "input_ids"}
+        out["input_ids"] = torch.from_numpy(b["input_ids"][lo * chunks:hi * chunks]).to(dev)
+        return out
+
+    ust, tst = states()
+    ref_loss = []
+    for i in range(K):
+        ust, m = TU.train_step(ust, part(gb[i], 0, G), None, sched, text_encoder_state=tst)
+        ref_loss.append(float(m["loss"]))
+    ref_u, ref_t = ust.arena.master.clone(), tst.arena.master.clone()
+    del ust, tst
+    out = {"loss_1rank_concatenated": ref_loss, "modes": {}}
+    lr_bound = 2 * K * (1e-6 / 7) * 1.1
+    for mode in ("eager", "graph"):
+        ust, tst = states()
+        if world > 1:
+            parallel.attach(ust, sync="verify")
+            parallel.attach(tst, sync="verify")
+        step = TU.compile_train_step(ust, sched, text_encoder_state=tst) if mode == "graph" else \
+            (lambda s, b, r: TU.train_step(s, b, r, sched, text_encoder_state=tst))
+        losses, ident = [], []
+        for i in range(K):
+            ust, m = step(ust, part(gb[i], rank * B, (rank + 1) * B), None)
+            torch.cuda.synchronize()
+            losses.append(float(m["loss"]))
+            iu, it = ranks_identical(ust, world), ranks_identical(tst, world)
+            ident.append({"unet": iu, "text_encoder": it})
+        du = float((ust.arena.master - ref_u).abs().max())
+        dt = float((tst.arena.master - ref_t).abs().max())
+        ok = all(all(d["unet"].values()) and all(d["text_encoder"].values()) for d in ident)
+        ok = ok and all(abs(a - b) <= 2e-3 * abs(b) for a, b in zip(losses, ref_loss))
+        ok = ok and du <= lr_bound and dt <= lr_bound and int(tst.step) == K
+        out["modes"][mode] = {"loss": losses, "ranks_bit_identical_per_step": ident,
+                              "unet_masters_max_abs_diff_vs_1rank_concatenated": du,
+                              "text_masters_max_abs_diff_vs_1rank_concatenated": dt,
+                              "text_bytes_all_reduced": int(tst.dp.bytes_reduced) if tst.dp is not None else 0,
+                              "ok": bool(ok)}
+        del ust, tst, step
+        torch.cuda.empty_cache()
+    out["ok"] = bool(all(v["ok"] for v in out["modes"].values()))
+    return out
 
 
 def main():
@@ -193,7 +259,10 @@ def main():
             del st2
         del st, step
         torch.cuda.empty_cache()
-    report["ok"] = bool(all(v["ok"] for v in report["modes"].values()) and report["sampling"]["ok"])
+    if args.config == "tiny":
+        report["joint"] = joint_check(cfg, params_np, sched, dev, rank, world, B, K)
+    report["ok"] = bool(all(v["ok"] for v in report["modes"].values()) and report["sampling"]["ok"]
+                        and report.get("joint", {"ok": True})["ok"])
     if rank == 0:
         print(json.dumps(report))
         if args.out:
