@@ -20,7 +20,7 @@ Rounding model (`mode`):
 from __future__ import annotations
 
 import math
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Dict, Tuple
 
 import torch

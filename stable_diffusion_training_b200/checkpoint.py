@@ -29,8 +29,6 @@ import msgpack
 import numpy as np
 import torch
 
-from .lion_quant import flatten_dict, unflatten_dict
-
 _EXT_NDARRAY, _EXT_NPSCALAR = 1, 3
 _MAX_CHUNK_SIZE = 2 ** 30
 

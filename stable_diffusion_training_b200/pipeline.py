@@ -28,7 +28,6 @@ from . import _lib, ops
 from . import clip as CL
 from . import jax_random as JR
 from . import unet as UN
-from . import vae as VA
 from .lion_quant import flatten_dict
 
 BF16 = torch.bfloat16

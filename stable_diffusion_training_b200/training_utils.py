@@ -22,10 +22,9 @@ views with the reference's tree structure and the (int8 codes, fp32 reciprocal-a
 """
 from __future__ import annotations
 
-import math
 import os
-from dataclasses import dataclass, field
-from typing import Any, Callable, Dict, List, Optional, Tuple
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Tuple
 
 import numpy as np
 import torch
@@ -36,7 +35,7 @@ from . import lion_quant as LQ
 from .lion_quant import create_mask, flatten_dict, unflatten_dict
 from .schedulers import FlaxDDPMScheduler
 from . import clip as CL
-from .unet import SD15, T, UNet, UNetConfig, init_params_numpy, layer_program, param_shapes
+from .unet import SD15, UNet, UNetConfig, init_params_numpy, layer_program, param_shapes
 
 
 @dataclass

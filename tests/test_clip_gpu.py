@@ -9,7 +9,6 @@ PyTorch CLIPTextModel (tests/test_oracle_clip.py):
    with BOS / EOS stripping (641-674), UNet, loss, both backward passes, both Lion updates (732-733) — loss and BOTH
    gradient sets vs the oracle; compiled (CUDA graph) == eager.
 """
-import math
 
 import numpy as np
 import pytest

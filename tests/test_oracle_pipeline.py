@@ -87,8 +87,7 @@ def test_bf16_emulation_stays_close_to_exact_arithmetic():
 
 # ---- product pipeline: argument handling that needs no GPU ------------------------------------------------------
 def _product_pipeline():
-    from stable_diffusion_training_b200 import clip as PC, pipeline as PP, schedulers as PS, training_utils as TU, \
-        unet as PU, vae as PV
+    from stable_diffusion_training_b200 import clip as PC, pipeline as PP, training_utils as TU, unet as PU, vae as PV
     return PP, PP.FlaxStableDiffusionPipeline(vae=PV.AutoencoderKL(PV.TINY_VAE), text_encoder=PC.CLIPTextModel(PC.TINY_CLIP),
                                               tokenizer=None, unet=TU.UNetModel(PU.TINY), scheduler=None)
 
