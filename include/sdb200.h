@@ -22,7 +22,7 @@
 extern "C" {
 #endif
 
-#define SDB200_ABI_VERSION 5
+#define SDB200_ABI_VERSION 6
 
 #ifndef __CUDA_RUNTIME_H__
 typedef struct CUstream_st* cudaStream_t;
@@ -190,7 +190,11 @@ typedef struct {
   const void* residual;
   long long ldr;
   int m_halves;         /* sdb_gemm_tc: M tile = 128 * m_halves rows (1 or 2; 0 = 1). Two halves share every B stage */
-  long long splitk_slab; /* FWD split-K: elements between per-range slabs (see splits); 0 = atomic accumulation */
+  long long splitk_slab; /* FWD split-K: elements between per-range slabs (see splits); 0 = atomic accumulation.
+                            WGRAD with splits > 1: > 0 = every pixel range stores its dW-shaped partial result into the
+                            slab D + s * splitk_slab (the effective number of ranges is ceil(PB / ceil(PB / splits)),
+                            PB = pixel blocks of 64); fold them with sdb_splitk_finish_f32 — run-to-run identical
+                            bits. 0 = the call zeroes dW and the ranges accumulate with red.global.add (order varies) */
 } sdb_gemm_desc;
 
 int sdb_gemm_tc(const sdb_gemm_desc* desc, cudaStream_t stream);
@@ -211,9 +215,12 @@ int sdb_conv3x3_c4out_fwd(const void* x, const void* w_hwio, const float* bias, 
 int sdb_conv3x3_c4out_dgrad(const void* dy4, const void* w_hwio, void* dx, int B, int H, int W, int C,
                             cudaStream_t stream);
 /* c4_is_input = 1: conv_in  (c4 = x [B,H,W,4],  wide = dy [B,H,W,C]) -> dw [3,3,4,C]
- * c4_is_input = 0: conv_out (c4 = dy [B,H,W,4], wide = x  [B,H,W,C]) -> dw [3,3,C,4] */
+ * c4_is_input = 0: conv_out (c4 = dy [B,H,W,4], wide = x  [B,H,W,C]) -> dw [3,3,C,4]
+ * workspace (sdb_conv3x3_c4_wgrad_workspace_bytes(C) bytes): every CTA stores its partial dw there and a second launch
+ * folds them in CTA order — run-to-run identical bits; NULL: red.global.add into the zeroed dw (order varies). */
+size_t sdb_conv3x3_c4_wgrad_workspace_bytes(int C);
 int sdb_conv3x3_c4_wgrad(const void* wide, const void* c4, float* dw, int B, int H, int W, int C, int c4_is_input,
-                         cudaStream_t stream);
+                         void* workspace, size_t ws_bytes, cudaStream_t stream);
 
 /* ---- normalisation / activation (flax.linen GroupNorm, LayerNorm, nn.gelu as used by diffusers-0.21.4
  * FlaxResnetBlock2D / FlaxTransformer2DModel / FlaxBasicTransformerBlock / FlaxGEGLU [upstream, un-vendored], reached
@@ -328,6 +335,10 @@ int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStrea
 int sdb_splitk_finish(const float* acc, long long lda, int nslabs, long long slab_stride, const float* bias,
                       const void* temb, long long ldt, long long rows_per_image, const void* residual, long long ldr,
                       void* out, long long ldo, long long rows, int N, cudaStream_t stream);
+/* out[i] = slab_0[i] + slab_1[i] + ... (fixed order): the fold of a slab-mode split weight gradient (sdb_gemm_tc, WGRAD,
+ * splitk_slab > 0); n elements per slab, n % 4 == 0. */
+int sdb_splitk_finish_f32(const float* slabs, int nslabs, long long slab_stride, float* out, long long n,
+                          cudaStream_t stream);
 /* acc: nslabs fp32 [rows, lda] slabs slab_stride elements apart, summed in slab order (nslabs = 1: one buffer). */
 size_t sdb_colsum_workspace_bytes(long long rows, int cols);
 int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long rows_per_seg, int cols, float* out_total,

@@ -73,7 +73,8 @@ SIGNATURES = {
     "sdb_conv3x3_c4in_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "sdb_conv3x3_c4out_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "sdb_conv3x3_c4out_dgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _P]),
-    "sdb_conv3x3_c4_wgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "sdb_conv3x3_c4_wgrad_workspace_bytes": (_SZ, [_I]),
+    "sdb_conv3x3_c4_wgrad": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _SZ, _P]),
     "sdb_groupnorm_workspace_bytes": (_SZ, [_I, _I, _I]),
     "sdb_groupnorm_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _F, _I, _P, _SZ, _P]),
     "sdb_groupnorm_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P, _SZ, _P]),
@@ -109,6 +110,7 @@ SIGNATURES = {
     "sdb_copy2d_bf16": (_I, [_P, _LL, _P, _LL, _LL, _I, _I, _P]),
     "sdb_add_bf16": (_I, [_P, _P, _P, _LL, _P]),
     "sdb_splitk_finish": (_I, [_P, _LL, _I, _LL, _P, _P, _LL, _LL, _P, _LL, _P, _LL, _LL, _I, _P]),
+    "sdb_splitk_finish_f32": (_I, [_P, _I, _LL, _P, _LL, _P]),
     "sdb_colsum_workspace_bytes": (_SZ, [_LL, _I]),
     "sdb_colsum_bf16": (_I, [_P, _LL, _I, _LL, _I, _P, _P, _P, _SZ, _P]),
     "sdb_silu_fwd": (_I, [_P, _P, _LL, _P]),

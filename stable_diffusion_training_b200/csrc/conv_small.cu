@@ -128,7 +128,7 @@ wide_to_c4_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __re
 template <bool C4_IS_INPUT>
 __global__ void __launch_bounds__(1024)
 wgrad_c4_kernel(const __nv_bfloat16* __restrict__ wide, const __nv_bfloat16* __restrict__ c4, float* __restrict__ dw, int B,
-                int H, int W, int C, long long pix_per_cta) {
+                int H, int W, int C, long long pix_per_cta, float* __restrict__ partials) {
   sdb::pdl_trigger();
   const int nv = C / 8;
   const int tap = threadIdx.x / nv, v = threadIdx.x % nv;
@@ -159,10 +159,23 @@ wgrad_c4_kernel(const __nv_bfloat16* __restrict__ wide, const __nv_bfloat16* __r
   for (int i = 0; i < 8; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
-      float* dst = C4_IS_INPUT ? dw + ((long long)tap * 4 + j) * C + v * 8 + i
-                               : dw + ((long long)tap * C + v * 8 + i) * 4 + j;
-      asm volatile("red.global.add.f32 [%0], %1;" ::"l"(dst), "f"(acc[i][j]) : "memory");
+      const long long o = C4_IS_INPUT ? ((long long)tap * 4 + j) * C + v * 8 + i : ((long long)tap * C + v * 8 + i) * 4 + j;
+      if (partials != nullptr)  // this CTA's own dW-shaped slab, folded afterwards in CTA order (deterministic)
+        partials[(long long)blockIdx.x * 36 * C + o] = acc[i][j];
+      else
+        asm volatile("red.global.add.f32 [%0], %1;" ::"l"(dw + o), "f"(acc[i][j]) : "memory");
     }
+}
+
+// dw[i] = sum over CTAs, in CTA order, of partials[cta][i]
+__global__ void __launch_bounds__(256) wgrad_c4_fold_kernel(const float* __restrict__ partials, int nparts, int n,
+                                                            float* __restrict__ dw) {
+  sdb::pdl_trigger();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float a = 0.f;
+  for (int s = 0; s < nparts; ++s) a += partials[(long long)s * n + i];
+  dw[i] = a;
 }
 
 int check_c4(const char* name, int B, int H, int W, int C) {
@@ -232,12 +245,20 @@ extern "C" int sdb_conv3x3_c4out_fwd(const void* x, const void* w, const float* 
   return SDB_OK;
 }
 
+extern "C" size_t sdb_conv3x3_c4_wgrad_workspace_bytes(int C) { return (size_t)2 * sdb::kNumSMs * 36 * C * sizeof(float); }
+
 extern "C" int sdb_conv3x3_c4_wgrad(const void* wide, const void* c4, float* dw, int B, int H, int W, int C,
-                                    int c4_is_input, cudaStream_t stream) {
+                                    int c4_is_input, void* workspace, size_t ws_bytes, cudaStream_t stream) {
   int rc = check_c4("sdb_conv3x3_c4_wgrad", B, H, W, C);
   if (rc) return rc;
-  cudaError_t e = cudaMemsetAsync(dw, 0, (size_t)36 * C * sizeof(float), stream);
-  if (e != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_conv3x3_c4_wgrad: memset: %s", cudaGetErrorString(e));
+  float* partials = reinterpret_cast<float*>(workspace);
+  if (partials != nullptr && ws_bytes < sdb_conv3x3_c4_wgrad_workspace_bytes(C))
+    return sdb_set_error(SDB_ERR_WORKSPACE, "sdb_conv3x3_c4_wgrad: workspace %zu < %zu", ws_bytes,
+                         sdb_conv3x3_c4_wgrad_workspace_bytes(C));
+  if (partials == nullptr) {  // no workspace: the CTAs accumulate into the zeroed dw with red.global.add (order varies)
+    cudaError_t e = cudaMemsetAsync(dw, 0, (size_t)36 * C * sizeof(float), stream);
+    if (e != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_conv3x3_c4_wgrad: memset: %s", cudaGetErrorString(e));
+  }
   const long long npix = (long long)B * H * W;
   int blocks = 2 * sdb::kNumSMs;
   if (blocks > npix) blocks = (int)npix;
@@ -246,10 +267,14 @@ extern "C" int sdb_conv3x3_c4_wgrad(const void* wide, const void* c4, float* dw,
   const int threads = ((9 * (C / 8) + 31) / 32) * 32;
   if (c4_is_input)
     wgrad_c4_kernel<true><<<blocks, threads, 0, stream>>>((const __nv_bfloat16*)wide, (const __nv_bfloat16*)c4, dw, B, H, W,
-                                                         C, ppc);
+                                                         C, ppc, partials);
   else
     wgrad_c4_kernel<false><<<blocks, threads, 0, stream>>>((const __nv_bfloat16*)wide, (const __nv_bfloat16*)c4, dw, B, H,
-                                                          W, C, ppc);
+                                                          W, C, ppc, partials);
   SDB_CUDA_LAUNCH_CHECK("sdb_conv3x3_c4_wgrad");
+  if (partials != nullptr) {
+    wgrad_c4_fold_kernel<<<(36 * C + 255) / 256, 256, 0, stream>>>(partials, blocks, 36 * C, dw);
+    SDB_CUDA_LAUNCH_CHECK("sdb_conv3x3_c4_wgrad(fold)");
+  }
   return SDB_OK;
 }

@@ -453,6 +453,32 @@ extern "C" int sdb_splitk_finish(const float* acc, long long lda, int nslabs, lo
   return SDB_OK;
 }
 
+// out[i] = slab_0[i] + slab_1[i] + ... in that order: the fold of a slab-mode split weight gradient (fp32 in, fp32 out)
+__global__ void splitk_finish_f32_kernel(const float* __restrict__ slabs, int nslabs, long long slab_stride,
+                                         float* __restrict__ out, long long nvec) {
+  sdb::pdl_trigger();
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float4 a = sdb::ld_f4(slabs + 4 * i);
+    for (int s = 1; s < nslabs; ++s) {
+      const float4 b = sdb::ld_f4(slabs + (long long)s * slab_stride + 4 * i);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    sdb::st_f4(out + 4 * i, a);
+  }
+}
+
+extern "C" int sdb_splitk_finish_f32(const float* slabs, int nslabs, long long slab_stride, float* out, long long n,
+                                     cudaStream_t stream) {
+  SDB_CHECK_ARG(slabs != nullptr && out != nullptr && n > 0 && n % 4 == 0, "sdb_splitk_finish_f32: bad arguments");
+  SDB_CHECK_ARG(nslabs >= 1 && (nslabs == 1 || (slab_stride >= n && slab_stride % 4 == 0)),
+                "sdb_splitk_finish_f32: bad slab layout (nslabs %d, stride %lld)", nslabs, slab_stride);
+  SDB_CHECK_ARG((((uintptr_t)slabs | (uintptr_t)out) & 15) == 0, "sdb_splitk_finish_f32: 16-byte alignment required");
+  splitk_finish_f32_kernel<<<ew_grid(n / 4), 256, 0, stream>>>(slabs, nslabs, slab_stride, out, n / 4);
+  SDB_CUDA_LAUNCH_CHECK("sdb_splitk_finish_f32");
+  return SDB_OK;
+}
+
 extern "C" int sdb_add_bf16(const void* a, const void* b, void* out, long long n, cudaStream_t stream) {
   SDB_CHECK_ARG(n % 8 == 0, "sdb_add_bf16: n must be a multiple of 8");
   if (n == 0) return SDB_OK;

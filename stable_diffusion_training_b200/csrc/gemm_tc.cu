@@ -429,7 +429,10 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
       } else {
         const int m = ti.m_off + row;
         const bool valid = (m < p.M) && !SDB_DBG(p, 2);
-        float* out = reinterpret_cast<float*>(p.d) + ((long long)p.tap_brow[ti.tap] + m) * p.ldd + ti.n_off;
+        // split over pixel ranges: red.global.add into the zeroed dW (default), or — slab mode — plain stores into this
+        // range's own dW-shaped slab, folded afterwards in a fixed order (sdb_splitk_finish_f32: run-to-run identical bits)
+        float* out = reinterpret_cast<float*>(p.d) + (long long)ti.split * p.slab +
+                     ((long long)p.tap_brow[ti.tap] + m) * p.ldd + ti.n_off;
         for (int c0 = c_first; c0 < ti.nw; c0 += c_step) {
           uint32_t v[32];
           ptx::tmem_ld_32x32(taddr + (uint32_t)c0, v);
@@ -439,7 +442,7 @@ __global__ void __launch_bounds__(kThreads, 1) gemm_tc_kernel(const __grid_const
             for (int j4 = 0; j4 < 32; j4 += 4) {
               if (c0 + j4 < ti.nw) {
                 float* dst = out + c0 + j4;
-                if (p.splits > 1) {
+                if (p.splits > 1 && p.slab == 0) {
                   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst),
                                "f"(__uint_as_float(v[j4])), "f"(__uint_as_float(v[j4 + 1])),
                                "f"(__uint_as_float(v[j4 + 2])), "f"(__uint_as_float(v[j4 + 3]))
@@ -631,9 +634,13 @@ extern "C" int sdb_gemm_tc(const sdb_gemm_desc* d, cudaStream_t stream) {
     p.total_tiles = p.ntaps * p.tiles_m * p.tiles_n * p.splits;
     rc = encode_view(&p.mapB, d->b, 64, d->bw, d->bh, d->bn, "B (wgrad output gradients)");
     if (rc) return rc;
-    if (p.splits > 1) {  // the pixel ranges are accumulated with red.global.add: start from zero (a memset node, no SMs)
-      int last_row = 0;
-      for (int t = 0; t < d->ntaps; ++t) last_row = d->tap_brow[t] > last_row ? d->tap_brow[t] : last_row;
+    int last_row = 0;
+    for (int t = 0; t < d->ntaps; ++t) last_row = d->tap_brow[t] > last_row ? d->tap_brow[t] : last_row;
+    if (p.splits > 1 && d->splitk_slab > 0) {  // deterministic mode: one dW-shaped slab per pixel range, plain stores
+      SDB_CHECK_ARG(d->splitk_slab >= ((long long)last_row + d->M) * d->ldd && d->splitk_slab % 4 == 0,
+                    "sdb_gemm_tc: splitk_slab (%lld) must cover the dW rows x ldd and be a multiple of 4", d->splitk_slab);
+      p.slab = d->splitk_slab;
+    } else if (p.splits > 1) {  // the pixel ranges are accumulated with red.global.add: start from zero (a memset node, no SMs)
       const cudaError_t me = cudaMemset2DAsync(d->d, (size_t)d->ldd * sizeof(float), 0, (size_t)d->N * sizeof(float),
                                                (size_t)last_row + (size_t)d->M, stream);
       if (me != cudaSuccess) return sdb_set_error(SDB_ERR_CUDA, "sdb_gemm_tc: memset: %s", cudaGetErrorString(me));

@@ -186,6 +186,10 @@ def _pick_splitk(N: int, pix, b_mn: bool, nkb: int, mt0: int, bn0: int):
 # experiment switch (SDB_EXPERIMENTS=1 SDB_SPLITK_RED=1): accumulate split-K partial sums with red.global.add into one
 # buffer (the round-1 path, schedule-dependent summation order) instead of per-range slabs folded in a fixed order
 _SPLITK_RED = _lib.experiments_enabled() and os.environ.get("SDB_SPLITK_RED") == "1"
+# SDB_DETERMINISTIC=1 (or ops.DETERMINISTIC = True before the first step / graph capture): split weight gradients go
+# through per-range slabs folded in a fixed order instead of red.global.add — with the slab split-K forward this makes a
+# UNet train step reproduce bit for bit from run to run (the text encoder's token-embedding gradient still uses atomics)
+DETERMINISTIC = os.environ.get("SDB_DETERMINISTIC", "0") == "1"
 _SKIP_GEMM = set(x for x in os.environ.get("SDB_SKIP", "").split(",") if x.startswith("gemm_")) \
     if _lib.experiments_enabled() else set()
 
@@ -291,6 +295,20 @@ def gemm_wgrad(a_views, taps, b_view: View4, out: torch.Tensor, pix, M: int, N: 
     total_pb = -(-W // d.bw) * -(-H // d.bh) * -(-NI // d.bn)
     splits = max(1, min(total_pb, (2 * NUM_SMS) // max(1, tiles)))
     d.splits = splits  # > 1: sdb_gemm_tc zeroes the output rows itself (memset node) before the red.add accumulation
+    if DETERMINISTIC and splits > 1 and not (impl == "tc" and out.is_contiguous()):
+        d.splits = splits = 1   # the CUDA-core cross-check path / strided outputs: one pixel range, no atomics
+    if DETERMINISTIC and splits > 1:
+        # deterministic mode: every pixel range writes its own dW-shaped slab, folded in a fixed order
+        nslabs = -(-total_pb // -(-total_pb // splits))   # the library's effective number of ranges
+        n = out.numel()
+        ws = workspace(out.device, nslabs * n * 4)
+        d.d = ws.data_ptr()
+        d.ldd = N
+        d.splitk_slab = n
+        _launch(d, impl)
+        _lib.check(_lib.lib().sdb_splitk_finish_f32(ws.data_ptr(), nslabs, n, out.data_ptr(), n, _lib.stream_ptr()),
+                   "sdb_splitk_finish_f32")
+        return
     d.d = out.data_ptr()
     d.ldd = out.stride(0)
     _launch(d, impl)
@@ -404,8 +422,11 @@ def conv3x3_c4_wgrad(x, dy, *, out):
     B, H, W, cin = x.shape
     c4_is_input = cin == 4
     wide, c4 = (dy, x) if c4_is_input else (x, dy)
+    # per-CTA partial sums folded in CTA order (no atomics: the same bits every run; +~5 us on a 0.13 ms kernel)
+    ws = workspace(out.device, _lib.lib().sdb_conv3x3_c4_wgrad_workspace_bytes(wide.shape[3]))
     _lib.check(_lib.lib().sdb_conv3x3_c4_wgrad(wide.data_ptr(), c4.data_ptr(), out.data_ptr(), B, H, W, wide.shape[3],
-                                               int(c4_is_input), _lib.stream_ptr()), "sdb_conv3x3_c4_wgrad")
+                                               int(c4_is_input), ws.data_ptr(), ws.numel(), _lib.stream_ptr()),
+               "sdb_conv3x3_c4_wgrad")
     return out
 
 

@@ -26,7 +26,7 @@ def test_header_symbols_exported_and_bound():
 
 def test_library_level_calls_without_gpu():
     l = _lib.lib()
-    assert l.sdb_abi_version() == 5
+    assert l.sdb_abi_version() == 6
     assert l.sdb_sumsq_workspace_bytes() > 0
     assert l.sdb_launch_count() >= 0
     # argument validation happens before any CUDA call and reports through the error string

@@ -77,7 +77,7 @@ def test_c_abi_exports_every_declared_symbol():
     for name in declared:
         assert hasattr(lib, name), f"{name} declared in sdb200.h but not exported"
     assert declared == set(_lib.SIGNATURES), (declared ^ set(_lib.SIGNATURES))
-    assert lib.sdb_abi_version() == 5
+    assert lib.sdb_abi_version() == 6
     assert isinstance(lib.sdb_last_error_string(), bytes)
     # struct layout agreement between ctypes and the header
     assert ctypes.sizeof(_lib.View4) == 48
