@@ -206,6 +206,7 @@ def run_ours(args):
         train_rng = JR.RngStream(1234)
     step_fn = TU.compile_train_step(state, sched, **extra) if args.graph else \
         (lambda s, b, r: TU.train_step(s, b, r, frozen_noise_scheduler_state=sched, **extra))
+    compiled = step_fn if args.graph else None
     if full:  # the step draws VAE sample noise, diffusion noise and timesteps itself from train_rng
         inner = step_fn
         step_fn = lambda s, b, r: inner(s, b, train_rng)
@@ -234,8 +235,8 @@ def run_ours(args):
     e1.record()
     barrier()
     launches = L.sdb_launch_count() - n0
-    if args.graph:
-        launches = getattr(step_fn, "launches_per_replay", 0) * args.steps
+    if compiled is not None:  # replays do not pass through the library's counter; what runs eagerly around them does
+        launches += compiled.launches_per_replay * args.steps   # (the frozen VAE encode, the Threefry draws)
     ms = e0.elapsed_time(e1)
     loss_last = float(m["loss"])
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
