@@ -77,6 +77,11 @@ int sdb_add_f32(const float* a, const float* b, float* out, long long n, cudaStr
  * nranks - 1 device pointers (ascending rank, self skipped) holding the slices pulled from the peers. nranks <= 9. */
 int sdb_sum_slices_f32(float* dst, const float* const* staged_host, int nranks, int self_pos, long long n,
                        cudaStream_t stream);
+/* The same exchange step through NVSwitch multicast (NVLS): `multicast_slice` is the multicast address of this rank's
+ * slice of the bucket (every rank's gradient arena bound to one multicast object); the switch returns the sum over
+ * ranks (multimem.ld_reduce) and the kernel stores it to every rank's copy (multimem.st). Call between two cross-rank
+ * barriers; every rank calls it on ITS slice, so all ranks end with identical bits. ctas <= 0: 148. */
+int sdb_nvls_allreduce_f32(float* multicast_slice, long long n, int ctas, cudaStream_t stream);
 
 /* ---- schedulers (schedulers/scheduling_utils_flax.py:316-343; scheduling_ddpm_flax.py:196-297) ----
  * alphas_cumprod has num_timesteps entries; a timestep outside the table is wrapped once if negative and clamped,

@@ -58,6 +58,7 @@ SIGNATURES = {
     "sdb_clip_by_global_norm_f32": (_I, [_P, _P, _LL, _P, _D, _P]),
     "sdb_add_f32": (_I, [_P, _P, _P, _LL, _P]),
     "sdb_sum_slices_f32": (_I, [_P, _P, _I, _I, _LL, _P]),
+    "sdb_nvls_allreduce_f32": (_I, [_P, _LL, _I, _P]),
     "sdb_add_noise": (_I, [_P, _P, _P, _P, _I, _P, _I, _LL, _P]),
     "sdb_get_velocity": (_I, [_P, _P, _P, _P, _I, _P, _I, _LL, _P]),
     "sdb_ddpm_step": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _F, _I, _I, _P]),

@@ -158,6 +158,17 @@ class PeerAllReduce:
                      for p in range(self.world)]
         self.stage: Optional[torch.Tensor] = None
         self.direct = os.environ.get("SDB_DP_PEER_DIRECT", "0") == "1"
+        # NVLS variant (SDB_DP_ALLREDUCE=nvls): the arena is also bound to an NVSwitch multicast object; the exchange is
+        # ONE kernel per bucket slice (multimem.ld_reduce through the switch + multimem.st to every rank) instead of
+        # pull / sum / push: each gradient crosses this rank's HBM once in and once out (no staging copies)
+        self.mc_ptr = int(getattr(self.hdl, "multicast_ptr", 0) or 0)
+        self.nvls = os.environ.get("SDB_DP_ALLREDUCE", "peer") == "nvls"
+        if self.nvls and self.mc_ptr == 0:
+            if self.rank == 0:
+                sys.stderr.write("[sdb dp] SDB_DP_ALLREDUCE=nvls: no multicast support on this system, using the "
+                                 "copy-engine exchange\n")
+            self.nvls = False
+        self.nvls_ctas = int(os.environ.get("SDB_DP_NVLS_CTAS", "0"))
 
     def _slices(self, s: int, e: int):
         n = e - s
@@ -166,6 +177,8 @@ class PeerAllReduce:
         return [(min(e, s + q * per), min(e, s + (q + 1) * per)) for q in range(self.world)]
 
     def prepare(self, max_bucket_elems: int) -> None:
+        if self.nvls:
+            return   # no staging buffers
         per = -(-(-(-max_bucket_elems // self.world)) // 4) * 4
         self.stage = torch.empty((max(self.world - 1, 1), per), dtype=torch.float32, device=self.buf.device)
 
@@ -177,6 +190,11 @@ class PeerAllReduce:
         a, b = self._slices(s, e)[r]
         n = b - a
         self.hdl.barrier(channel=0, timeout_ms=30000)
+        if self.nvls:
+            if n > 0:
+                _lib.check(_lib.lib().sdb_nvls_allreduce_f32(self.mc_ptr + 4 * a, n, self.nvls_ctas,
+                                                             _lib.stream_ptr(self.buf.device)), "sdb_nvls_allreduce_f32")
+            return
         order = [(r + k) % W for k in range(1, W)]           # start with the next rank: spreads the NVLink load
         if n > 0:
             if self.direct:
@@ -432,7 +450,7 @@ def attach(state, group=None, bucket_bytes: int = DEFAULT_BUCKET_BYTES, sync: st
     _replicate_state(state, group, sync)
     peer = None
     mode = os.environ.get("SDB_DP_ALLREDUCE", "peer")
-    if a.device.type == "cuda" and dist.is_initialized() and dist.get_world_size(group) > 1 and mode == "peer":
+    if a.device.type == "cuda" and dist.is_initialized() and dist.get_world_size(group) > 1 and mode in ("peer", "nvls"):
         # the gradient arena moves into symmetric memory (peers read / write it directly); every view is rebound
         peer = PeerAllReduce(a.n_total, a.device, group)
         a.grad = peer.buf

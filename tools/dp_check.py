@@ -237,6 +237,8 @@ def main():
             "masters_max_abs_diff_vs_1rank": max_master,
             "ranks_bit_identical_per_step": ident,
             "bytes_all_reduced": int(st.dp.bytes_reduced) if st.dp is not None else 0,
+            "exchange": ("nvls" if st.dp.peer.nvls else "peer") if (st.dp is not None and st.dp.peer is not None) else
+                        ("nccl" if st.dp is not None else "none"),
         }
         ok = all(all(d.values()) for d in ident)
         # strict: against the micro-batched single rank (same kernels): fp32 summation order only
