@@ -350,6 +350,18 @@ int sdb_colsum_bf16(const void* x, long long ld, int nseg, long long rows_per_se
                     void* out_seg_bf16, void* workspace, size_t ws_bytes, cudaStream_t stream);
 /* column sums of a bf16 [nseg*rows_per_seg, cols] matrix: out_total[c] (fp32, nullable) = bias gradient;
  * out_seg[s][c] (bf16, nullable) = per-image sums = gradient of the broadcast time-embedding add. */
+/* Allocation-free variant of sdb_colsum_bf16 (one segment, out_total only). It has NO counterpart in the reference: it was
+ * added for callers that cannot allocate (CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). The partial sums go to a file-scope static __device__ array of
+ * sdb_colsum_static_max_scratch_bytes() = 2 MiB that every GPU loading the library holds until exit; the call itself
+ * allocates nothing (no cudaMalloc / cudaFree / allocating library routine) and returns an error (-3) for shapes whose
+ * partial sums exceed the array (ceil(rows / rpb) * cols * 4 bytes, rpb in [32, 256] as sdb_colsum_bf16 picks it: e.g.
+ * [32768, 2560] fits, [262144, 2560] does not). The array is shared by all calls on a device and keeps the last call's
+ * contents (nothing needs clearing: every partial sum read was written by the same call): calls on one stream are
+ * ordered; calls that overlap on the GPU (different streams) race on it. x bf16 [rows, cols], row stride ld (elements),
+ * cols % 8 == 0, ld % 8 == 0, 16-byte aligned; out_total fp32 [cols]. */
+size_t sdb_colsum_static_max_scratch_bytes(void);
+int sdb_colsum_bf16_static(const void* x, long long ld, long long rows, int cols, float* out_total, cudaStream_t stream);
 int sdb_silu_fwd(const void* x, void* y, long long n, cudaStream_t stream);
 int sdb_silu_bwd(const void* x, const void* dy, void* dx, long long n, cudaStream_t stream);
 int sdb_timestep_embedding(const int* timesteps, void* out, int B, int dim, int flip_sin_to_cos, float freq_shift,

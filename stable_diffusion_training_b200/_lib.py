@@ -114,6 +114,8 @@ SIGNATURES = {
     "sdb_splitk_finish_f32": (_I, [_P, _I, _LL, _P, _LL, _P]),
     "sdb_colsum_workspace_bytes": (_SZ, [_LL, _I]),
     "sdb_colsum_bf16": (_I, [_P, _LL, _I, _LL, _I, _P, _P, _P, _SZ, _P]),
+    "sdb_colsum_static_max_scratch_bytes": (_SZ, []),
+    "sdb_colsum_bf16_static": (_I, [_P, _LL, _LL, _I, _P, _P]),
     "sdb_silu_fwd": (_I, [_P, _P, _LL, _P]),
     "sdb_silu_bwd": (_I, [_P, _P, _P, _LL, _P]),
     "sdb_timestep_embedding": (_I, [_P, _P, _I, _I, _I, _F, _P]),

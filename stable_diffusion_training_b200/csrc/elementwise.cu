@@ -560,3 +560,75 @@ extern "C" int sdb_timestep_embedding(const int* timesteps, void* out, int B, in
   SDB_CUDA_LAUNCH_CHECK("sdb_timestep_embedding");
   return SDB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free column sum (no counterpart in the reference).
+// The partial sums of sdb_colsum_bf16 live in a caller-provided workspace (torch's allocator in this package). Callers
+// that must not allocate — code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc — get
+// the same result from a scratch array that is part of the library image: every GPU that loads libsdb200.so holds these
+// 2 MiB until the process exits.
+//   * One array per device, shared by every call: two calls that overlap on the GPU (different streams) RACE on it.
+//     Calls on one stream are ordered and safe.
+//   * The array keeps the previous call's partial sums; nothing has to start at zero (every element that the second
+//     launch reads was written by the first launch of the same call), so nothing is cleared.
+//   * In host code `g_colsum_static_scratch` is only a stand-in for the symbol: the device address comes from
+//     cudaGetSymbolAddress, once per device, with that device current.
+namespace {
+constexpr size_t kColsumStaticBytes = (size_t)2 << 20;
+static __device__ __align__(256) float g_colsum_static_scratch[kColsumStaticBytes / sizeof(float)];
+
+constexpr int kMaxDevices = 64;
+std::mutex g_static_scratch_mutex;
+float* g_static_scratch_ptr[kMaxDevices] = {};
+
+// device address of the calling thread's current device's copy of the array (nullptr + error set on failure)
+float* colsum_static_scratch_ptr() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    sdb_set_error(SDB_ERR_CUDA, "sdb_colsum_bf16_static: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(g_static_scratch_mutex);
+  if (g_static_scratch_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_colsum_static_scratch);
+    if (e != cudaSuccess || p == nullptr) {
+      sdb_set_error(SDB_ERR_CUDA, "sdb_colsum_bf16_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return nullptr;
+    }
+    g_static_scratch_ptr[dev] = p;
+  }
+  return g_static_scratch_ptr[dev];
+}
+}  // namespace
+
+extern "C" size_t sdb_colsum_static_max_scratch_bytes(void) { return kColsumStaticBytes; }
+
+extern "C" int sdb_colsum_bf16_static(const void* x, long long ld, long long rows, int cols, float* out_total,
+                                      cudaStream_t stream) {
+  SDB_CHECK_ARG(x != nullptr && out_total != nullptr, "sdb_colsum_bf16_static: null pointer");
+  SDB_CHECK_ARG(cols > 0 && cols % 8 == 0 && ld % 8 == 0 && ld >= cols && rows > 0 && rows < (1ll << 31),
+                "sdb_colsum_bf16_static: cols / ld must be multiples of 8, ld >= cols, 0 < rows < 2^31");
+  SDB_CHECK_ARG((((uintptr_t)x) & 15) == 0, "sdb_colsum_bf16_static: x needs 16-byte alignment");
+  // the grid of sdb_colsum_bf16 for one segment: rows per block halved until ~2 waves of blocks exist
+  const int col_chunks = (cols + 255) / 256;
+  int rpb = 256;
+  while (rpb > kColsumMinRows && ((rows + rpb - 1) / rpb) * col_chunks < 2 * sdb::kNumSMs) rpb >>= 1;
+  const int bps = (int)((rows + rpb - 1) / rpb);
+  const size_t need = (size_t)bps * cols * sizeof(float);
+  if (need > kColsumStaticBytes)
+    return sdb_set_error(SDB_ERR_WORKSPACE,
+                         "sdb_colsum_bf16_static: [%lld, %d] needs %zu bytes of partial sums, the static scratch holds "
+                         "%zu (use sdb_colsum_bf16 with a caller-provided workspace)",
+                         rows, cols, need, kColsumStaticBytes);
+  float* part = colsum_static_scratch_ptr();
+  if (part == nullptr) return SDB_ERR_CUDA;
+  // two launches, no arrival counters: no state besides the scratch array
+  colsum_partial_kernel<<<dim3(bps, col_chunks), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), ld, rows,
+                                                                   bps, rpb, cols, part, 1, nullptr, nullptr, nullptr);
+  SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16_static(partial)");
+  colsum_final_kernel<<<(cols + 31) / 32, 256, 0, stream>>>(part, 1, bps, cols, out_total, nullptr);
+  SDB_CUDA_LAUNCH_CHECK("sdb_colsum_bf16_static(final)");
+  return SDB_OK;
+}
