@@ -5,11 +5,16 @@
 
     <dir>/unet/config.json                          the FlaxUNet2DConditionModel config
     <dir>/unet/diffusion_flax_model.msgpack         flax.serialization.to_bytes(params)
+    <dir>/text_encoder/config.json                  the CLIPTextConfig          (transformers: flax_model.msgpack)
+    <dir>/text_encoder/flax_model.msgpack
+    <dir>/vae/config.json                           the FlaxAutoencoderKL config
+    <dir>/vae/diffusion_flax_model.msgpack
     <dir>/scheduler/scheduler_config.json           the DDIM placeholder of training_utils.py:997-1004
     <dir>/model_index.json
 
-and `from_pretrained` reads the same files back (training_utils.py:209-214). This module writes / reads the UNet part
-(the model this framework trains) bit-exactly, plus what the reference never saves but SURVEY asks to keep exportable:
+and `from_pretrained` reads the same files back (training_utils.py:209-222). This module writes / reads the UNet, the
+text encoder and the VAE parameter trees bit-exactly (`save_model` for a TrainState, `save_pipeline` with the
+reference's own `save_model` argument list), plus what the reference never saves but SURVEY asks to keep exportable:
 the 8-bit Lion state (`optimizer/lion8_state.msgpack`: int8 codes + fp32 reciprocal-absmax scales per quantised leaf in
 the reference's (n/bs, bs) / (n/bs, 1) layout, fp32 momentum otherwise, counters) and the EMA tree.
 
@@ -168,6 +173,93 @@ def save_model(state, output_dir: str, *, unet_ema_params: Optional[dict] = None
                 "block_size": np.int32(a.block_size), "mu_quant": lion.lion.mu_quant}
         with open(os.path.join(output_dir, "optimizer", "lion8_state.msgpack"), "wb") as f:
             f.write(msgpack_serialize(tree))
+
+
+def clip_config_dict(cfg) -> dict:
+    """config.json of transformers' CLIPTextModel for a clip.CLIPTextConfig (transformers field names)."""
+    return {"architectures": ["CLIPTextModel"], "model_type": "clip_text_model", "vocab_size": cfg.vocab_size,
+            "hidden_size": cfg.hidden_size, "intermediate_size": cfg.intermediate_size,
+            "num_hidden_layers": cfg.num_hidden_layers, "num_attention_heads": cfg.num_attention_heads,
+            "max_position_embeddings": cfg.max_position_embeddings, "hidden_act": cfg.hidden_act,
+            "layer_norm_eps": cfg.layer_norm_eps, "attention_dropout": 0.0, "dropout": 0.0}
+
+
+def vae_config_dict(cfg) -> dict:
+    """config.json of FlaxAutoencoderKL (diffusers 0.21.4 field names) for a vae.VAEConfig."""
+    n = len(cfg.block_out_channels)
+    return {"_class_name": "FlaxAutoencoderKL", "_diffusers_version": "0.21.4", "in_channels": cfg.in_channels,
+            "out_channels": cfg.in_channels, "down_block_types": ["DownEncoderBlock2D"] * n,
+            "up_block_types": ["UpDecoderBlock2D"] * n, "block_out_channels": list(cfg.block_out_channels),
+            "layers_per_block": cfg.layers_per_block, "act_fn": "silu", "latent_channels": cfg.latent_channels,
+            "norm_num_groups": cfg.norm_num_groups, "sample_size": 512, "scaling_factor": cfg.scaling_factor}
+
+
+def _write_tree(directory: str, filename: str, tree, config: Optional[dict]) -> None:
+    os.makedirs(directory, exist_ok=True)
+    with open(os.path.join(directory, filename), "wb") as f:
+        f.write(msgpack_serialize(tree))
+    if config is not None:
+        with open(os.path.join(directory, "config.json"), "w") as f:
+            json.dump(config, f, indent=2)
+
+
+def save_pipeline(model_object_dict: dict, tokenizer_object: Any, unet_params: dict, text_encoder_params: dict,
+                  vae_params: dict, output_dir: str) -> None:
+    """The reference's save_model (training_utils.py:986-1025), same argument list: `model_object_dict` holds the module
+    stand-ins {"unet": UNetModel, "text_encoder": clip.CLIPTextModel, "vae": vae.AutoencoderKL}; the three parameter
+    trees (Flax layouts; device tensors or NumPy) go to the diffusers folder layout with the DDIM placeholder scheduler.
+    `tokenizer_object`: saved through its own `save_pretrained(<dir>/tokenizer)` when it has one (CLIPTokenizer)."""
+    devs = {v.device for t in (unet_params, text_encoder_params, vae_params) if t is not None
+            for v in _flat_leaves(t) if isinstance(v, torch.Tensor) and v.is_cuda}
+    for d in devs:
+        torch.cuda.synchronize(d)
+    index = {"_class_name": "FlaxStableDiffusionPipeline", "_diffusers_version": "0.21.4",
+             "scheduler": ["diffusers", "FlaxDDIMScheduler"]}
+    if unet_params is not None:
+        _write_tree(os.path.join(output_dir, "unet"), "diffusion_flax_model.msgpack", unet_params,
+                    unet_config_dict(model_object_dict["unet"].config))
+        index["unet"] = ["diffusers", "FlaxUNet2DConditionModel"]
+    if text_encoder_params is not None:
+        _write_tree(os.path.join(output_dir, "text_encoder"), "flax_model.msgpack", text_encoder_params,
+                    clip_config_dict(model_object_dict["text_encoder"].config))
+        index["text_encoder"] = ["transformers", "FlaxCLIPTextModel"]
+    if vae_params is not None:
+        _write_tree(os.path.join(output_dir, "vae"), "diffusion_flax_model.msgpack", vae_params,
+                    vae_config_dict(model_object_dict["vae"].config))
+        index["vae"] = ["diffusers", "FlaxAutoencoderKL"]
+    if tokenizer_object is not None and hasattr(tokenizer_object, "save_pretrained"):
+        tokenizer_object.save_pretrained(os.path.join(output_dir, "tokenizer"))
+        index["tokenizer"] = ["transformers", "CLIPTokenizer"]
+    os.makedirs(os.path.join(output_dir, "scheduler"), exist_ok=True)
+    with open(os.path.join(output_dir, "scheduler", "scheduler_config.json"), "w") as f:
+        json.dump(DDIM_PLACEHOLDER, f, indent=2)
+    with open(os.path.join(output_dir, "model_index.json"), "w") as f:
+        json.dump(index, f, indent=2)
+
+
+def _flat_leaves(tree):
+    for v in tree.values():
+        if isinstance(v, dict):
+            yield from _flat_leaves(v)
+        else:
+            yield v
+
+
+def _load_tree(model_dir: str, subfolder: str, filename: str) -> dict:
+    sub = os.path.join(model_dir, subfolder)
+    path = os.path.join(sub if os.path.isdir(sub) else model_dir, filename)
+    with open(path, "rb") as f:
+        return msgpack_restore(f.read())
+
+
+def load_text_encoder_params(model_dir: str) -> dict:
+    """FlaxCLIPTextModel.from_pretrained(..., subfolder="text_encoder") parameter tree (training_utils.py:215-217)."""
+    return _load_tree(model_dir, "text_encoder", "flax_model.msgpack")
+
+
+def load_vae_params(model_dir: str) -> dict:
+    """FlaxAutoencoderKL.from_pretrained(..., subfolder="vae") parameter tree (training_utils.py:218-222)."""
+    return _load_tree(model_dir, "vae", "diffusion_flax_model.msgpack")
 
 
 def load_unet_params(model_dir: str) -> dict:

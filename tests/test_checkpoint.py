@@ -91,3 +91,47 @@ def test_save_and_load_reproduce_the_train_state(cuda, tmp_path):
     torch.cuda.synchronize()
     assert float(m1["loss"]) == float(m2["loss"])
     assert float((st2.arena.master != state.arena.master).float().mean()) < 1e-3  # wgrad red.add order only
+
+
+def test_save_pipeline_writes_the_three_models_in_the_diffusers_layout(tmp_path):
+    """The reference's save_model argument list (training_utils.py:986-1025); CPU only (NumPy / CPU-tensor trees)."""
+    from stable_diffusion_training_b200 import clip as PC
+    from stable_diffusion_training_b200 import lion_quant as LQ
+    from stable_diffusion_training_b200 import training_utils as TU
+    from stable_diffusion_training_b200 import unet as PU
+    from stable_diffusion_training_b200 import vae as PV
+    up = PU.init_params_numpy(PU.TINY, 0)
+    tp = PC.init_params_numpy(PC.TINY_CLIP, 1)
+    vp = dict(PV.init_params_numpy(PV.TINY_VAE, 2), **PV.init_decoder_params_numpy(PV.TINY_VAE, 2))
+    models = {"unet": TU.UNetModel(PU.TINY), "text_encoder": PC.CLIPTextModel(PC.TINY_CLIP),
+              "vae": PV.AutoencoderKL(PV.TINY_VAE)}
+
+    class Tok:
+        def save_pretrained(self, d):
+            os.makedirs(d, exist_ok=True)
+            open(os.path.join(d, "vocab.json"), "w").write("{}")
+
+    ttree = LQ.unflatten_dict({k: torch.from_numpy(v) for k, v in tp.items()})   # tensors and arrays both serialise
+    CK.save_pipeline(models, Tok(), LQ.unflatten_dict(up), ttree, LQ.unflatten_dict(vp), str(tmp_path))
+    for rel in ("unet/diffusion_flax_model.msgpack", "unet/config.json", "text_encoder/flax_model.msgpack",
+                "text_encoder/config.json", "vae/diffusion_flax_model.msgpack", "vae/config.json",
+                "scheduler/scheduler_config.json", "model_index.json", "tokenizer/vocab.json"):
+        assert os.path.exists(os.path.join(tmp_path, rel)), rel
+    idx = json.load(open(os.path.join(tmp_path, "model_index.json")))
+    assert idx["_class_name"] == "FlaxStableDiffusionPipeline" and idx["text_encoder"] == ["transformers", "FlaxCLIPTextModel"]
+    assert idx["vae"] == ["diffusers", "FlaxAutoencoderKL"] and idx["scheduler"] == ["diffusers", "FlaxDDIMScheduler"]
+    sc = json.load(open(os.path.join(tmp_path, "scheduler", "scheduler_config.json")))
+    assert sc["prediction_type"] == "v_prediction" and sc["beta_schedule"] == "scaled_linear"   # training_utils.py:997-1004
+    cc = json.load(open(os.path.join(tmp_path, "text_encoder", "config.json")))
+    assert cc["hidden_size"] == PC.TINY_CLIP.hidden_size and cc["hidden_act"] == "quick_gelu"
+    vc = json.load(open(os.path.join(tmp_path, "vae", "config.json")))
+    assert vc["block_out_channels"] == list(PV.TINY_VAE.block_out_channels) and vc["scaling_factor"] == 0.18215
+    for loaded, want in ((CK.load_unet_params(str(tmp_path)), up), (CK.load_text_encoder_params(str(tmp_path)), tp),
+                         (CK.load_vae_params(str(tmp_path)), vp)):
+        flat = LQ.flatten_dict(loaded)
+        assert set(flat) == set(want)
+        assert all(flat[k].dtype == np.float32 and np.array_equal(flat[k], want[k]) for k in want)
+    # partial saves: what is None is left out of the folder and of the index
+    CK.save_pipeline(models, None, LQ.unflatten_dict(up), None, None, str(tmp_path / "unet_only"))
+    idx = json.load(open(os.path.join(tmp_path, "unet_only", "model_index.json")))
+    assert "text_encoder" not in idx and "vae" not in idx and "tokenizer" not in idx
