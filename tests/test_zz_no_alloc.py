@@ -4,7 +4,6 @@ caller-provided workspace. Called through the C ABI (ctypes), checked against th
 within the tolerance of tests/test_ops_gpu.py's column-sum checks (rtol 1e-4, atol 1e-2), on two calls in a row (the
 second with other data and another shape: the array keeps the first call's contents), plus the size limit and the
 "allocates nothing" claim as far as the process can see it. The file is named to be collected last."""
-import ctypes as C
 
 import pytest
 import torch
@@ -34,6 +33,11 @@ def test_static_scratch_colsum_matches_the_workspace_entry_point(cuda):
     ws = torch.empty(l.sdb_colsum_workspace_bytes(32768, 2560), dtype=torch.uint8, device=cuda)
     for x, ref in zip(xs, refs):
         _reference_colsum(l, x, ref, ws)
+    # one untimed call first: CUDA loads a kernel's code lazily at its first launch, which may take device memory that
+    # has nothing to do with the entry point (the second-stage kernel is first launched here in a fresh process)
+    warm = torch.empty(cases[0][1], device=cuda)
+    assert l.sdb_colsum_bf16_static(xs[0].data_ptr(), xs[0].stride(0), cases[0][0], cases[0][1], warm.data_ptr(),
+                                    _lib.stream_ptr()) == 0, l.sdb_last_error_string().decode()
     torch.cuda.synchronize()
     alloc0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
     free0 = torch.cuda.mem_get_info()[0]
