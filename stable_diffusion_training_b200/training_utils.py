@@ -24,7 +24,7 @@ from __future__ import annotations
 
 import os
 from dataclasses import dataclass
-from typing import Any, Dict, List, Optional, Tuple
+from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 import torch
@@ -76,6 +76,44 @@ def create_lion_optimizer(params: dict, cfg: TrainingConfig = TrainingConfig()) 
                         b1=0.9, b2=0.99, weight_decay=1e-2 * cfg.adam_to_lion_scale_factor, mask=wd_mask,
                         block_size=cfg.lion_8bit_block_size, excluded_layer_mask=q_mask)
     return LQ.chain(LQ.clip_by_global_norm(1), lion)
+
+
+def create_lion_optimizer_states(models: dict, train_unet: bool = True, train_text_encoder: bool = True,
+                                 adam_to_lion_scale_factor: int = 7, u_net_learning_rate: float = 1e-6,
+                                 text_encoder_learning_rate: float = 1e-6,
+                                 excluded_layer_pattern_from_weight_decay: Sequence[str] = (),
+                                 excluded_layer_from_quantization: Sequence[str] = (),
+                                 lion_8bit_block_size: Optional[int] = None, quantize_unet_state: bool = False,
+                                 quantize_text_encoder_state: bool = False, device="cuda") -> dict:
+    """create_lion_optimizer_states (training_utils.py:281-428), same arguments and result:
+    models = {"unet": {"unet_model", "unet_params"}, "text_encoder": {"text_encoder_model", "text_encoder_params"}} ->
+    {"unet_state": TrainState | None, "text_encoder_state": TrainState | None}, each over
+    clip_by_global_norm(1) -> Lion(lr / scale, b1 .9, b2 .99, weight_decay 1e-2 * scale, decay mask by path component),
+    8-bit block-quantised momentum for the leaves the quantisation list does not exclude when quantize_*_state is set
+    (else fp32 momentum everywhere: the reference's optax.lion branch). `device`: where the states live (the reference
+    builds them on the host and device_puts them later, training_utils.py:446-460)."""
+    out = {"unet_state": None, "text_encoder_state": None}
+
+    def build(params, lr, quantize):
+        wd_mask = create_mask(params, list(excluded_layer_pattern_from_weight_decay)) \
+            if excluded_layer_pattern_from_weight_decay else None
+        q_mask = create_mask(params, list(excluded_layer_from_quantization)) \
+            if (quantize and lion_8bit_block_size is not None) else LQ.tree_map(lambda _p: False, params)
+        lion = LQ.lion_8bit(learning_rate=LQ.constant_schedule(lr / adam_to_lion_scale_factor), b1=0.9, b2=0.99,
+                            weight_decay=1e-2 * adam_to_lion_scale_factor, mask=wd_mask,
+                            block_size=lion_8bit_block_size or 16, excluded_layer_mask=q_mask)
+        return LQ.chain(LQ.clip_by_global_norm(1), lion)
+
+    if train_unet:
+        p = models["unet"]["unet_params"]
+        out["unet_state"] = TrainState.create(apply_fn=models["unet"]["unet_model"].apply, params=p,
+                                              tx=build(p, u_net_learning_rate, quantize_unet_state), device=device)
+    if train_text_encoder:
+        p = models["text_encoder"]["text_encoder_params"]
+        out["text_encoder_state"] = TrainState.create(
+            apply_fn=models["text_encoder"]["text_encoder_model"].__call__, params=p,
+            tx=build(p, text_encoder_learning_rate, quantize_text_encoder_state), device=device)
+    return out
 
 
 # ---------------------------------------------------------------------------------------------------------------

@@ -10,6 +10,8 @@ PyTorch CLIPTextModel (tests/test_oracle_clip.py):
    gradient sets vs the oracle; compiled (CUDA graph) == eager.
 """
 
+import math
+
 import numpy as np
 import pytest
 import torch
@@ -256,3 +258,49 @@ def test_text_encoder_ema_follows_the_reference_rule(cuda, mode):
     if mode == "graph":
         with pytest.raises(ValueError, match="text_encoder_ema_params"):
             TU.compile_train_step(ustate, sched, text_encoder_state=tstate, text_encoder_ema_params={"x": 1}, ema_rate=rate)
+
+
+def test_create_lion_optimizer_states_mirrors_the_reference_factory(cuda):
+    """training_utils.py:281-428: {"unet_state", "text_encoder_state"} from the models dict; the states it builds step
+    exactly like states built by hand with the same hyper-parameters; without quantisation every leaf keeps an fp32
+    momentum (the reference's optax.lion branch)."""
+    ucfg, tcfg = PU.TINY, CL.TINY_CLIP
+    cfgd = TU.TrainingConfig()
+
+    def models():
+        return {"unet": {"unet_model": TU.UNetModel(ucfg), "unet_params": LQ.unflatten_dict(PU.init_params_numpy(ucfg, 0))},
+                "text_encoder": {"text_encoder_model": CL.CLIPTextModel(tcfg),
+                                 "text_encoder_params": LQ.unflatten_dict(CL.init_params_numpy(tcfg, 0))}}
+
+    kw = dict(excluded_layer_pattern_from_weight_decay=list(cfgd.excluded_layer_pattern_from_weight_decay),
+              excluded_layer_from_quantization=list(cfgd.excluded_layer_from_quantization), lion_8bit_block_size=16,
+              device=cuda)
+    st = TU.create_lion_optimizer_states(models(), quantize_unet_state=True, quantize_text_encoder_state=True, **kw)
+    assert set(st) == {"unet_state", "text_encoder_state"}
+    ua, ta = st["unet_state"], st["text_encoder_state"]
+    assert ua.arena.n_quant > 0 and ta.arena.n_quant > 0
+    only_unet = TU.create_lion_optimizer_states(models(), train_text_encoder=False, quantize_unet_state=True, **kw)
+    assert only_unet["text_encoder_state"] is None and only_unet["unet_state"] is not None
+    plain = TU.create_lion_optimizer_states(models(), **kw)   # quantize_* default False
+    assert plain["unet_state"].arena.n_quant == 0 and plain["text_encoder_state"].arena.n_quant == 0
+    mu = LQ.flatten_dict(plain["unet_state"].opt_state[1].lion.mu_quant)
+    assert all(isinstance(v, torch.Tensor) and v.dtype == torch.float32 for v in mu.values())
+    # hand-built reference states
+    utree = LQ.unflatten_dict(PU.init_params_numpy(ucfg, 0))
+    ub = TU.TrainState.create(apply_fn=TU.UNetModel(ucfg).apply, params=utree, tx=TU.create_lion_optimizer(utree),
+                              device=cuda)
+    _, _, tb = _text_state(cuda, tcfg, seed=0)
+    sched = TU.default_scheduler(cuda, "scaled_linear", "epsilon")
+    for s in (1, 2):
+        b = {k: torch.from_numpy(v).to(cuda) for k, v in _joint_batch(2, 2, 16, tcfg.vocab_size, s).items()}
+        ua, ma = TU.train_step(ua, b, None, sched, text_encoder_state=ta)
+        ub, mb = TU.train_step(ub, b, None, sched, text_encoder_state=tb)
+    torch.cuda.synchronize()
+    assert float(ma["loss"]) == float(mb["loss"])
+    assert float((ua.arena.master != ub.arena.master).float().mean()) < 1e-3   # red.add weight gradients: 1e-7 noise
+    assert float((ta.arena.master != tb.arena.master).float().mean()) < 1e-3
+    # the unquantised states train too
+    pu, pt = plain["unet_state"], plain["text_encoder_state"]
+    pu, mp = TU.train_step(pu, b, None, sched, text_encoder_state=pt)
+    torch.cuda.synchronize()
+    assert math.isfinite(float(mp["loss"])) and int(pt.step) == 1
