@@ -34,6 +34,15 @@ def test_ddim_timesteps_follow_set_timesteps():
     assert OP.ddim_timesteps(4, steps_offset=1).tolist() == [751, 501, 251, 1]
 
 
+def test_ddim_timesteps_match_the_reference_run_golden():
+    """tests/golden/ddim_ref.npz was produced by the UNMODIFIED reference scheduler under the jax shim
+    (oracle/make_golden.py:ddim_cases: 50 steps, steps_offset 1)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ddim_ref.npz"))
+    for one in (0, 1):
+        assert np.array_equal(OP.ddim_timesteps(50, 1000, steps_offset=1), np.asarray(g[f"timesteps/{one}"]).astype(np.int64))
+
+
 def test_generate_shapes_range_and_determinism():
     p = _params()
     img, lat = OP.generate(TINY_UNET, OC.TINY_CLIP, OV.TINY_VAE, p, _ids(2, 0), _ids(2, 1), OT.PRNGKey(5), 2, 32, 48, 7.5,
